@@ -1,0 +1,148 @@
+/*
+ * tlb200.h — C ABI of libtlb200.so, the B200 (sm_100a) backend for TileLang's
+ * dense-contraction path (T.gemm fed by T.copy global->shared staging).
+ *
+ * Every entry point below replaces one piece of the host C ABI that the
+ * reference generates per JIT-compiled kernel, or one compile-time helper that
+ * a maintainer needs at the same boundary.  Reference citations are to the
+ * Tilelang-Mesh snapshot (TileLang 0.1.7 lineage):
+ *
+ *   generated host trio   tilelang/jit/adapter/wrapper.py:31-51
+ *                         (`init`, `call`, `get_last_error`)
+ *   call() body           tilelang/jit/adapter/wrapper.py:202-295
+ *   TMA descriptor build  tilelang/jit/adapter/wrapper.py:76-99,
+ *                         src/runtime/runtime.cc:98-110
+ *   instr descriptor      src/op/tcgen5_meta.h:94-172
+ *   atom selection        src/op/tcgen5_meta.h:21-92
+ *   smem descriptor       src/tl_templates/cuda/common.h:481-496
+ *
+ * Conventions (same as the reference's generated code): plain pointers and
+ * sizes only, `int` return 0 = ok / non-zero = error, message retrievable as a
+ * C string.  Unlike the reference (one process-global 1024-byte buffer) the
+ * error string is thread-local.  The library keeps no pointer past a call; all
+ * tensors stay owned by the caller (torch in the Python adapter).
+ */
+#ifndef TLB200_H_
+#define TLB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TLB200_ABI_VERSION 1
+
+/* Element types.  Values follow the DLPack-free compact enum used by the
+ * Python adapter; names follow tilelang/utils/tensor.py:34-51. */
+typedef enum tlb200_dtype {
+  TLB200_FLOAT16 = 0,      /* "float16"      */
+  TLB200_BFLOAT16 = 1,     /* "bfloat16"     */
+  TLB200_FLOAT8_E4M3 = 2,  /* "float8_e4m3"  (torch.float8_e4m3fn) */
+  TLB200_FLOAT8_E5M2 = 3,  /* "float8_e5m2"  */
+  TLB200_FLOAT32 = 4       /* "float32"/"float" (output / accumulator only) */
+} tlb200_dtype;
+
+/* Epilogue flags (fused into the TMEM->global drain). */
+#define TLB200_EPI_NONE 0u
+#define TLB200_EPI_RELU 1u /* examples/quickstart.py:42-43: C = max(C, 0) */
+
+/*
+ * One dense contraction  C[M,N] = alpha * op(A) * op(B)  with fp32 accumulate
+ * and a single round-to-nearest-even at the output cast — the whole-kernel
+ * meaning of a TileLang GEMM program (T.copy A/B tiles -> T.gemm -> T.copy C).
+ *
+ *   trans_a == 0 : A is [M,K] row-major (K contiguous), lda = row stride
+ *   trans_a == 1 : A is [K,M] row-major (M contiguous), lda = row stride
+ *   trans_b == 1 : B is [N,K] row-major (K contiguous)      <- benchmark/matmul
+ *   trans_b == 0 : B is [K,N] row-major (N contiguous)      <- examples/quickstart.py
+ * Same meaning as transpose_A / transpose_B of T.gemm
+ * (tilelang/language/gemm.py:105-116, K_A == K_B check at :78-81).
+ * Leading dimensions are in ELEMENTS.
+ *
+ * The cfg_* fields are optional tuning hints (0 = choose automatically); they
+ * play the role of the tile-program's block_M/N/K, num_stages and
+ * T.use_swizzle(panel) knobs but never change the numerical contract.
+ */
+typedef struct tlb200_gemm_desc {
+  int32_t abi_version; /* must be TLB200_ABI_VERSION */
+  int32_t m, n, k;
+  int32_t ab_dtype; /* tlb200_dtype of A and B (must be equal, as T.gemm) */
+  int32_t c_dtype;  /* tlb200_dtype of C */
+  int32_t trans_a, trans_b;
+  int64_t lda, ldb, ldc;
+  float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
+  uint32_t epilogue;  /* TLB200_EPI_* */
+  int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles */
+  int32_t cfg_block_n;   /* 0 auto, else multiple of 16 (32 for cta_group 2) in [16,256] */
+  int32_t cfg_stages;    /* 0 auto */
+  int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
+  int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */
+  int32_t reserved[3];
+} tlb200_gemm_desc;
+
+/* The configuration the library resolved for a descriptor (for reports/tests). */
+typedef struct tlb200_gemm_plan {
+  int32_t cta_group, block_m, block_n, block_k, stages;
+  int32_t tiles_m, tiles_n, grid, threads, smem_bytes;
+  int32_t raster, epilogue, tmem_cols;
+  uint32_t instr_desc;
+  int32_t reserved[2];
+} tlb200_gemm_plan;
+
+/* Replaces the generated `int init()` (wrapper.py:40-44): binds the CUDA
+ * driver entry points, raises the dynamic-smem limit of every kernel on
+ * `device` and caches its SM count.  Idempotent, may be called per device. */
+int tlb200_init(int device);
+
+/* Replaces the generated `int call(A, B, C, ..., cudaStream_t)`
+ * (wrapper.py:46-51, 202-295): encodes the TMA descriptors on the stack and
+ * launches ONE persistent kernel on `stream` (a cudaStream_t; 0 = default) of
+ * the CURRENT device.  A, B, C are device pointers.  Asynchronous. */
+int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
+                void* stream);
+
+/* Same contract through HOST buffers: stages A and B to the device, runs
+ * tlb200_gemm and copies C back, all on `stream`, then synchronises it.
+ * `workspace` is a caller-owned device buffer of at least
+ * tlb200_gemm_host_workspace_bytes(desc) bytes (the library never allocates).
+ * This is the host-buffer form of the reference's adapter call path
+ * (tilelang/jit/adapter/cython/cython_wrapper.pyx:164-287 with CPU tensors moved
+ * by the caller) and is what bench.py times as `e2e`. */
+int64_t tlb200_gemm_host_workspace_bytes(const tlb200_gemm_desc* desc);
+int tlb200_gemm_host(const tlb200_gemm_desc* desc, const void* host_a, const void* host_b,
+                     void* host_c, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Resolve the plan without launching (pure host arithmetic; no GPU needed). */
+int tlb200_gemm_plan_query(const tlb200_gemm_desc* desc, int sm_count, tlb200_gemm_plan* out);
+
+/* Replaces `const char* get_last_error()` (wrapper.py:36-38). Thread-local. */
+const char* tlb200_last_error(void);
+
+/* ABI version of the loaded library. */
+int tlb200_abi_version(void);
+
+/* Number of kernels this library has launched in the calling process (for the
+ * `gpu_launches` figure bench.py reports). */
+int64_t tlb200_launch_count(void);
+
+/* Restates GetTCGEN5InstrDesc (src/op/tcgen5_meta.h:94-172): the 32-bit
+ * tcgen05.mma instruction descriptor.  Pure arithmetic; no GPU needed.
+ * Returns 0 on unsupported arguments (and sets the error string). */
+uint32_t tlb200_instr_desc(int atom_m, int atom_n, int atom_k, int ab_dtype, int c_dtype,
+                           int a_is_k_major, int b_is_k_major, int scale_in_a, int scale_in_b);
+
+/* Restates GetTCGEN5MMAMeta (src/op/tcgen5_meta.h:21-92): atom the REFERENCE
+ * would pick for a (M,N,K) tile.  out5 = {atom_m, atom_n, atom_k, ws, 2cta}.
+ * Returns 1 if supported, 0 if not. */
+int tlb200_tcgen5_meta(int m, int n, int k, int ab_dtype, int c_dtype, int32_t* out5);
+
+/* Restates initialize_tcgen05_descriptor (src/tl_templates/cuda/common.h:481-496):
+ * 64-bit shared-memory matrix descriptor from a shared-window byte address. */
+uint64_t tlb200_smem_desc(uint32_t smem_addr, int leading_byte_offset_16, int stride_byte_offset_16,
+                          int base_offset, int leading_is_absolute, int swizzle_mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TLB200_H_ */

@@ -1,0 +1,416 @@
+// gemm_sm100.cuh — the persistent, warp-specialised tcgen05 GEMM kernel.
+//
+// One kernel covers the whole TileLang GEMM program  (T.copy A,B tiles -> T.gemm -> T.copy C):
+//
+//   warp 0  producer : TMA bulk-tensor loads of the A / B K-blocks into 128B-swizzled smem,
+//                      multi-stage full/empty mbarrier ring          (replaces T.copy g->s:
+//                      src/op/copy.cc:1399-1688, tl::tma_load copy_sm90.h:17-268,
+//                      and the cp.async path the reference is forced onto, copy.h:16-78)
+//   warp 1  MMA      : one lane issues tcgen05.mma (cta_group::1 or ::2) into a
+//                      double-buffered TMEM accumulator; tcgen05.commit frees smem stages
+//                      and publishes finished accumulators     (replaces tl::tcgen5mma_gemm_ss
+//                      gemm_sm100.h:342-436 and tcgen05_macro_generator.py:140-349)
+//   warp 2  TMEM     : tcgen05.alloc / dealloc                  (replaces tcgen_05.h:13-27)
+//   warp 3  idle
+//   warps 4-7 epilogue: tcgen05.ld -> alpha/relu -> cast -> swizzled smem -> TMA store (or
+//                      predicated 16 B global stores)           (replaces copy.cc:1191-1377
+//                      tmem->fragment, copy.cc:920-958 fragment->shared->global)
+//
+// Tiles: BLOCK_M = 128 rows per CTA (256 per 2-CTA pair), BLOCK_N <= 256 columns,
+// BLOCK_K = 128 bytes of K per stage (64 x 16-bit or 128 x 8-bit elements) = one 128B
+// swizzle atom, consumed by 4 MMAs of K = 32 bytes each.  A static persistent scheduler walks
+// the tile grid in L2-friendly row groups (replaces threadblock_swizzle.h:7-41).
+//
+// Pipeline protocol = the reference's warp-specialised ring: parity
+// (k / stages) & 1, producer waits the inverted parity, expect_tx = bytes of the stage.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+
+#include "ptx.cuh"
+
+namespace tlb200 {
+
+constexpr int kBlockM = 128;          // rows of C per CTA (TMEM lanes)
+constexpr int kStageRowBytes = 128;   // K bytes per stage row = one 128B swizzle atom
+constexpr int kUmmaKBytes = 32;       // K bytes consumed by one tcgen05.mma
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple of 4)
+constexpr int kEpiWarps = 4;
+constexpr int kEpiBufBytes = 32 * 128;     // one warp's staging slab: 32 rows x 128 B
+constexpr int kEpiBufsPerWarp = 2;
+constexpr int kMaxStages = 12;
+constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
+
+enum OutKind : int { kOutF16 = 0, kOutBF16 = 1, kOutE4M3 = 2, kOutE5M2 = 3, kOutF32 = 4 };
+
+struct alignas(64) GemmKernelParams {
+  CUtensorMap tm_a;  // operand A boxes
+  CUtensorMap tm_b;  // operand B boxes
+  CUtensorMap tm_c;  // C store boxes (32 rows x 128 B), valid iff epi_tma
+  void* c;
+  long long ldc;  // elements
+  int m, n;
+  int num_k_blocks;
+  int tiles_m, tiles_n;  // in units of (kBlockM * cta_group) rows, block_n columns
+  int raster;            // tile rows per raster group
+  int block_n;
+  int stages;
+  int k_elems_per_block;  // 128 / sizeof(ab)
+  int a_mn_major, b_mn_major;
+  int a_boxes, b_boxes;            // TMA issues per stage for A / B
+  int a_box_bytes, b_box_bytes;    // bytes each issue writes
+  int b_rows_per_cta;              // block_n / cta_group
+  uint32_t idesc;
+  uint32_t desc_hi_a, desc_hi_b;   // upper 32 bits of the smem matrix descriptors (SBO, version, swizzle)
+  uint32_t desc_lbo_a, desc_lbo_b; // (LBO >> 4) << 16: the leading-byte-offset field of the lower word
+  uint32_t kadv_a, kadv_b;         // (bytes >> 4) to advance desc.lo per MMA along K
+  int out_kind;
+  int is_f8;
+  int epi_tma;
+  int relu;
+  float alpha;
+};
+
+// ---------------------------------------------------------------- output conversion helpers
+template <int kOut>
+struct OutTraits;
+template <>
+struct OutTraits<kOutF16> { static constexpr int kBytes = 2; };
+template <>
+struct OutTraits<kOutBF16> { static constexpr int kBytes = 2; };
+template <>
+struct OutTraits<kOutE4M3> { static constexpr int kBytes = 1; };
+template <>
+struct OutTraits<kOutE5M2> { static constexpr int kBytes = 1; };
+template <>
+struct OutTraits<kOutF32> { static constexpr int kBytes = 4; };
+
+// Convert 16/sizeof(out) consecutive fp32 values to one 16-byte packet, round-to-nearest-even
+// (reference epilogue: __float22bfloat162_rn / __float22half2_rn in generated code; fp8 through
+// cute::float_e4m3_t(float), common.h:505-523 = cvt.rn.satfinite).
+template <int kOut>
+__device__ __forceinline__ uint4 pack16(const float* v) {
+  uint4 r;
+  if constexpr (kOut == kOutBF16) {
+    __nv_bfloat162 p0 = __float22bfloat162_rn(make_float2(v[0], v[1]));
+    __nv_bfloat162 p1 = __float22bfloat162_rn(make_float2(v[2], v[3]));
+    __nv_bfloat162 p2 = __float22bfloat162_rn(make_float2(v[4], v[5]));
+    __nv_bfloat162 p3 = __float22bfloat162_rn(make_float2(v[6], v[7]));
+    r.x = *reinterpret_cast<uint32_t*>(&p0);
+    r.y = *reinterpret_cast<uint32_t*>(&p1);
+    r.z = *reinterpret_cast<uint32_t*>(&p2);
+    r.w = *reinterpret_cast<uint32_t*>(&p3);
+  } else if constexpr (kOut == kOutF16) {
+    __half2 p0 = __float22half2_rn(make_float2(v[0], v[1]));
+    __half2 p1 = __float22half2_rn(make_float2(v[2], v[3]));
+    __half2 p2 = __float22half2_rn(make_float2(v[4], v[5]));
+    __half2 p3 = __float22half2_rn(make_float2(v[6], v[7]));
+    r.x = *reinterpret_cast<uint32_t*>(&p0);
+    r.y = *reinterpret_cast<uint32_t*>(&p1);
+    r.z = *reinterpret_cast<uint32_t*>(&p2);
+    r.w = *reinterpret_cast<uint32_t*>(&p3);
+  } else if constexpr (kOut == kOutF32) {
+    r.x = __float_as_uint(v[0]);
+    r.y = __float_as_uint(v[1]);
+    r.z = __float_as_uint(v[2]);
+    r.w = __float_as_uint(v[3]);
+  } else {
+    constexpr __nv_fp8_interpretation_t kI = (kOut == kOutE4M3) ? __NV_E4M3 : __NV_E5M2;
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * i + 0], v[4 * i + 1]), __NV_SATFINITE, kI);
+      uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(v[4 * i + 2], v[4 * i + 3]), __NV_SATFINITE, kI);
+      w[i] = (lo & 0xffffu) | (hi << 16);
+    }
+    r.x = w[0]; r.y = w[1]; r.z = w[2]; r.w = w[3];
+  }
+  return r;
+}
+
+template <int kOut>
+__device__ __forceinline__ void store_scalar(void* c, long long idx, float v) {
+  if constexpr (kOut == kOutBF16) {
+    reinterpret_cast<__nv_bfloat16*>(c)[idx] = __float2bfloat16_rn(v);
+  } else if constexpr (kOut == kOutF16) {
+    reinterpret_cast<__half*>(c)[idx] = __float2half_rn(v);
+  } else if constexpr (kOut == kOutF32) {
+    reinterpret_cast<float*>(c)[idx] = v;
+  } else {
+    constexpr __nv_fp8_interpretation_t kI = (kOut == kOutE4M3) ? __NV_E4M3 : __NV_E5M2;
+    reinterpret_cast<uint8_t*>(c)[idx] = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, kI);
+  }
+}
+
+// ---------------------------------------------------------------- epilogue for one tile
+// Executed by the 4 epilogue warps.  Warp `q` owns TMEM lanes / tile rows [32q, 32q+32).
+// tmem_acc = TMEM address of the accumulator (lane 0, first column).
+template <int kOut>
+__device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_t tmem_acc, int q,
+                                              int lane, int row0, int col0, uint32_t stage_smem,
+                                              int& slab_iter) {
+  constexpr int kOB = OutTraits<kOut>::kBytes;
+  constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
+  constexpr int kPacketsPerLd = 32 * kOB / 16;  // 16 B packets produced by one x32 load
+  constexpr int kValsPerPacket = 16 / kOB;
+  const int grow = row0 + q * 32 + lane;  // global row of this thread
+  const uint32_t lane_taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
+  const float alpha = p.alpha;
+  const bool relu = p.relu != 0;
+
+  if (p.epi_tma) {
+    for (int cs = 0; cs < p.block_n; cs += kColsPerSlab) {
+      if (col0 + cs >= p.n) break;  // warp-uniform: remaining slabs are fully out of range
+      const uint32_t slab = stage_smem + (slab_iter & (kEpiBufsPerWarp - 1)) * kEpiBufBytes;
+      // The TMA store that last read this slab (two slabs ago) must have drained it.
+      if (lane == 0) tma_store_wait_read<kEpiBufsPerWarp - 1>();
+      __syncwarp();
+#pragma unroll
+      for (int l = 0; l < kColsPerSlab / 32; ++l) {
+        if (cs + l * 32 < p.block_n) {
+          uint32_t r[32];
+          tmem_ld_32x32(lane_taddr + cs + l * 32, r);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float x = __uint_as_float(r[i]) * alpha;
+            v[i] = relu ? fmaxf(x, 0.f) : x;
+          }
+#pragma unroll
+          for (int pk = 0; pk < kPacketsPerLd; ++pk) {
+            const int chunk = l * kPacketsPerLd + pk;  // 16 B chunk index in the 128 B row
+            const uint32_t addr = slab + lane * 128 + ((chunk ^ (lane & 7)) << 4);
+            uint4 w = pack16<kOut>(&v[pk * kValsPerPacket]);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w.x), "r"(w.y),
+                         "r"(w.z), "r"(w.w)
+                         : "memory");
+          }
+        }
+      }
+      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+      __syncwarp();
+      if (lane == 0) {
+        if (row0 + q * 32 < p.m) tma_store_2d(&p.tm_c, slab, col0 + cs, row0 + q * 32);
+        tma_store_commit();
+      }
+      ++slab_iter;
+    }
+  } else {
+    const bool row_ok = grow < p.m;
+    const bool vec_ok = ((p.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(p.c) % 16) == 0);
+    for (int cs = 0; cs < p.block_n; cs += 32) {
+      if (col0 + cs >= p.n) break;
+      uint32_t r[32];
+      tmem_ld_32x32(lane_taddr + cs, r);
+      tmem_ld_wait();
+      float v[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        float x = __uint_as_float(r[i]) * alpha;
+        v[i] = relu ? fmaxf(x, 0.f) : x;
+      }
+      if (row_ok) {
+        const int gcol = col0 + cs;
+        const long long base = static_cast<long long>(grow) * p.ldc + gcol;
+        if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.c) + base * kOB);
+#pragma unroll
+          for (int pk = 0; pk < kPacketsPerLd; ++pk) dst[pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (gcol + i < p.n) store_scalar<kOut>(p.c, base + i, v[i]);
+        }
+      }
+      __syncwarp();  // tcgen05.ld is .sync.aligned: re-converge after the predicated stores
+    }
+  }
+}
+
+// ---------------------------------------------------------------- the kernel
+template <int kCta>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (kCta == 2) ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
+
+  // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int stages = p.stages;
+  const uint32_t b_stage_bytes = static_cast<uint32_t>(p.b_rows_per_cta) * kStageRowBytes;
+  const uint32_t smem_a = smem_base;
+  const uint32_t smem_b = smem_a + stages * kABytesPerStage;
+  const uint32_t smem_epi = smem_b + stages * b_stage_bytes;
+  const uint32_t smem_bar = smem_epi + kEpiWarps * kEpiBufsPerWarp * kEpiBufBytes;
+  const uint32_t bar_full = smem_bar;                    // [stages]
+  const uint32_t bar_empty = bar_full + 8 * stages;      // [stages]
+  const uint32_t bar_tfull = bar_empty + 8 * stages;     // [2]
+  const uint32_t bar_tempty = bar_tfull + 16;            // [2]
+  const uint32_t smem_tptr = bar_tempty + 16;            // u32 TMEM base address
+  const uint32_t stage_tx_bytes = (kABytesPerStage + b_stage_bytes) * kCta;
+  const uint32_t tmem_cols = (2u * p.block_n <= 32u)    ? 32u
+                             : (2u * p.block_n <= 64u)  ? 64u
+                             : (2u * p.block_n <= 128u) ? 128u
+                             : (2u * p.block_n <= 256u) ? 256u
+                                                        : 512u;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_a);
+    tma_prefetch_desc(&p.tm_b);
+    if (p.epi_tma) tma_prefetch_desc(&p.tm_c);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
+      mbar_init(bar_empty + 8 * s, 1);  // one tcgen05.commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar_tfull + 8 * a, 1);                    // one tcgen05.commit
+      mbar_init(bar_tempty + 8 * a, kEpiWarps * kCta);    // one arrive per epilogue warp (per CTA)
+    }
+    fence_mbar_init();
+  }
+  __syncwarp();
+  if (warp == 2) tmem_alloc<kCta>(smem_tptr, tmem_cols);
+  tc_fence_before();
+  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int cluster_id = blockIdx.x / kCta;
+  const int num_clusters = gridDim.x / kCta;
+  const int nkb = p.num_k_blocks;
+
+  auto tile_coord = [&](int t, int& tm, int& tn) {
+    const int group = p.raster * p.tiles_n;
+    const int g = t / group;
+    const int first = g * p.raster;
+    const int rows = min(p.raster, p.tiles_m - first);
+    const int within = t - g * group;
+    tm = first + within % rows;
+    tn = within / rows;
+  };
+
+  if (warp == 0) {
+    // ===================================================== TMA producer (one lane)
+    if (lane == 0) {
+      const uint64_t pol = policy_evict_normal();
+      int s = 0;
+      uint32_t ph = 0;
+      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+        int tm, tn;
+        tile_coord(t, tm, tn);
+        const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
+        const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
+          const uint32_t full = bar_full + 8 * s;
+          if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
+          const int k0 = kb * p.k_elems_per_block;
+          const uint32_t dst_a = smem_a + s * kABytesPerStage;
+          const uint32_t dst_b = smem_b + s * b_stage_bytes;
+          // K-major operand: box = [rows x 128 B of K], coords {k, row}.
+          // MN-major operand: boxes = [K-block rows x 128 B of M/N], coords {row + j*span, k}.
+          for (int j = 0; j < p.a_boxes; ++j) {
+            const int c0 = p.a_mn_major ? row_a + j * p.k_elems_per_block : k0;
+            const int c1 = p.a_mn_major ? k0 : row_a + j * (p.a_box_bytes / kStageRowBytes);
+            if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
+            else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
+          }
+          for (int j = 0; j < p.b_boxes; ++j) {
+            const int c0 = p.b_mn_major ? row_b + j * p.k_elems_per_block : k0;
+            const int c1 = p.b_mn_major ? k0 : row_b + j * (p.b_box_bytes / kStageRowBytes);
+            if constexpr (kCta == 2) tma_load_2d_pair(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
+            else tma_load_2d(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
+          }
+          if (++s == stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer (one lane, leader CTA)
+    if (lane == 0 && leader) {
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1u;
+        mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * p.block_n;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
+          tc_fence_after();
+          const uint32_t a_lo = ((smem_a + s * kABytesPerStage) & 0x3FFFFu) >> 4;
+          const uint32_t b_lo = ((smem_b + s * b_stage_bytes) & 0x3FFFFu) >> 4;
+#pragma unroll
+          for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
+            const uint64_t da = (static_cast<uint64_t>(p.desc_hi_a) << 32) |
+                                (p.desc_lbo_a | ((a_lo + k * p.kadv_a) & 0x3FFFu));
+            const uint64_t db = (static_cast<uint64_t>(p.desc_hi_b) << 32) |
+                                (p.desc_lbo_b | ((b_lo + k * p.kadv_b) & 0x3FFFu));
+            const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+            if (p.is_f8) umma_ss<kCta, true>(d_tmem, da, db, p.idesc, acc);
+            else umma_ss<kCta, false>(d_tmem, da, db, p.idesc, acc);
+          }
+          umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
+          if (++s == stages) { s = 0; ph ^= 1u; }
+        }
+        umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ===================================================== epilogue warps
+    const int q = warp - kEpiWarp0;  // == warp % 4: the TMEM lane quarter this warp may read
+    const uint32_t my_stage = smem_epi + q * kEpiBufsPerWarp * kEpiBufBytes;
+    const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, 0) : bar_tempty;
+    int it = 0;
+    int slab_iter = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+      int tm, tn;
+      tile_coord(t, tm, tn);
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1u;
+      const int row0 = (tm * kCta + (int)cta_rank) * kBlockM;
+      const int col0 = tn * p.block_n;
+      mbar_wait(bar_tfull + 8 * as, aph, 3);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + as * p.block_n;
+      if (row0 < p.m) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
+        switch (p.out_kind) {
+          case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+          case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+          case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+          case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+          default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+        }
+      }
+      // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * as);
+        else mbar_arrive(bar_tempty + 8 * as);
+      }
+    }
+    if (p.epi_tma && lane == 0) tma_store_wait_all<0>();
+  }
+
+  // ---- teardown: nobody may still be using TMEM / peer smem when it is released
+  __syncwarp();  // re-converge the single-lane roles before the .aligned barriers
+  tc_fence_before();
+  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc<kCta>(tmem_base, tmem_cols);
+}
+
+}  // namespace tlb200

@@ -1,0 +1,515 @@
+// tlb200.cu — host side of libtlb200.so: the C ABI declared in include/tlb200.h.
+//
+// Mirrors the host wrapper the reference generates per kernel
+// (tilelang/jit/adapter/wrapper.py:31-51 trio, :76-99 TMA descriptor encode, :202-295 call):
+// validate -> plan -> encode CUtensorMaps on the stack -> one launch on the caller's stream.
+// No allocation, no retained pointers, thread-local error text.
+#include "tlb200.h"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "gemm_sm100.cuh"
+
+namespace {
+
+using namespace tlb200;
+
+thread_local char g_err[1024] = {0};
+std::atomic<long long> g_launches{0};
+
+int fail(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+// ---- driver entry point (bound at init; the library does not link libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+std::mutex g_init_mu;
+constexpr int kMaxDevices = 64;
+int g_sm_count[kMaxDevices] = {0};
+bool g_dev_ready[kMaxDevices] = {false};
+
+constexpr int kSmemLimit = 232448;  // 227 KiB opt-in per block on sm_100
+constexpr int kSmemFixed = 1024 /*alignment slack*/ + kEpiWarps * kEpiBufsPerWarp * kEpiBufBytes +
+                           (2 * kMaxStages + 4) * 8 + 16;
+
+int dtype_bytes(int dt) {
+  switch (dt) {
+    case TLB200_FLOAT16:
+    case TLB200_BFLOAT16: return 2;
+    case TLB200_FLOAT8_E4M3:
+    case TLB200_FLOAT8_E5M2: return 1;
+    case TLB200_FLOAT32: return 4;
+    default: return 0;
+  }
+}
+bool is_ab_dtype(int dt) {
+  return dt == TLB200_FLOAT16 || dt == TLB200_BFLOAT16 || dt == TLB200_FLOAT8_E4M3 ||
+         dt == TLB200_FLOAT8_E5M2;
+}
+
+uint32_t instr_desc_impl(int atom_m, int atom_n, int atom_k, int ab, int c, bool a_k_major,
+                         bool b_k_major, int sa, int sb) {
+  // Field map: src/op/tcgen5_meta.h:142-171.
+  uint32_t fmt;
+  switch (ab) {
+    case TLB200_FLOAT16: fmt = 0; break;
+    case TLB200_BFLOAT16: fmt = 1; break;
+    case TLB200_FLOAT8_E4M3: fmt = 0; break;
+    case TLB200_FLOAT8_E5M2: fmt = 1; break;
+    default: return 0;
+  }
+  uint32_t cfmt;
+  if (c == TLB200_FLOAT16) cfmt = 0;
+  else if (c == TLB200_FLOAT32) cfmt = 1;
+  else return 0;
+  if (atom_m % 16 || atom_n % 8 || (atom_k != 16 && atom_k != 32)) return 0;
+  if ((sa != 1 && sa != -1) || (sb != 1 && sb != -1)) return 0;
+  uint32_t d = 0;
+  d |= (cfmt & 3u) << 4;
+  d |= (fmt & 7u) << 7;
+  d |= (fmt & 7u) << 10;
+  d |= (sa == -1 ? 1u : 0u) << 13;
+  d |= (sb == -1 ? 1u : 0u) << 14;
+  d |= (a_k_major ? 0u : 1u) << 15;
+  d |= (b_k_major ? 0u : 1u) << 16;
+  d |= (static_cast<uint32_t>(atom_n >> 3) & 0x3fu) << 17;
+  d |= (static_cast<uint32_t>(atom_m >> 4) & 0x1fu) << 24;
+  return d;
+}
+
+uint64_t smem_desc_impl(uint32_t addr, int lbo16, int sbo16, int base_offset, int lbo_abs, int swz) {
+  // Bit layout: src/tl_templates/cuda/common.h:481-496 (Tcgen05SMemDescriptor).
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((addr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>(lbo16 & 0x3fff) << 16;
+  d |= static_cast<uint64_t>(sbo16 & 0x3fff) << 32;
+  d |= 1ull << 46;  // version_ = 1
+  d |= static_cast<uint64_t>(base_offset & 7) << 49;
+  d |= static_cast<uint64_t>(lbo_abs ? 1 : 0) << 52;
+  d |= static_cast<uint64_t>(swz & 7) << 61;
+  return d;
+}
+
+struct Resolved {
+  tlb200_gemm_plan plan;
+  int es, ob;             // operand / output element bytes
+  int span;               // elements per 128 B of an operand row
+  bool a_mn, b_mn;
+  int b_rows_per_cta;
+  int num_k_blocks;
+  bool epi_tma;
+};
+
+int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r) {
+  if (!d) return fail("tlb200: null descriptor");
+  if (d->abi_version != TLB200_ABI_VERSION)
+    return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
+                TLB200_ABI_VERSION);
+  if (d->m < 0 || d->n < 0 || d->k < 0) return fail("tlb200: negative extent (m=%d n=%d k=%d)", d->m, d->n, d->k);
+  if (!is_ab_dtype(d->ab_dtype))
+    return fail("tlb200: unsupported operand dtype %d (float16, bfloat16, float8_e4m3, float8_e5m2)", d->ab_dtype);
+  if (dtype_bytes(d->c_dtype) == 0) return fail("tlb200: unsupported output dtype %d", d->c_dtype);
+  r->es = dtype_bytes(d->ab_dtype);
+  r->ob = dtype_bytes(d->c_dtype);
+  r->span = 128 / r->es;
+  r->a_mn = d->trans_a != 0;
+  r->b_mn = d->trans_b == 0;
+  const long long a_cols = r->a_mn ? d->m : d->k, b_cols = r->b_mn ? d->n : d->k;
+  if (d->lda < a_cols) return fail("tlb200: lda=%lld < %lld", (long long)d->lda, a_cols);
+  if (d->ldb < b_cols) return fail("tlb200: ldb=%lld < %lld", (long long)d->ldb, b_cols);
+  if (d->ldc < d->n) return fail("tlb200: ldc=%lld < n=%d", (long long)d->ldc, d->n);
+  // TMA needs 16-byte row pitches (same constraint as the reference's bulk copy,
+  // src/op/copy.cc:1489-1499: strides in bytes, % 16, < 2^40).
+  if ((d->lda * r->es) % 16 || (d->ldb * r->es) % 16)
+    return fail("tlb200: operand row pitch must be a multiple of 16 bytes (lda=%lld ldb=%lld, %d-byte elements)",
+                (long long)d->lda, (long long)d->ldb, r->es);
+
+  tlb200_gemm_plan& p = r->plan;
+  memset(&p, 0, sizeof(p));
+  int cg = d->cfg_cta_group;
+  if (cg == 0) cg = (d->m > kBlockM) ? 2 : 1;
+  if (cg != 1 && cg != 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", cg);
+  if (sm_count > 0 && sm_count < 2) cg = 1;
+  int bn = d->cfg_block_n;
+  const int n_min = r->b_mn ? r->span * cg : 16 * cg;  // MN-major B is staged in whole 128 B spans
+  if (bn == 0) {
+    bn = 256;
+    while (bn / 2 >= d->n && bn / 2 >= n_min) bn /= 2;
+  }
+  if (bn < n_min || bn > 256 || bn % (16 * cg) || (r->b_mn && (bn / cg) % r->span))
+    return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need multiple of %d in [%d,256])", bn, cg,
+                r->b_mn ? ", N-major B" : "", r->b_mn ? r->span * cg : 16 * cg, n_min);
+  r->b_rows_per_cta = bn / cg;
+  const int per_stage = kABytesPerStage + r->b_rows_per_cta * kStageRowBytes;
+  int stages = d->cfg_stages;
+  const int max_stages = (kSmemLimit - kSmemFixed) / per_stage;
+  if (stages == 0) stages = max_stages < kMaxStages ? max_stages : kMaxStages;
+  if (stages < 2 || stages > kMaxStages || stages > max_stages)
+    return fail("tlb200: cfg_stages=%d out of range [2,%d]", stages, max_stages < kMaxStages ? max_stages : kMaxStages);
+  p.cta_group = cg;
+  p.block_m = kBlockM * cg;
+  p.block_n = bn;
+  p.block_k = r->span;
+  p.stages = stages;
+  p.tiles_m = (d->m + p.block_m - 1) / p.block_m;
+  p.tiles_n = (d->n + bn - 1) / bn;
+  r->num_k_blocks = (d->k + r->span - 1) / r->span;
+  const long long tiles = static_cast<long long>(p.tiles_m) * p.tiles_n;
+  const int sms = sm_count > 0 ? sm_count : 148;
+  long long clusters = sms / cg;
+  if (clusters > tiles) clusters = tiles;
+  if (clusters < 1) clusters = 1;
+  p.grid = static_cast<int>(clusters) * cg;
+  p.threads = kThreads;
+  p.smem_bytes = kSmemFixed + stages * per_stage;
+  p.raster = d->cfg_raster > 0 ? d->cfg_raster : (16 / cg);
+  int epi = d->cfg_epilogue;
+  const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0);
+  if (epi == 0) epi = tma_ok ? 2 : 1;
+  if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C and row pitch");
+  if (epi != 1 && epi != 2) return fail("tlb200: cfg_epilogue must be 0, 1 or 2");
+  p.epilogue = epi;
+  r->epi_tma = epi == 2;
+  p.tmem_cols = 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512;
+  p.instr_desc = instr_desc_impl(kBlockM * cg, bn, 32 / r->es, d->ab_dtype, TLB200_FLOAT32, !r->a_mn, !r->b_mn, 1, 1);
+  if (p.instr_desc == 0) return fail("tlb200: cannot encode instruction descriptor");
+  return 0;
+}
+
+CUtensorMapDataType tm_dtype(int dt) {
+  switch (dt) {
+    case TLB200_FLOAT16: return CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    case TLB200_BFLOAT16: return CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    case TLB200_FLOAT32: return CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    default: return CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  }
+}
+
+// 2-D row-major tensor [rows, cols] (cols contiguous, pitch `ld` elements) -> tiled map with a
+// [box_rows x box_cols] box and the 128B swizzle.
+int encode_2d(CUtensorMap* tm, int dt, const void* base, long long rows, long long cols, long long ld,
+              int box_cols, int box_rows, const char* what) {
+  const int eb = dtype_bytes(dt);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * eb};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult rc = g_encode(tm, tm_dtype(dt), 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS)
+    return fail("tlb200: cuTensorMapEncodeTiled(%s) failed with CUresult %d (base=%p rows=%lld cols=%lld ld=%lld box=%dx%d)",
+                what, (int)rc, base, rows, cols, ld, box_rows, box_cols);
+  return 0;
+}
+
+template <int kOut>
+__global__ void fill_zero_kernel(void* c, long long ldc, int m, int n) {
+  const long long total = static_cast<long long>(m) * n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / n, col = i - r * n;
+    store_scalar<kOut>(c, r * ldc + col, 0.f);
+  }
+}
+
+int out_kind_of(int dt) {
+  switch (dt) {
+    case TLB200_FLOAT16: return kOutF16;
+    case TLB200_BFLOAT16: return kOutBF16;
+    case TLB200_FLOAT8_E4M3: return kOutE4M3;
+    case TLB200_FLOAT8_E5M2: return kOutE5M2;
+    default: return kOutF32;
+  }
+}
+
+int current_device_ready(int* dev_out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail("tlb200: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices) return fail("tlb200: device ordinal %d out of range", dev);
+  if (!g_dev_ready[dev]) {
+    int rc = tlb200_init(dev);
+    if (rc) return rc;
+  }
+  *dev_out = dev;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* tlb200_last_error(void) { return g_err; }
+int tlb200_abi_version(void) { return TLB200_ABI_VERSION; }
+int64_t tlb200_launch_count(void) { return g_launches.load(); }
+
+uint32_t tlb200_instr_desc(int atom_m, int atom_n, int atom_k, int ab_dtype, int c_dtype,
+                           int a_is_k_major, int b_is_k_major, int scale_in_a, int scale_in_b) {
+  uint32_t d = instr_desc_impl(atom_m, atom_n, atom_k, ab_dtype, c_dtype, a_is_k_major != 0,
+                               b_is_k_major != 0, scale_in_a, scale_in_b);
+  if (d == 0) fail("tlb200_instr_desc: unsupported arguments");
+  return d;
+}
+
+int tlb200_tcgen5_meta(int M, int N, int K, int ab, int c, int32_t* out5) {
+  // Decision table of src/op/tcgen5_meta.h:21-92, restated.
+  auto ok = [&](int am, int an, int ak, int ws, int two) {
+    if (out5) { out5[0] = am; out5[1] = an; out5[2] = ak; out5[3] = ws; out5[4] = two; }
+    return 1;
+  };
+  const int ws_ns[3] = {256, 128, 64};
+  const bool half_in = ab == TLB200_FLOAT16 || ab == TLB200_BFLOAT16;
+  const bool f8_in = ab == TLB200_FLOAT8_E4M3 || ab == TLB200_FLOAT8_E5M2;
+  if (half_in && c == TLB200_FLOAT32) {
+    if (K % 16) return 0;
+    if (M % 128 == 0) {
+      for (int an = 256; an >= 16; an -= 16)
+        if (N % an == 0) return ok(128, an, 16, 0, 0);
+      return 0;
+    }
+    const int am = (M % 64 == 0) ? 64 : (M % 32 == 0) ? 32 : 0;
+    if (!am) return 0;
+    for (int an : ws_ns)
+      if (N % an == 0) return ok(am, an, 16, 1, 0);
+    return 0;
+  }
+  if (f8_in && (c == TLB200_FLOAT32 || c == TLB200_FLOAT16)) {
+    if (K % 32) return 0;
+    if (M % 128 == 0) {
+      for (int an : ws_ns)
+        if (N % an == 0) return ok(128, an, 32, 1, 0);
+      for (int an = 256; an >= 16; an -= 16)
+        if (N % an == 0) return ok(128, an, 32, 0, 1);
+      for (int an = 256; an >= 8; an -= 8)
+        if (N % an == 0) return ok(128, an, 32, 0, 0);
+      return 0;
+    }
+    if (M % 64 == 0) {
+      for (int an : ws_ns)
+        if (N % an == 0) return ok(64, an, 32, 1, 0);
+      for (int an = 256; an >= 8; an -= 8)
+        if (N % an == 0) return ok(64, an, 32, 0, 0);
+      return 0;
+    }
+    if (M % 32 == 0) {
+      for (int an : ws_ns)
+        if (N % an == 0) return ok(32, an, 32, 1, 0);
+      return 0;
+    }
+  }
+  return 0;
+}
+
+uint64_t tlb200_smem_desc(uint32_t smem_addr, int lbo16, int sbo16, int base_offset,
+                          int leading_is_absolute, int swizzle_mode) {
+  return smem_desc_impl(smem_addr, lbo16, sbo16, base_offset, leading_is_absolute, swizzle_mode);
+}
+
+int tlb200_gemm_plan_query(const tlb200_gemm_desc* desc, int sm_count, tlb200_gemm_plan* out) {
+  Resolved r;
+  int rc = resolve(desc, sm_count, nullptr, &r);
+  if (rc) return rc;
+  if (out) *out = r.plan;
+  return 0;
+}
+
+int tlb200_init(int device) {
+  std::lock_guard<std::mutex> lk(g_init_mu);
+  g_err[0] = 0;
+  if (device < 0 || device >= kMaxDevices) return fail("tlb200_init: device ordinal %d out of range", device);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail("tlb200_init: no CUDA device (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device >= ndev) return fail("tlb200_init: device %d >= device count %d", device, ndev);
+  int prev = -1;
+  cudaGetDevice(&prev);
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("tlb200_init: cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  int rc = 0;
+  do {
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) { rc = fail("tlb200_init: %s", cudaGetErrorString(e)); break; }
+    if (prop.major != 10) {
+      rc = fail("tlb200_init: device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+      break;
+    }
+    g_sm_count[device] = prop.multiProcessorCount;
+    if (!g_encode) {
+      void* fn = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+      if (e != cudaSuccess || !fn || q != cudaDriverEntryPointSuccess) {
+        rc = fail("tlb200_init: cannot bind cuTensorMapEncodeTiled (%s)", cudaGetErrorString(e));
+        break;
+      }
+      g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    }
+    // Same step as the generated init(): raise the dynamic shared memory limit (wrapper.py:15-21).
+    if ((e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) {
+      rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
+      break;
+    }
+    g_dev_ready[device] = true;
+  } while (0);
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);
+  return rc;
+}
+
+int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
+  g_err[0] = 0;
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
+  Resolved r;
+  if (int rc = resolve(d, g_sm_count[dev], c, &r)) return rc;
+  if (d->m == 0 || d->n == 0) return 0;
+  if (!a || !b || !c) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
+  if ((reinterpret_cast<uintptr_t>(a) % 16) || (reinterpret_cast<uintptr_t>(b) % 16))
+    return fail("tlb200_gemm: operand base addresses must be 16-byte aligned for TMA");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  const int out_kind = out_kind_of(d->c_dtype);
+  cudaError_t e;
+  if (d->k == 0) {  // empty contraction: C = 0 (T.clear semantics)
+    const int blocks = 148 * 4;
+    switch (out_kind) {
+      case kOutF16: fill_zero_kernel<kOutF16><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+      case kOutBF16: fill_zero_kernel<kOutBF16><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+      case kOutF32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+      case kOutE4M3: fill_zero_kernel<kOutE4M3><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+      default: fill_zero_kernel<kOutE5M2><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+    }
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail("tlb200_gemm: fill launch: %s", cudaGetErrorString(e));
+    g_launches++;
+    return 0;
+  }
+
+  const tlb200_gemm_plan& pl = r.plan;
+  GemmKernelParams kp;
+  memset(&kp, 0, sizeof(kp));
+  const int bk = r.span;  // K elements per stage
+  // A
+  if (!r.a_mn) {
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, d->lda, bk, kBlockM, "A[M,K]")) return rc;
+    kp.a_boxes = 1; kp.a_box_bytes = kABytesPerStage;
+  } else {
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->k, d->m, d->lda, r.span, bk, "A[K,M]")) return rc;
+    kp.a_boxes = kBlockM / r.span; kp.a_box_bytes = bk * kStageRowBytes;
+  }
+  // B
+  if (!r.b_mn) {
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->n, d->k, d->ldb, bk, r.b_rows_per_cta, "B[N,K]")) return rc;
+    kp.b_boxes = 1; kp.b_box_bytes = r.b_rows_per_cta * kStageRowBytes;
+  } else {
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->k, d->n, d->ldb, r.span, bk, "B[K,N]")) return rc;
+    kp.b_boxes = r.b_rows_per_cta / r.span; kp.b_box_bytes = bk * kStageRowBytes;
+  }
+  if (r.epi_tma) {
+    if (int rc = encode_2d(&kp.tm_c, d->c_dtype, c, d->m, d->n, d->ldc, 128 / r.ob, 32, "C[M,N]")) return rc;
+  }
+  kp.c = c;
+  kp.ldc = d->ldc;
+  kp.m = d->m; kp.n = d->n;
+  kp.num_k_blocks = r.num_k_blocks;
+  kp.tiles_m = pl.tiles_m; kp.tiles_n = pl.tiles_n;
+  kp.raster = pl.raster;
+  kp.block_n = pl.block_n;
+  kp.stages = pl.stages;
+  kp.k_elems_per_block = bk;
+  kp.a_mn_major = r.a_mn; kp.b_mn_major = r.b_mn;
+  kp.b_rows_per_cta = r.b_rows_per_cta;
+  kp.idesc = pl.instr_desc;
+  // Shared-memory matrix descriptors, 128B swizzle (layout_type 2), SBO = 8 rows x 128 B.
+  // K-major: LBO is ignored by the hardware for swizzled layouts (reference sets 16 B,
+  // tcgen05_macro_generator.py:186-190); K advances 32 B inside the swizzle atom (:312-327).
+  // MN-major: LBO = distance between 128 B spans along M/N = one TMA box; K advances by
+  // UMMA_K rows of 128 B.
+  const uint32_t hi = static_cast<uint32_t>(smem_desc_impl(0, 0, 1024 >> 4, 0, 0, 2) >> 32);
+  kp.desc_hi_a = hi; kp.desc_hi_b = hi;
+  const uint32_t umma_k = 32 / r.es;
+  kp.desc_lbo_a = (r.a_mn ? static_cast<uint32_t>(kp.a_box_bytes >> 4) : 1u) << 16;
+  kp.desc_lbo_b = (r.b_mn ? static_cast<uint32_t>(kp.b_box_bytes >> 4) : 1u) << 16;
+  kp.kadv_a = r.a_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
+  kp.kadv_b = r.b_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
+  kp.out_kind = out_kind;
+  kp.is_f8 = r.es == 1;
+  kp.epi_tma = r.epi_tma;
+  kp.relu = (d->epilogue & TLB200_EPI_RELU) ? 1 : 0;
+  kp.alpha = d->alpha;
+
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(pl.grid, 1, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = pl.smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = pl.cta_group;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (pl.cta_group == 2) e = cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2>, kp);
+  else e = cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1>, kp);
+  if (e != cudaSuccess)
+    return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
+                pl.cta_group, pl.smem_bytes);
+  g_launches++;
+  return 0;
+}
+
+static long long extent_bytes(long long rows, long long cols, long long ld, int eb) {
+  if (rows <= 0 || cols <= 0) return 0;
+  return ((rows - 1) * ld + cols) * eb;
+}
+static long long round256(long long x) { return (x + 255) & ~255ll; }
+
+int64_t tlb200_gemm_host_workspace_bytes(const tlb200_gemm_desc* d) {
+  if (!d) return -1;
+  const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
+  if (!es || !ob) return -1;
+  const long long a = extent_bytes(d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, d->lda, es);
+  const long long b = extent_bytes(d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, d->ldb, es);
+  const long long c = extent_bytes(d->m, d->n, d->ldc, ob);
+  return round256(a) + round256(b) + round256(c);
+}
+
+int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, void* hc, void* ws,
+                     int64_t ws_bytes, void* stream_v) {
+  g_err[0] = 0;
+  const int64_t need = tlb200_gemm_host_workspace_bytes(d);
+  if (need < 0) return fail("tlb200_gemm_host: bad descriptor");
+  if (ws_bytes < need || (!ws && need > 0)) return fail("tlb200_gemm_host: workspace %lld B < required %lld B", (long long)ws_bytes, (long long)need);
+  if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_host: workspace must be 256-byte aligned");
+  const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
+  const long long ab = extent_bytes(d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, d->lda, es);
+  const long long bb = extent_bytes(d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, d->ldb, es);
+  const long long cb = extent_bytes(d->m, d->n, d->ldc, ob);
+  char* da = static_cast<char*>(ws);
+  char* db = da + round256(ab);
+  char* dc = db + round256(bb);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  cudaError_t e;
+  if (ab && (e = cudaMemcpyAsync(da, ha, ab, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return fail("tlb200_gemm_host: H2D A: %s", cudaGetErrorString(e));
+  if (bb && (e = cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return fail("tlb200_gemm_host: H2D B: %s", cudaGetErrorString(e));
+  if (int rc = tlb200_gemm(d, da, db, dc, stream_v)) return rc;
+  if (cb && (e = cudaMemcpyAsync(hc, dc, cb, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail("tlb200_gemm_host: D2H C: %s", cudaGetErrorString(e));
+  if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail("tlb200_gemm_host: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+"""Host-side GEMM call: torch tensors -> C ABI (tlb200_gemm).
+
+Mirrors what the reference's kernel adapters do around the generated ``call()``:
+argument count / device / dtype / shape / stride checks raised as ValueError
+(tilelang/jit/adapter/cython/cython_wrapper.pyx:78-156,259-265), output allocation with
+``torch.empty`` on the inputs' device (:192-228), torch's *current* raw stream passed through
+(:178-185), non-zero return code -> RuntimeError(get_last_error()) (:279-281).
+PyTorch is plumbing only (memory + streams); the arithmetic is the CUDA kernel.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import _abi
+
+_TORCH2TLB = {
+    torch.float16: _abi.FLOAT16,
+    torch.bfloat16: _abi.BFLOAT16,
+    torch.float8_e4m3fn: _abi.FLOAT8_E4M3,
+    torch.float8_e5m2: _abi.FLOAT8_E5M2,
+    torch.float32: _abi.FLOAT32,
+}
+_AB_DTYPES = (torch.float16, torch.bfloat16, torch.float8_e4m3fn, torch.float8_e5m2)
+
+_inited_devices = set()
+
+
+def _ensure_init(device_index: int):
+    if device_index not in _inited_devices:
+        lib = _abi.load()
+        _abi.check(lib.tlb200_init(device_index), f"tlb200_init({device_index})")
+        _inited_devices.add(device_index)
+
+
+def _row_pitch(t: torch.Tensor, name: str) -> int:
+    if t.dim() != 2:
+        raise ValueError(f"{name}: expected a 2-D tensor, got {t.dim()}-D")
+    if t.shape[1] > 1 and t.stride(1) != 1:
+        raise ValueError(f"{name}: innermost dimension must be contiguous (stride {t.stride(1)})")
+    if t.shape[0] > 1:
+        return t.stride(0)
+    return max(t.shape[1], 1)
+
+
+def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha=1.0, relu=False,
+              cta_group=0, block_n=0, stages=0, raster=0, epilogue=0) -> _abi.GemmDesc:
+    d = _abi.GemmDesc()
+    d.abi_version = _abi.ABI_VERSION
+    d.m, d.n, d.k = int(m), int(n), int(k)
+    d.ab_dtype, d.c_dtype = int(ab_dtype), int(c_dtype)
+    d.trans_a, d.trans_b = int(bool(trans_a)), int(bool(trans_b))
+    d.lda, d.ldb, d.ldc = int(lda), int(ldb), int(ldc)
+    d.alpha = float(alpha)
+    d.epilogue = _abi.EPI_RELU if relu else _abi.EPI_NONE
+    d.cfg_cta_group, d.cfg_block_n, d.cfg_stages = int(cta_group), int(block_n), int(stages)
+    d.cfg_raster, d.cfg_epilogue = int(raster), int(epilogue)
+    return d
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, trans_a: bool = False,
+         trans_b: bool = True, out_dtype: Optional[torch.dtype] = None, alpha: float = 1.0,
+         relu: bool = False, **cfg) -> torch.Tensor:
+    """C = alpha * op(A) @ op(B) with fp32 accumulation on the tcgen05 path.
+
+    ``trans_a`` / ``trans_b`` have T.gemm's meaning (tilelang/language/gemm.py:105-116):
+    A is [K, M] if trans_a else [M, K]; B is [N, K] if trans_b else [K, N].
+    """
+    if not (isinstance(a, torch.Tensor) and isinstance(b, torch.Tensor)):
+        raise ValueError("gemm: A and B must be torch tensors")
+    if not a.is_cuda or not b.is_cuda:
+        raise ValueError("gemm: A and B must live on a CUDA device (there is no CPU fallback)")
+    if a.device != b.device:
+        raise ValueError(f"gemm: A on {a.device} but B on {b.device}")
+    if a.dtype != b.dtype:
+        raise ValueError(f"gemm: A is {a.dtype} but B is {b.dtype}")
+    if a.dtype not in _AB_DTYPES:
+        raise ValueError(f"gemm: unsupported operand dtype {a.dtype}")
+    lda, ldb = _row_pitch(a, "A"), _row_pitch(b, "B")
+    m, ka = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    n, kb = (b.shape[0], b.shape[1]) if trans_b else (b.shape[1], b.shape[0])
+    if ka != kb:  # language/gemm.py:78-81
+        raise ValueError(f"gemm: T.gemm K shape check failed: K_A = {ka}, K_B = {kb}")
+    if c is None:
+        c = torch.empty((m, n), dtype=out_dtype or a.dtype, device=a.device)
+    else:
+        if c.device != a.device:
+            raise ValueError(f"gemm: C on {c.device} but A on {a.device}")
+        if tuple(c.shape) != (m, n):
+            raise ValueError(f"gemm: C has shape {tuple(c.shape)}, expected {(m, n)}")
+        if out_dtype is not None and c.dtype != out_dtype:
+            raise ValueError(f"gemm: C is {c.dtype}, expected {out_dtype}")
+    if c.dtype not in _TORCH2TLB:
+        raise ValueError(f"gemm: unsupported output dtype {c.dtype}")
+    ldc = _row_pitch(c, "C")
+    dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, lda, ldb,
+                     ldc, alpha, relu, **cfg)
+    lib = _abi.load()
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        rc = lib.tlb200_gemm(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), stream)
+    _abi.check(rc, "tlb200_gemm")
+    return c
+
+
+def plan(m, n, k, ab_dtype=torch.bfloat16, c_dtype=torch.bfloat16, trans_a=False, trans_b=True,
+         sm_count=148, **cfg) -> dict:
+    """Resolve the tile plan for a problem without touching a GPU."""
+    lda = m if trans_a else k
+    ldb = k if trans_b else n
+    desc = make_desc(m, n, k, _TORCH2TLB[ab_dtype], _TORCH2TLB[c_dtype], trans_a, trans_b, lda, ldb, n,
+                     **cfg)
+    out = _abi.GemmPlan()
+    lib = _abi.load()
+    _abi.check(lib.tlb200_gemm_plan_query(ctypes.byref(desc), sm_count, ctypes.byref(out)),
+               "tlb200_gemm_plan_query")
+    return out.as_dict()
