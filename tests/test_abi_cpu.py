@@ -1,0 +1,139 @@
+"""CPU tests of the C-ABI boundary: the library loads, exports every symbol include/tlb200.h
+declares, and its pure-arithmetic entry points agree bit-for-bit with the oracle.  No compute
+call is made here (there is no GPU); compute parity lives in the -m gpu tests.
+"""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from oracle import descriptors as D
+from tilelang_mesh_b200 import _abi
+from tilelang_mesh_b200 import gemm as G
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NAMES = {_abi.FLOAT16: "float16", _abi.BFLOAT16: "bfloat16", _abi.FLOAT8_E4M3: "float8_e4m3",
+         _abi.FLOAT8_E5M2: "float8_e5m2", _abi.FLOAT32: "float32"}
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "tlb200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(tlb200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_and_binding_agree(built_lib):
+    declared = _declared_symbols()
+    assert declared, "no declarations parsed from include/tlb200.h"
+    assert sorted(_abi.SYMBOLS) == declared
+    for name in declared:
+        assert hasattr(built_lib, name), f"libtlb200.so does not export {name}"
+    assert built_lib.tlb200_abi_version() == _abi.ABI_VERSION
+
+
+def test_struct_layout_matches_header(built_lib):
+    # 8 int32 + 3 int64 + float + uint32 + 5 int32 + 3 reserved, natural alignment
+    assert ctypes.sizeof(_abi.GemmDesc) == 96
+    assert _abi.GemmDesc.lda.offset == 32 and _abi.GemmDesc.alpha.offset == 56
+    assert ctypes.sizeof(_abi.GemmPlan) == 64
+
+
+def test_instr_desc_bit_exact_vs_oracle(built_lib):
+    for ab in (_abi.FLOAT16, _abi.BFLOAT16, _abi.FLOAT8_E4M3, _abi.FLOAT8_E5M2):
+        ak = 16 if ab in (_abi.FLOAT16, _abi.BFLOAT16) else 32
+        for am in (64, 128, 256):
+            for an in range(16, 257, 16):
+                for akm in (0, 1):
+                    for bkm in (0, 1):
+                        got = built_lib.tlb200_instr_desc(am, an, ak, ab, _abi.FLOAT32, akm, bkm, 1, 1)
+                        want = D.tcgen5_instr_desc(am, an, ak, NAMES[ab], "float32", bool(akm), bool(bkm))
+                        assert got == want
+    assert built_lib.tlb200_instr_desc(128, 256, 16, _abi.BFLOAT16, _abi.FLOAT32, 1, 1, 1, 1) == 138413200
+    assert built_lib.tlb200_instr_desc(128, 256, 16, _abi.BFLOAT16, _abi.FLOAT32, 1, 1, -1, 1) == 138413200 | (1 << 13)
+    assert built_lib.tlb200_instr_desc(100, 256, 16, _abi.BFLOAT16, _abi.FLOAT32, 1, 1, 1, 1) == 0
+    assert "unsupported" in _abi.last_error()
+
+
+def test_tcgen5_meta_bit_exact_vs_oracle(built_lib):
+    out = (ctypes.c_int32 * 5)()
+    for ab in (_abi.FLOAT16, _abi.BFLOAT16, _abi.FLOAT8_E4M3):
+        for c in (_abi.FLOAT32, _abi.FLOAT16):
+            for M in (32, 64, 96, 128, 256, 100):
+                for N in (8, 24, 48, 64, 80, 128, 192, 256, 512):
+                    for K in (16, 32, 48, 64, 128):
+                        ok = built_lib.tlb200_tcgen5_meta(M, N, K, ab, c, out)
+                        want = D.tcgen5_mma_meta(M, N, K, NAMES[ab], NAMES[c])
+                        assert bool(ok) == (want is not None), (M, N, K, ab, c)
+                        if want:
+                            assert tuple(out) == tuple(int(x) for x in want)
+
+
+def test_smem_desc_bit_exact_vs_oracle(built_lib):
+    for addr in (0, 0x400, 0x12340, 0x3FFF0):
+        for lbo, sbo, swz in ((1, 64, 2), (512, 64, 2), (1, 32, 4), (0, 0, 0)):
+            assert built_lib.tlb200_smem_desc(addr, lbo, sbo, 0, 0, swz) == D.tcgen05_smem_desc(addr, lbo, sbo, 0, False, swz)
+
+
+def test_plan_headline_configs(built_lib):
+    p = G.plan(8192, 8192, 8192)  # C2
+    assert (p["cta_group"], p["block_m"], p["block_n"], p["block_k"]) == (2, 256, 256, 64)
+    assert p["grid"] == 148 and p["tmem_cols"] == 512 and p["smem_bytes"] <= 232448
+    assert p["tiles_m"] * p["tiles_n"] == 1024
+    assert p["instr_desc"] == D.tcgen5_instr_desc(256, 256, 16, "bfloat16", "float32")
+    p8 = G.plan(8192, 8192, 8192, torch.float8_e4m3fn, torch.bfloat16)  # C3
+    assert p8["block_k"] == 128 and p8["instr_desc"] == D.tcgen5_instr_desc(256, 256, 32, "float8_e4m3", "float32")
+    pq = G.plan(1024, 1024, 1024, torch.float16, torch.float16, False, False, cta_group=1)  # C1 shape, NN
+    assert pq["instr_desc"] == D.tcgen5_instr_desc(128, 256, 16, "float16", "float32", True, False)
+    for m, n, k in ((16384, 14336, 4096), (16384, 4096, 14336)):  # C4
+        p4 = G.plan(m, n, k)
+        assert p4["tiles_m"] * p4["tiles_n"] == (m // 256) * (n // 256)
+
+
+def test_plan_small_and_ragged(built_lib):
+    p = G.plan(100, 40, 72, cta_group=0)
+    assert p["cta_group"] == 1 and p["block_n"] == 64 and p["tiles_m"] == 1 and p["tiles_n"] == 1
+    assert p["epilogue"] == 2  # ldc = 40 bf16 = 80 B: TMA-store capable
+    p = G.plan(300, 200, 136)
+    assert p["cta_group"] == 2 and p["tiles_m"] == 2 and p["tiles_n"] == 1
+
+
+def test_plan_rejects_bad_arguments(built_lib):
+    with pytest.raises(RuntimeError, match="16 bytes"):
+        G.plan(128, 128, 100)  # K*2 bytes not a multiple of 16 -> TMA cannot address it
+    with pytest.raises(RuntimeError, match="cfg_block_n"):
+        G.plan(128, 128, 128, block_n=24, cta_group=2)
+    with pytest.raises(RuntimeError, match="cfg_cta_group"):
+        G.plan(128, 128, 128, cta_group=3)
+    with pytest.raises(RuntimeError, match="cfg_stages"):
+        G.plan(128, 128, 128, stages=40)
+    d = G.make_desc(8, 8, 8, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 8, 8, 8)
+    d.abi_version = 99
+    assert built_lib.tlb200_gemm_plan_query(ctypes.byref(d), 148, None) != 0
+    assert "abi_version" in _abi.last_error()
+
+
+def test_no_gpu_fails_loudly(built_lib):
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    assert built_lib.tlb200_init(0) != 0
+    assert "no CPU fallback" in _abi.last_error()
+    a = torch.zeros(8, 8, dtype=torch.bfloat16)
+    with pytest.raises(ValueError, match="CUDA device"):
+        G.gemm(a, a)
+
+
+def test_host_workspace_bytes(built_lib):
+    d = G.make_desc(8192, 8192, 8192, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 8192, 8192, 8192)
+    assert built_lib.tlb200_gemm_host_workspace_bytes(ctypes.byref(d)) == 3 * 128 * 1024 * 1024
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "tilelang_mesh_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
+                assert "oracle/" not in txt or f == "README.md", f

@@ -231,12 +231,18 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
 }
 
 // ---------------------------------------------------------------- the kernel
-template <int kCta>
+// Control flow of every role is kept WARP-UNIFORM (role chosen from a shuffled warp index, loop
+// bounds from kernel parameters) and only the issuing instructions are predicated on one elected
+// lane.  tcgen05.mma / TMA take their operands from uniform registers; inside a lane-divergent
+// region the compiler cannot prove uniformity and wraps every such instruction in an
+// ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" loop, which made the first version of this kernel
+// issue-bound (~870 cycles per K-block instead of 512; profiles/r1_notes.md).
+template <int kCta, bool kF8>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = static_cast<int>(lane_id());
   const uint32_t cta_rank = (kCta == 2) ? cluster_ctarank() : 0u;
   const bool leader = cta_rank == 0;
 
@@ -260,24 +266,28 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
                              : (2u * p.block_n <= 256u) ? 256u
                                                         : 512u;
 
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tm_a);
-    tma_prefetch_desc(&p.tm_b);
-    if (p.epi_tma) tma_prefetch_desc(&p.tm_c);
-  }
-  if (warp == 1 && lane == 0) {
-    for (int s = 0; s < stages; ++s) {
-      mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
-      mbar_init(bar_empty + 8 * s, 1);  // one tcgen05.commit
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tm_a);
+      tma_prefetch_desc(&p.tm_b);
+      if (p.epi_tma) tma_prefetch_desc(&p.tm_c);
     }
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(bar_tfull + 8 * a, 1);                    // one tcgen05.commit
-      mbar_init(bar_tempty + 8 * a, kEpiWarps * kCta);    // one arrive per epilogue warp (per CTA)
+  } else if (warp == 1) {
+    if (elect_one()) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
+        mbar_init(bar_empty + 8 * s, 1);  // one tcgen05.commit
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(bar_tfull + 8 * a, 1);                    // one tcgen05.commit
+        mbar_init(bar_tempty + 8 * a, kEpiWarps * kCta);    // one arrive per epilogue warp (per CTA)
+      }
+      fence_mbar_init();
     }
-    fence_mbar_init();
+  } else if (warp == 2) {
+    tmem_alloc<kCta>(smem_tptr, tmem_cols);
   }
   __syncwarp();
-  if (warp == 2) tmem_alloc<kCta>(smem_tptr, tmem_cols);
   tc_fence_before();
   if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
@@ -300,44 +310,56 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   };
 
   if (warp == 0) {
-    // ===================================================== TMA producer (one lane)
-    if (lane == 0) {
-      const uint64_t pol = policy_evict_normal();
-      int s = 0;
-      uint32_t ph = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-        int tm, tn;
-        tile_coord(t, tm, tn);
-        const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
-        const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
+    // ===================================================== TMA producer (one elected lane issues)
+    const bool elected = elect_one();
+    const uint64_t pol = policy_evict_normal();
+    const int kspan = p.k_elems_per_block;
+    const int a_rows_per_box = p.a_box_bytes / kStageRowBytes;
+    const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
+    int s = 0;
+    uint32_t ph = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      int tm, tn;
+      tile_coord(t, tm, tn);
+      const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
+      const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
+        if (elected) {
           const uint32_t full = bar_full + 8 * s;
           if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
-          const int k0 = kb * p.k_elems_per_block;
+          const int k0 = kb * kspan;
           const uint32_t dst_a = smem_a + s * kABytesPerStage;
           const uint32_t dst_b = smem_b + s * b_stage_bytes;
           // K-major operand: box = [rows x 128 B of K], coords {k, row}.
           // MN-major operand: boxes = [K-block rows x 128 B of M/N], coords {row + j*span, k}.
           for (int j = 0; j < p.a_boxes; ++j) {
-            const int c0 = p.a_mn_major ? row_a + j * p.k_elems_per_block : k0;
-            const int c1 = p.a_mn_major ? k0 : row_a + j * (p.a_box_bytes / kStageRowBytes);
+            const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
+            const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
             if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
             else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
           }
           for (int j = 0; j < p.b_boxes; ++j) {
-            const int c0 = p.b_mn_major ? row_b + j * p.k_elems_per_block : k0;
-            const int c1 = p.b_mn_major ? k0 : row_b + j * (p.b_box_bytes / kStageRowBytes);
+            const int c0 = p.b_mn_major ? row_b + j * kspan : k0;
+            const int c1 = p.b_mn_major ? k0 : row_b + j * b_rows_per_box;
             if constexpr (kCta == 2) tma_load_2d_pair(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
             else tma_load_2d(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
           }
-          if (++s == stages) { s = 0; ph ^= 1u; }
         }
+        __syncwarp();
+        if (++s == stages) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer (one lane, leader CTA)
-    if (lane == 0 && leader) {
+    // ===================================================== MMA issuer (leader CTA; one elected lane)
+    if (leader) {
+      const bool elected = elect_one();
+      const uint32_t idesc = p.idesc;
+      const uint64_t hi_a = static_cast<uint64_t>(p.desc_hi_a) << 32 | p.desc_lbo_a;
+      const uint64_t hi_b = static_cast<uint64_t>(p.desc_hi_b) << 32 | p.desc_lbo_b;
+      const uint32_t kadv_a = p.kadv_a, kadv_b = p.kadv_b;
+      const uint32_t a_lo0 = (smem_a & 0x3FFFFu) >> 4, b_lo0 = (smem_b & 0x3FFFFu) >> 4;
+      const uint32_t a_step = kABytesPerStage >> 4, b_step = b_stage_bytes >> 4;
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
@@ -350,22 +372,22 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
           tc_fence_after();
-          const uint32_t a_lo = ((smem_a + s * kABytesPerStage) & 0x3FFFFu) >> 4;
-          const uint32_t b_lo = ((smem_b + s * b_stage_bytes) & 0x3FFFFu) >> 4;
+          if (elected) {
+            const uint32_t a_lo = a_lo0 + s * a_step;
+            const uint32_t b_lo = b_lo0 + s * b_step;
 #pragma unroll
-          for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
-            const uint64_t da = (static_cast<uint64_t>(p.desc_hi_a) << 32) |
-                                (p.desc_lbo_a | ((a_lo + k * p.kadv_a) & 0x3FFFu));
-            const uint64_t db = (static_cast<uint64_t>(p.desc_hi_b) << 32) |
-                                (p.desc_lbo_b | ((b_lo + k * p.kadv_b) & 0x3FFFu));
-            const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
-            if (p.is_f8) umma_ss<kCta, true>(d_tmem, da, db, p.idesc, acc);
-            else umma_ss<kCta, false>(d_tmem, da, db, p.idesc, acc);
+            for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
+              const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
+              const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
+              umma_ss<kCta, kF8>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
           }
-          umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1u; }
         }
-        umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
+        if (elected) umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
+        __syncwarp();
       }
     }
   } else if (warp >= kEpiWarp0) {
@@ -406,7 +428,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   }
 
   // ---- teardown: nobody may still be using TMEM / peer smem when it is released
-  __syncwarp();  // re-converge the single-lane roles before the .aligned barriers
+  __syncwarp();  // re-converge the single-lane regions before the .aligned barriers
   tc_fence_before();
   if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();

@@ -359,8 +359,10 @@ int tlb200_init(int device) {
       g_encode = reinterpret_cast<EncodeTiledFn>(fn);
     }
     // Same step as the generated init(): raise the dynamic shared memory limit (wrapper.py:15-21).
-    if ((e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) {
+    if ((e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
     }
@@ -463,8 +465,11 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (pl.cta_group == 2) e = cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2>, kp);
-  else e = cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1>, kp);
+  const bool f8 = r.es == 1;
+  if (pl.cta_group == 2) e = f8 ? cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2, true>, kp)
+                                : cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2, false>, kp);
+  else e = f8 ? cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1, true>, kp)
+              : cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1, false>, kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);
