@@ -74,7 +74,7 @@ typedef struct tlb200_gemm_desc {
   float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
   uint32_t epilogue;  /* TLB200_EPI_* */
   int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles */
-  int32_t cfg_block_n;   /* 0 auto, else multiple of 16 (32 for cta_group 2) in [16,256] */
+  int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
   int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */

@@ -103,7 +103,10 @@ def test_plan_rejects_bad_arguments(built_lib):
     with pytest.raises(RuntimeError, match="16 bytes"):
         G.plan(128, 128, 100)  # K*2 bytes not a multiple of 16 -> TMA cannot address it
     with pytest.raises(RuntimeError, match="cfg_block_n"):
-        G.plan(128, 128, 128, block_n=24, cta_group=2)
+        G.plan(128, 128, 128, block_n=48, cta_group=2)
+    with pytest.raises(RuntimeError, match="multiple of 128"):
+        G.plan(128, 128, 128, torch.float8_e4m3fn, torch.float8_e4m3fn, block_n=64, epilogue=2)
+    assert G.plan(128, 64, 128, torch.float8_e4m3fn, torch.float8_e4m3fn)["epilogue"] == 1
     with pytest.raises(RuntimeError, match="cfg_cta_group"):
         G.plan(128, 128, 128, cta_group=3)
     with pytest.raises(RuntimeError, match="cfg_stages"):

@@ -132,7 +132,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (d->ldc < d->n) return fail("tlb200: ldc=%lld < n=%d", (long long)d->ldc, d->n);
   // TMA needs 16-byte row pitches (same constraint as the reference's bulk copy,
   // src/op/copy.cc:1489-1499: strides in bytes, % 16, < 2^40).
-  if ((d->lda * r->es) % 16 || (d->ldb * r->es) % 16)
+  if (d->k > 0 && d->m > 0 && d->n > 0 && ((d->lda * r->es) % 16 || (d->ldb * r->es) % 16))
     return fail("tlb200: operand row pitch must be a multiple of 16 bytes (lda=%lld ldb=%lld, %d-byte elements)",
                 (long long)d->lda, (long long)d->ldb, r->es);
 
@@ -143,14 +143,17 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (cg != 1 && cg != 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", cg);
   if (sm_count > 0 && sm_count < 2) cg = 1;
   int bn = d->cfg_block_n;
-  const int n_min = r->b_mn ? r->span * cg : 16 * cg;  // MN-major B is staged in whole 128 B spans
+  // The epilogue drains TMEM 32 columns at a time, so tiles are whole multiples of 32 columns;
+  // an N-major B is staged in whole 128 B spans per CTA.
+  const int n_step = r->b_mn ? r->span * cg : 32;
+  const int n_min = n_step;
   if (bn == 0) {
     bn = 256;
     while (bn / 2 >= d->n && bn / 2 >= n_min) bn /= 2;
   }
-  if (bn < n_min || bn > 256 || bn % (16 * cg) || (r->b_mn && (bn / cg) % r->span))
-    return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need multiple of %d in [%d,256])", bn, cg,
-                r->b_mn ? ", N-major B" : "", r->b_mn ? r->span * cg : 16 * cg, n_min);
+  if (bn < n_min || bn > 256 || bn % n_step)
+    return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need a multiple of %d in [%d,256])", bn, cg,
+                r->b_mn ? ", N-major B" : "", n_step, n_min);
   r->b_rows_per_cta = bn / cg;
   const int per_stage = kABytesPerStage + r->b_rows_per_cta * kStageRowBytes;
   int stages = d->cfg_stages;
@@ -177,8 +180,12 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.raster = d->cfg_raster > 0 ? d->cfg_raster : (16 / cg);
   int epi = d->cfg_epilogue;
   const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0);
-  if (epi == 0) epi = tma_ok ? 2 : 1;
+  // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
+  const bool slab_ok = bn % (128 / r->ob) == 0;
+  if (epi == 0) epi = (tma_ok && slab_ok) ? 2 : 1;
   if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C and row pitch");
+  if (epi == 2 && !slab_ok)
+    return fail("tlb200: TMA-store epilogue needs block_n (%d) to be a multiple of %d for %d-byte outputs", bn, 128 / r->ob, r->ob);
   if (epi != 1 && epi != 2) return fail("tlb200: cfg_epilogue must be 0, 1 or 2");
   p.epilogue = epi;
   r->epi_tma = epi == 2;
