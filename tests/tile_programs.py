@@ -1,0 +1,76 @@
+"""Tile programs written against the reference's public API (T.prim_func / T.Kernel / T.copy /
+T.gemm / T.Pipelined), used by the facade tests.  They are this repo's own programs: the four
+program shapes the reference ships for this path — register-accumulator NT (benchmark/matmul),
+NN + relu (examples/quickstart.py), tensor-memory accumulator with user mbarrier
+(examples/gemm_sm100), fp8 (benchmark/matmul_fp8) — re-expressed compactly."""
+import tilelang
+import tilelang.language as T
+
+
+def nt_fragment(M, N, K, bM=128, bN=128, bK=32, dtype="float16", out_dtype=None, stages=3, threads=128, raster=True):
+    out_dtype = out_dtype or dtype
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), dtype), B: T.Tensor((N, K), dtype), C: T.Tensor((M, N), out_dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=threads) as (bx, by):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bN, bK), dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            c_s = T.alloc_shared((bM, bN), out_dtype)
+            T.use_swizzle(panel_size=10, enable=raster)
+            T.annotate_layout({c_s: tilelang.layout.make_swizzled_layout(c_s)})
+            T.clear(acc)
+            for k in T.Pipelined(T.ceildiv(K, bK), num_stages=stages):
+                T.copy(A[by * bM, k * bK], a_s)
+                T.copy(B[bx * bN, k * bK], b_s)
+                T.gemm(a_s, b_s, acc, transpose_B=True, policy=T.GemmWarpPolicy.Square)
+            T.copy(acc, c_s)
+            T.copy(c_s, C[by * bM, bx * bN])
+
+    return prog
+
+
+def nn_relu(M, N, K, bM=128, bN=128, bK=32, dtype="float16"):
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), dtype), B: T.Tensor((K, N), dtype), C: T.Tensor((M, N), dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=128) as (bx, by):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bK, bN), dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            T.clear(acc)
+            for ko in T.Pipelined(T.ceildiv(K, bK), num_stages=3):
+                T.copy(A[by * bM, ko * bK], a_s)
+                T.copy(B[ko * bK, bx * bN], b_s)
+                T.gemm(a_s, b_s, acc)
+            for i, j in T.Parallel(bM, bN):
+                acc[i, j] = T.max(acc[i, j], 0)
+            T.copy(acc, C[by * bM, bx * bN])
+
+    return prog
+
+
+def tmem_accumulator(M, N, K, bM=128, bN=256, bK=128, trans_A=False, trans_B=True, in_dtype="bfloat16",
+                     out_dtype="bfloat16", stages=2, threads=256):
+    a_shape, b_shape = ((K, M) if trans_A else (M, K)), ((N, K) if trans_B else (K, N))
+    a_tile, b_tile = ((bK, bM) if trans_A else (bM, bK)), ((bN, bK) if trans_B else (bK, bN))
+
+    @T.prim_func
+    def prog(A: T.Tensor(a_shape, in_dtype), B: T.Tensor(b_shape, in_dtype), C: T.Tensor((M, N), out_dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=threads) as (bx, by):
+            a_s = T.alloc_shared(a_tile, in_dtype)
+            b_s = T.alloc_shared(b_tile, in_dtype)
+            c_t = T.alloc_tmem([bM, bN], "float")
+            bar = T.alloc_barrier(1)
+            c_l = T.alloc_fragment((bM, bN), "float")
+            c_s = T.alloc_shared((bM, bN), out_dtype)
+            for k in T.Pipelined(T.ceildiv(K, bK), num_stages=stages):
+                T.copy(A[(k * bK, by * bM) if trans_A else (by * bM, k * bK)], a_s)
+                T.copy(B[(bx * bN, k * bK) if trans_B else (k * bK, bx * bN)], b_s)
+                T.gemm(a_s, b_s, c_t, trans_A, trans_B, mbar=bar, wg_wait=-1, clear_accum=k == 0)
+                T.mbarrier_wait_parity(bar, k % 2)
+            T.copy(c_t, c_l)
+            T.copy(c_l, c_s)
+            T.copy(c_s, C[by * bM, bx * bN])
+
+    return prog

@@ -1,0 +1,98 @@
+"""A small `@autotune` (tilelang/autotuner/tuner.py:685-783) so that the reference's benchmark
+programs run unchanged.
+
+The reference searches hundreds of tile programs because each config is a different generated
+kernel.  Here every config of a GEMM program maps onto the same hand-written kernel and the tile
+sizes are hints, so the tuner (a) drops configs whose program is not a valid GEMM tile program,
+(b) times the backend's own plan candidates for the problem (cta_group x block_n x raster), once,
+and (c) returns the kernel carrying `.latency`, `.config`, `.ref_latency` like the reference's
+AutotuneResult consumers expect (benchmark/matmul/benchmark_matmul.py:239-246).
+"""
+from __future__ import annotations
+
+import inspect
+import itertools
+import logging
+from typing import Callable, Optional
+
+logger = logging.getLogger("tilelang_mesh_b200")
+
+PLAN_CANDIDATES = [dict(), dict(cta_group=2, block_n=256, raster=8), dict(cta_group=2, block_n=256, raster=4),
+                   dict(cta_group=2, block_n=256, raster=16), dict(cta_group=2, block_n=128), dict(cta_group=1, block_n=256),
+                   dict(cta_group=1, block_n=128)]
+
+
+class AutoTuner:
+
+    def __init__(self, jit_impl, configs, warmup=25, rep=100, timeout=100, supply_type=None, ref_prog=None,
+                 supply_prog=None, rtol=1e-2, atol=1e-2, max_mismatched_ratio=0.01, skip_check=False,
+                 manual_check_prog=None, cache_input_tensors=False):
+        self.jit_impl, self.configs, self.warmup, self.rep = jit_impl, configs, warmup, rep
+        self.ref_prog, self.skip_check, self.rtol, self.atol = ref_prog, skip_check, rtol, atol
+        self.max_mismatched_ratio = max_mismatched_ratio
+        self._cache = {}
+
+    def _first_valid(self, args, kwargs):
+        cfgs = self.configs(args, kwargs) if callable(self.configs) else list(self.configs)
+        sig = self.jit_impl.signature
+        last = None
+        for cfg in cfgs:
+            try:
+                bound = sig.bind(*args, **kwargs, **cfg) if isinstance(cfg, dict) else sig.bind(*args, *cfg, **kwargs)
+                k = self.jit_impl(*bound.args, **bound.kwargs)
+                return k, (cfg if isinstance(cfg, dict) else dict(zip(list(sig.parameters)[len(args):], cfg)))
+            except (NotImplementedError, ValueError, AssertionError, TypeError) as e:  # invalid tile program
+                last = e
+        raise RuntimeError(f"autotune: no config yields a valid GEMM tile program (last error: {last})")
+
+    def run(self, *args, **kwargs):
+        key = (args, tuple(sorted(kwargs.items())))
+        if key in self._cache:
+            return self._cache[key]
+        import torch
+        from ..jit import JITKernel
+        kernel, cfg = self._first_valid(args, kwargs)
+        prof = kernel.get_profiler()
+        best, best_hints = None, {}
+        if torch.cuda.is_available():
+            ins = prof._get_inputs()
+            for hints in PLAN_CANDIDATES:
+                try:
+                    cand = JITKernel(kernel.prim_func, out_idx=kernel.out_idx, tile_hints=hints)
+                    cand.plan()
+                    lat = prof.do_bench(cand, warmup=self.warmup, rep=self.rep, input_tensors=ins)
+                except RuntimeError as e:
+                    logger.debug("autotune: plan %s rejected: %s", hints, e)
+                    continue
+                if best is None or lat < best:
+                    best, best_hints, kernel = lat, hints, cand
+            ref_lat = None
+            if self.ref_prog is not None:
+                ref_lat = prof.do_bench(self.ref_prog, warmup=self.warmup, rep=self.rep, input_tensors=ins)
+                if not self.skip_check:
+                    prof.assert_allclose(self.ref_prog, input_tensors=ins, rtol=self.rtol, atol=self.atol,
+                                         max_mismatched_ratio=self.max_mismatched_ratio)
+            kernel.update_tuner_result(best, dict(cfg, backend_plan=best_hints), ref_lat)
+        self._cache[key] = kernel
+        return kernel
+
+
+def autotune(func: Optional[Callable] = None, *, configs=None, warmup: int = 25, rep: int = 100, timeout: int = 100,
+             supply_type=None, ref_prog=None, supply_prog=None, rtol=1e-2, atol=1e-2, max_mismatched_ratio=0.01,
+             skip_check=False, manual_check_prog=None, cache_input_tensors=False, profile_args=None, compile_args=None,
+             **_):
+    def decorator(jit_impl):
+        from ..jit import JITImpl, jit
+        if not isinstance(jit_impl, JITImpl):
+            jit_impl = jit(jit_impl)
+        tuner = AutoTuner(jit_impl, configs, warmup, rep, timeout, supply_type, ref_prog, supply_prog, rtol, atol,
+                          max_mismatched_ratio, skip_check, manual_check_prog, cache_input_tensors)
+
+        def wrapper(*args, **kwargs):
+            return tuner.run(*args, **kwargs)
+
+        wrapper.__name__ = getattr(jit_impl, "__name__", "autotuned")
+        wrapper.tuner, wrapper.jit_impl = tuner, jit_impl
+        return wrapper
+
+    return decorator(func) if func is not None else decorator

@@ -386,8 +386,8 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   Resolved r;
   if (int rc = resolve(d, g_sm_count[dev], c, &r)) return rc;
   if (d->m == 0 || d->n == 0) return 0;
-  if (!a || !b || !c) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
-  if ((reinterpret_cast<uintptr_t>(a) % 16) || (reinterpret_cast<uintptr_t>(b) % 16))
+  if (!c || (d->k > 0 && (!a || !b))) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
+  if (d->k > 0 && ((reinterpret_cast<uintptr_t>(a) % 16) || (reinterpret_cast<uintptr_t>(b) % 16)))
     return fail("tlb200_gemm: operand base addresses must be 16-byte aligned for TMA");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   const int out_kind = out_kind_of(d->c_dtype);

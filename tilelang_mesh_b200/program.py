@@ -1,0 +1,286 @@
+"""Recognise the GEMM program family in a traced tile program.
+
+The reference lowers `T.copy` / `T.gemm` tile operators one by one (src/op/copy.cc:868-901,
+src/op/gemm.cc:437-573, src/op/gemm_py.cc:245-282) and relies on ~48 generic passes to stitch
+pipelining, barriers and layouts around them.  The B200 kernel embodies all of that, so the
+"lowering" here is pattern recognition: the trace of
+
+    with T.Kernel(ceildiv(N, bN), ceildiv(M, bM), threads=...) as (bx, by):
+        [T.clear(C_acc)]
+        for k in T.Pipelined(ceildiv(K, bK), num_stages=...):
+            T.copy(A[by*bM, k*bK], A_shared); T.copy(B[...], B_shared)
+            T.gemm(A_shared, B_shared, C_acc, transpose_A, transpose_B, [clear_accum=k==0], ...)
+        [element-wise epilogue over C_acc]
+        T.copy(C_acc, [C_local ->] [C_shared ->] C[by*bM, bx*bN])
+
+is turned into ONE whole-problem descriptor.  Anything that does not match raises
+NotImplementedError naming the first thing that fell outside the family.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+from . import language as T
+from .language.expr import BinOp, Call, Const, Expr, Var, as_affine, is_const
+
+
+@dataclass
+class GemmProgram:
+    M: int
+    N: int
+    K: int
+    in_dtype: str
+    out_dtype: str
+    accum_dtype: str
+    trans_A: bool
+    trans_B: bool
+    a_param: int  # positions of A, B, C in the prim_func signature
+    b_param: int
+    c_param: int
+    block_M: int
+    block_N: int
+    block_K: int
+    num_stages: int
+    threads: Optional[int]
+    relu: bool = False
+    alpha: float = 1.0
+    accumulator: str = "fragment"  # "fragment" (register accumulators in the reference) or "tmem"
+    rasterization: Optional[dict] = None
+    notes: List[str] = field(default_factory=list)
+
+    def summary(self) -> str:
+        lay = ("T" if self.trans_A else "N") + ("T" if self.trans_B else "N")
+        return (f"gemm {self.M}x{self.N}x{self.K} {self.in_dtype}->{self.out_dtype} (acc {self.accum_dtype}) {lay} "
+                f"tile-hint {self.block_M}x{self.block_N}x{self.block_K} stages {self.num_stages}"
+                + (" +relu" if self.relu else "") + (f" alpha={self.alpha}" if self.alpha != 1.0 else ""))
+
+
+class NotAGemmProgram(NotImplementedError):
+    pass
+
+
+def _fail(msg):
+    raise NotAGemmProgram("this tile program is outside the GEMM family the B200 backend accelerates: " + msg +
+                          " (there is no generic compiler or fallback behind this facade)")
+
+
+def _buf(x):
+    return x.buffer if isinstance(x, T.BufferRegion) else x
+
+
+def _tile_origin(region, want_vars: Dict[str, Var], what: str):
+    """For a global-tensor window return [(var, scale, offset)] per dimension."""
+    if isinstance(region, T.TileBuffer):
+        return [(None, 0, 0)] * len(region.shape)
+    out = []
+    for s in region.starts:
+        aff = as_affine(s)
+        if aff is None:
+            _fail(f"{what}: index {s!r} is not of the form var*block + const")
+        out.append(aff)
+    return out
+
+
+def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
+    tr = func.trace()
+    if not tr.in_kernel:
+        _fail("no T.Kernel frame")
+    gemms = [o for o in tr.ops if isinstance(o, T.GemmOp)]
+    if len(gemms) != 1:
+        _fail(f"expected exactly one T.gemm, found {len(gemms)}")
+    g = gemms[0]
+    if g.loop is None:
+        _fail("T.gemm is not inside a T.Pipelined / T.serial K loop")
+    kloop = next(li for li in tr.loops if li.var is g.loop)
+    A_s, B_s, C_acc = _buf(g.A), _buf(g.B), _buf(g.C)
+    for nm, b in (("A", A_s), ("B", B_s)):
+        if b.is_global or not b.scope.startswith("shared") or b.scope in ("shared.tmem", "shared.barrier"):
+            _fail(f"T.gemm operand {nm} must be a shared-memory tile (gemm_ss); got scope {b.scope!r} "
+                  "(reference tcgen05 path supports gemm_ss only: tileop/gemm/gemm_tcgen05.py:84-86)")
+    if C_acc.scope not in ("local.fragment", "shared.tmem"):
+        _fail(f"accumulator scope {C_acc.scope!r}")
+    if g.k_pack not in (1, 2):
+        raise ValueError("T.gemm: k_pack must be 1 or 2")  # src/op/gemm.cc:84-86
+    if len(A_s.shape) != 2 or len(B_s.shape) != 2 or len(C_acc.shape) != 2:
+        _fail("tile buffers must be 2-D")
+
+    bM, bN = C_acc.shape
+    bK = A_s.shape[0] if g.transpose_A else A_s.shape[1]
+    exp_a = (bK, bM) if g.transpose_A else (bM, bK)
+    exp_b = (bN, bK) if g.transpose_B else (bK, bN)
+    if tuple(A_s.shape) != exp_a or tuple(B_s.shape) != exp_b:
+        _fail(f"tile shapes A{A_s.shape} B{B_s.shape} C{C_acc.shape} are inconsistent with transpose flags")
+    if A_s.dtype != B_s.dtype:
+        _fail(f"A is {A_s.dtype} but B is {B_s.dtype}")
+
+    # ---- staging copies: global -> A_shared / B_shared inside the K loop
+    def staging(tile, nm):
+        cs = [o for o in tr.ops if isinstance(o, T.CopyOp) and _buf(o.dst) is tile]
+        if len(cs) != 1:
+            _fail(f"expected one T.copy into {nm}_shared, found {len(cs)}")
+        c = cs[0]
+        if c.loop is not g.loop:
+            _fail(f"T.copy into {nm}_shared is not in the same K loop as T.gemm")
+        src = _buf(c.src)
+        if not src.is_global:
+            _fail(f"{nm}_shared is not filled from a global tensor")
+        if src.dtype != tile.dtype:
+            _fail(f"T.copy {src.name}->{nm}_shared changes dtype ({src.dtype}->{tile.dtype})")
+        if len(src.shape) != 2:
+            _fail(f"global operand {src.name} must be 2-D")
+        return src, _tile_origin(c.src, {}, f"T.copy {src.name}->{nm}_shared")
+
+    A_g, a_org = staging(A_s, "A")
+    B_g, b_org = staging(B_s, "B")
+    bvars = list(tr.block_vars)
+
+    def classify(org, dims_are, nm):
+        """dims_are: tuple naming each dim of the global operand, e.g. ('M','K').  Returns block var of the M/N dim."""
+        blk = None
+        for (v, sc, off), role, tile_ext in zip(org, dims_are, (exp_a if nm == "A" else exp_b)):
+            if off != 0:
+                _fail(f"{nm}: tile origin has a constant offset {off}")
+            if role == "K":
+                if v is not g.loop or sc != bK:
+                    _fail(f"{nm}: K index must be k*block_K (got {v!r}*{sc})")
+            else:
+                if v is None and sc == 0:
+                    blk = None  # single tile along this dimension
+                elif any(v is bv for bv in bvars) and sc == tile_ext:
+                    blk = v
+                else:
+                    _fail(f"{nm}: {role} index must be block_index*block_{role} (got {v!r}*{sc}, tile {tile_ext})")
+        return blk
+
+    a_dims = ("K", "M") if g.transpose_A else ("M", "K")
+    b_dims = ("N", "K") if g.transpose_B else ("K", "N")
+    m_var = classify(a_org, a_dims, "A")
+    n_var = classify(b_org, b_dims, "B")
+    M = A_g.shape[1] if g.transpose_A else A_g.shape[0]
+    K = A_g.shape[0] if g.transpose_A else A_g.shape[1]
+    N = B_g.shape[0] if g.transpose_B else B_g.shape[1]
+    K_b = B_g.shape[1] if g.transpose_B else B_g.shape[0]
+    for v in (M, N, K, K_b):
+        if not isinstance(v, int):
+            _fail("dynamic shapes")
+    if K != K_b:
+        _fail(f"K of A ({K}) != K of B ({K_b})")
+
+    # ---- K loop must cover ceildiv(K, bK)
+    ext = kloop.extent
+    ext_v = ext if isinstance(ext, int) else None
+    if ext_v is None:
+        try:
+            from .language.expr import evaluate
+            ext_v = int(evaluate(ext, {}))
+        except Exception:  # noqa: BLE001
+            _fail("K loop extent is not a compile-time constant")
+    if ext_v != -(-K // bK):
+        _fail(f"K loop runs {ext_v} iterations, expected ceildiv({K},{bK}) = {-(-K // bK)}")
+
+    # ---- grid must cover the output
+    def grid_extent(v):
+        e = v.extent
+        if isinstance(e, int):
+            return e
+        from .language.expr import evaluate
+        return int(evaluate(e, {}))
+
+    if m_var is not None and grid_extent(m_var) != -(-M // bM):
+        _fail(f"grid dimension of {m_var!r} is {grid_extent(m_var)}, expected ceildiv(M, block_M) = {-(-M // bM)}")
+    if n_var is not None and grid_extent(n_var) != -(-N // bN):
+        _fail(f"grid dimension of {n_var!r} is {grid_extent(n_var)}, expected ceildiv(N, block_N) = {-(-N // bN)}")
+    if m_var is None and M > bM or n_var is None and N > bN:
+        _fail("a single tile does not cover the output and no block index walks it")
+
+    # ---- accumulator initialisation: T.clear before the loop, or clear_accum = (k == 0)
+    cleared = any(isinstance(o, T.ClearOp) and o.buffer is C_acc and o.value == 0.0 and o.loop is None for o in tr.ops)
+    ca = g.clear_accum
+    clear_first = False
+    if isinstance(ca, BinOp) and ca.op == "==":
+        clear_first = (ca.a is g.loop and is_const(ca.b, 0)) or (ca.b is g.loop and is_const(ca.a, 0))
+        if not clear_first:
+            _fail(f"clear_accum={ca!r} is not `k == 0`")
+    elif isinstance(ca, Expr):
+        _fail(f"clear_accum={ca!r}")
+    elif ca:
+        if ext_v != 1:
+            _fail("clear_accum=True inside a multi-iteration K loop discards all but the last K block")
+        clear_first = True
+    if not (cleared or clear_first):
+        _fail("the accumulator is never cleared (T.clear(C) before the loop or clear_accum=(k == 0)); "
+              "accumulating into an uninitialised tile has no whole-GEMM meaning")
+
+    # ---- epilogue: follow C_acc through on-chip copies to the global store
+    post = tr.ops[tr.ops.index(g) + 1:]
+    relu = False
+    alpha = 1.0
+    cur = C_acc
+    C_g, c_org = None, None
+    for o in post:
+        if isinstance(o, T.CopyOp):
+            if o.loop is not None:
+                _fail("T.copy inside the K loop after T.gemm")
+            if _buf(o.src) is not cur:
+                _fail(f"epilogue copies a buffer ({_buf(o.src).name}) that does not hold the accumulator")
+            dst = _buf(o.dst)
+            if dst.is_global:
+                C_g, c_org = dst, _tile_origin(o.dst, {}, f"T.copy ->{dst.name}")
+                break
+            if tuple(dst.shape) != (bM, bN):
+                _fail(f"epilogue staging buffer {dst.name} has shape {dst.shape}, expected {(bM, bN)}")
+            cur = dst
+        elif isinstance(o, T.ElemStore):
+            if o.buffer is not cur or len(o.index) != 2 or tuple(o.index) != tuple(o.parallel_vars):
+                _fail("element-wise epilogue must be `C[i, j] = f(C[i, j])` over the whole accumulator tile")
+            if tuple(v.extent for v in o.parallel_vars) != (bM, bN):
+                _fail("element-wise epilogue does not cover the accumulator tile")
+            val = o.value
+
+            def is_self(x):
+                return isinstance(x, T.ElemLoad) and x.buffer is cur and tuple(x.index) == tuple(o.index)
+
+            if isinstance(val, Call) and val.fn == "max" and ((is_self(val.args[0]) and is_const(val.args[1], 0)) or
+                                                              (is_self(val.args[1]) and is_const(val.args[0], 0))):
+                if alpha < 0:
+                    _fail("relu after a negative scale")
+                relu = True  # examples/quickstart.py:42-43
+            elif isinstance(val, BinOp) and val.op == "*" and ((is_self(val.a) and isinstance(val.b, Const)) or
+                                                               (is_self(val.b) and isinstance(val.a, Const))):
+                if relu:
+                    _fail("scale after relu (kernel applies alpha before relu)")
+                alpha *= float(val.b.value if is_self(val.a) else val.a.value)
+            else:
+                _fail(f"element-wise epilogue {val!r} (supported: relu, scale by a constant)")
+        elif isinstance(o, T.ClearOp):
+            _fail("T.clear/T.fill after T.gemm")
+    if C_g is None:
+        _fail("the accumulator is never copied to a global tensor")
+    if tuple(C_g.shape) != (M, N):
+        _fail(f"output tensor {C_g.name} has shape {C_g.shape}, expected {(M, N)}")
+    for (v, sc, off), want_v, ext_ in zip(c_org, (m_var, n_var), (bM, bN)):
+        if off != 0 or (want_v is None and v is not None) or (want_v is not None and (v is not want_v or sc != ext_)):
+            _fail("output tile origin does not match the operand tiles' block indices")
+    if len({A_g.param_index, B_g.param_index, C_g.param_index}) != 3:
+        _fail("A, B and C must be three distinct kernel parameters")
+    extra = [p for p in tr.params if p.param_index not in (A_g.param_index, B_g.param_index, C_g.param_index)]
+    if extra:
+        _fail(f"extra kernel parameters {[p.name for p in extra]}")
+    if A_s.dtype not in ("float16", "bfloat16", "float8_e4m3", "float8_e5m2"):
+        _fail(f"operand dtype {A_s.dtype}")
+    if C_acc.dtype != "float32":
+        _fail(f"accumulator dtype {C_acc.dtype}: the tcgen05 path accumulates in fp32 "
+              "(north_star; reference allows fp16 accumulate for fp8 only, tcgen5_meta.h:56-58)")
+    if C_g.dtype not in ("float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2"):
+        _fail(f"output dtype {C_g.dtype}")
+
+    notes = []
+    if g.wg_wait not in (0, -1):
+        notes.append(f"wg_wait={g.wg_wait} ignored (MMA completion is tracked by the kernel's own mbarriers)")
+    return GemmProgram(M=M, N=N, K=K, in_dtype=A_s.dtype, out_dtype=C_g.dtype, accum_dtype=C_acc.dtype,
+                       trans_A=g.transpose_A, trans_B=g.transpose_B, a_param=A_g.param_index, b_param=B_g.param_index,
+                       c_param=C_g.param_index, block_M=bM, block_N=bN, block_K=bK, num_stages=kloop.num_stages,
+                       threads=tr.threads if isinstance(tr.threads, int) else None, relu=relu, alpha=alpha,
+                       accumulator="tmem" if C_acc.scope == "shared.tmem" else "fragment", rasterization=tr.swizzle,
+                       notes=notes)
