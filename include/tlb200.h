@@ -74,11 +74,11 @@ typedef struct tlb200_gemm_desc {
   float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
   uint32_t epilogue;  /* TLB200_EPI_* */
   int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles */
-  int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] */
+  int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] or of 64 in (256,512] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
   int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */
-  int32_t reserved[3];
+  int32_t reserved[3];   /* reserved[0] = cfg_epi_warps: 0 auto, 4 or 8 epilogue warps; rest must be 0 */
 } tlb200_gemm_desc;
 
 /* The configuration the library resolved for a descriptor (for reports/tests). */
@@ -87,7 +87,7 @@ typedef struct tlb200_gemm_plan {
   int32_t tiles_m, tiles_n, grid, threads, smem_bytes;
   int32_t raster, epilogue, tmem_cols;
   uint32_t instr_desc;
-  int32_t reserved[2];
+  int32_t umma_n, epi_warps; /* N of one tcgen05.mma (block_n / accumulators per tile); epilogue warps */
 } tlb200_gemm_plan;
 
 /* Replaces the generated `int init()` (wrapper.py:40-44): binds the CUDA

@@ -77,18 +77,20 @@ def test_smem_desc_bit_exact_vs_oracle(built_lib):
 
 
 def test_plan_headline_configs(built_lib):
-    p = G.plan(8192, 8192, 8192)  # C2
-    assert (p["cta_group"], p["block_m"], p["block_n"], p["block_k"]) == (2, 256, 256, 64)
-    assert p["grid"] == 148 and p["tmem_cols"] == 512 and p["smem_bytes"] <= 232448
-    assert p["tiles_m"] * p["tiles_n"] == 1024
+    p = G.plan(8192, 8192, 8192)  # C2: 2-CTA pairs, 256 x 512 tiles = two 256-column accumulators sharing the A stage
+    assert (p["cta_group"], p["block_m"], p["block_n"], p["block_k"], p["umma_n"]) == (2, 256, 512, 64, 256)
+    assert p["grid"] == 148 and p["tmem_cols"] == 512 and p["smem_bytes"] <= 232448 and p["threads"] == 384
+    assert p["tiles_m"] * p["tiles_n"] == 512 and p["stages"] == 4
     assert p["instr_desc"] == D.tcgen5_instr_desc(256, 256, 16, "bfloat16", "float32")
     p8 = G.plan(8192, 8192, 8192, torch.float8_e4m3fn, torch.bfloat16)  # C3
     assert p8["block_k"] == 128 and p8["instr_desc"] == D.tcgen5_instr_desc(256, 256, 32, "float8_e4m3", "float32")
     pq = G.plan(1024, 1024, 1024, torch.float16, torch.float16, False, False, cta_group=1)  # C1 shape, NN
     assert pq["instr_desc"] == D.tcgen5_instr_desc(128, 256, 16, "float16", "float32", True, False)
+    assert pq["block_n"] == 256 and pq["threads"] == 256  # small problems keep double-buffered 256-wide tiles
     for m, n, k in ((16384, 14336, 4096), (16384, 4096, 14336)):  # C4
         p4 = G.plan(m, n, k)
-        assert p4["tiles_m"] * p4["tiles_n"] == (m // 256) * (n // 256)
+        assert p4["block_n"] == 512 and p4["tiles_m"] * p4["tiles_n"] == (m // 256) * (n // 512)
+    assert G.plan(8192, 8192, 8192, block_n=256)["stages"] == 6
 
 
 def test_plan_small_and_ragged(built_lib):

@@ -37,7 +37,7 @@ def test_recognize_benchmark_style_program():
     assert (p.a_param, p.b_param, p.c_param) == (0, 1, 2) and k.out_idx == [2] and not p.relu
     assert p.accumulator == "fragment" and p.rasterization["panel_size"] == 10
     plan = k.plan()
-    assert plan["cta_group"] == 2 and plan["block_n"] == 256
+    assert plan["cta_group"] == 2 and plan["block_n"] == 512 and plan["umma_n"] == 256
 
 
 def test_recognize_quickstart_c1_descriptor():

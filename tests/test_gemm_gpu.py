@@ -65,11 +65,11 @@ def test_reference_tcgen05_grid(m, n, k, dt):
 @pytest.mark.parametrize("ta,tb", [(False, True), (False, False), (True, True), (True, False)], ids=["nt", "nn", "tn", "tt"])
 @pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.bfloat16), (torch.float16, torch.float32),
                                     (torch.float8_e4m3fn, torch.bfloat16), (torch.float8_e5m2, torch.float16)])
-@pytest.mark.parametrize("cg", [1, 2])
-def test_bit_exact_vs_c_oracle_integer_inputs(ta, tb, dt, out, cg):
+@pytest.mark.parametrize("cg,bn", [(1, 0), (2, 0), (2, 512)])
+def test_bit_exact_vs_c_oracle_integer_inputs(ta, tb, dt, out, cg, bn):
     m, n, k = 192, 320, 256
     a, b = operands(m, n, k, dt, ta, tb, "int")
-    c = G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=out, cta_group=cg)
+    c = G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=out, cta_group=cg, block_n=bn)
     want = R.c_oracle_gemm(a, b, out, ta, tb)
     assert bit_equal(c.cpu(), want)
 
@@ -192,7 +192,8 @@ def test_llama_mlp_shapes(m, n, k):
 
 
 @pytest.mark.parametrize("cfg", [dict(cta_group=1, block_n=128), dict(cta_group=2, block_n=64), dict(cta_group=2, block_n=192),
-                                 dict(cta_group=1, block_n=96, stages=3), dict(cta_group=2, block_n=32), dict(cta_group=2, raster=1), dict(cta_group=2, raster=64, stages=2)])
+                                 dict(cta_group=1, block_n=96, stages=3), dict(cta_group=2, block_n=32), dict(cta_group=2, block_n=512),
+                                 dict(cta_group=2, block_n=512, epi_warps=4, epilogue=1), dict(cta_group=1, block_n=384, stages=2), dict(cta_group=2, block_n=448), dict(cta_group=2, raster=1), dict(cta_group=2, raster=64, stages=2)])
 def test_tuning_knobs_do_not_change_results(cfg):
     a, b = operands(1000, 1200, 520, torch.bfloat16)
     base = G.gemm(a, b, cta_group=1, block_n=256, epilogue=1)

@@ -13,7 +13,7 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libtlb200.so")
+LIB_PATH = os.environ.get("TLB200_LIB") or os.path.join(_HERE, "lib", "libtlb200.so")
 ABI_VERSION = 1
 
 # tlb200_dtype
@@ -61,7 +61,8 @@ class GemmPlan(ctypes.Structure):
         ("epilogue", ctypes.c_int32),
         ("tmem_cols", ctypes.c_int32),
         ("instr_desc", ctypes.c_uint32),
-        ("reserved", ctypes.c_int32 * 2),
+        ("umma_n", ctypes.c_int32),
+        ("epi_warps", ctypes.c_int32),
     ]
 
     def as_dict(self):

@@ -35,11 +35,10 @@ namespace tlb200 {
 constexpr int kBlockM = 128;          // rows of C per CTA (TMEM lanes)
 constexpr int kStageRowBytes = 128;   // K bytes per stage row = one 128B swizzle atom
 constexpr int kUmmaKBytes = 32;       // K bytes consumed by one tcgen05.mma
-constexpr int kThreads = 256;
+constexpr int kMaxThreads = 384;      // 4 control warps + up to 8 epilogue warps
 constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple of 4)
-constexpr int kEpiWarps = 4;
-constexpr int kEpiBufBytes = 32 * 128;     // one warp's staging slab: 32 rows x 128 B
-constexpr int kEpiBufsPerWarp = 2;
+constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
+constexpr int kEpiSlabs = 8;               // slabs per CTA: 4 warps x 2 or 8 warps x 1 (32 KiB)
 constexpr int kMaxStages = 12;
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
 
@@ -55,13 +54,18 @@ struct alignas(64) GemmKernelParams {
   int num_k_blocks;
   int tiles_m, tiles_n;  // in units of (kBlockM * cta_group) rows, block_n columns
   int raster;            // tile rows per raster group
-  int block_n;
+  int block_n;           // tile width = n_sub * umma_n
+  int umma_n;            // N of one tcgen05.mma (<= 256)
+  int n_sub;             // accumulators per tile (1, or 2 for 512-wide tiles sharing the A stage)
+  int acc_stages;        // 2 = double-buffered accumulator (block_n <= 256), 1 = the tile fills TMEM
+  int epi_warps;         // 4 or 8
   int stages;
   int k_elems_per_block;  // 128 / sizeof(ab)
   int a_mn_major, b_mn_major;
   int a_boxes, b_boxes;            // TMA issues per stage for A / B
   int a_box_bytes, b_box_bytes;    // bytes each issue writes
-  int b_rows_per_cta;              // block_n / cta_group
+  int b_rows_per_cta;              // umma_n / cta_group: rows of B one CTA stages per accumulator
+  int b_sub_bytes;                 // bytes of one accumulator's B rows in a stage
   uint32_t idesc;
   uint32_t desc_hi_a, desc_hi_b;   // upper 32 bits of the smem matrix descriptors (SBO, version, swizzle)
   uint32_t desc_lbo_a, desc_lbo_b; // (LBO >> 4) << 16: the leading-byte-offset field of the lower word
@@ -149,8 +153,8 @@ __device__ __forceinline__ void store_scalar(void* c, long long idx, float v) {
 // tmem_acc = TMEM address of the accumulator (lane 0, first column).
 template <int kOut>
 __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_t tmem_acc, int q,
-                                              int lane, int row0, int col0, uint32_t stage_smem,
-                                              int& slab_iter) {
+                                              int lane, int row0, int col0, int cbeg, int cend,
+                                              uint32_t stage_smem, int nslabs, int& slab_iter) {
   constexpr int kOB = OutTraits<kOut>::kBytes;
   constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
   constexpr int kPacketsPerLd = 32 * kOB / 16;  // 16 B packets produced by one x32 load
@@ -161,31 +165,46 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
   const bool relu = p.relu != 0;
 
   if (p.epi_tma) {
-    for (int cs = 0; cs < p.block_n; cs += kColsPerSlab) {
+    // Per 128-byte-wide slab: TMEM loads (two x32 loads in flight) and the cast run BEFORE waiting
+    // for the TMA store that last read the slab, so that store's smem read is hidden behind them.
+    constexpr int kLdsPerSlab = kColsPerSlab / 32;
+    constexpr int kPair = kLdsPerSlab >= 2 ? 2 : 1;
+    for (int cs = cbeg; cs < cend; cs += kColsPerSlab) {
       if (col0 + cs >= p.n) break;  // warp-uniform: remaining slabs are fully out of range
-      const uint32_t slab = stage_smem + (slab_iter & (kEpiBufsPerWarp - 1)) * kEpiBufBytes;
-      // The TMA store that last read this slab (two slabs ago) must have drained it.
-      if (lane == 0) tma_store_wait_read<kEpiBufsPerWarp - 1>();
-      __syncwarp();
+      const uint32_t slab = stage_smem + (nslabs == 2 ? (slab_iter & 1) : 0) * kEpiBufBytes;
+      bool slab_free = false;
 #pragma unroll
-      for (int l = 0; l < kColsPerSlab / 32; ++l) {
-        if (cs + l * 32 < p.block_n) {
-          uint32_t r[32];
-          tmem_ld_32x32(lane_taddr + cs + l * 32, r);
+      for (int l0 = 0; l0 < kLdsPerSlab; l0 += kPair) {
+        if (cs + l0 * 32 < cend) {
+          uint32_t r[kPair][32];
+          tmem_ld_32x32(lane_taddr + cs + l0 * 32, r[0]);
+          if constexpr (kPair == 2) tmem_ld_32x32(lane_taddr + cs + (l0 + 1) * 32, r[1]);
           tmem_ld_wait();
-          float v[32];
+          uint4 w[kPair * kPacketsPerLd];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float x = __uint_as_float(r[i]) * alpha;
-            v[i] = relu ? fmaxf(x, 0.f) : x;
+          for (int h = 0; h < kPair; ++h) {
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float x = __uint_as_float(r[h][i]) * alpha;
+              v[i] = relu ? fmaxf(x, 0.f) : x;
+            }
+#pragma unroll
+            for (int pk = 0; pk < kPacketsPerLd; ++pk) w[h * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
+          }
+          if (!slab_free) {  // the TMA store that last read this slab must have drained it
+            if (lane == 0) {
+              if (nslabs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
+            }
+            __syncwarp();
+            slab_free = true;
           }
 #pragma unroll
-          for (int pk = 0; pk < kPacketsPerLd; ++pk) {
-            const int chunk = l * kPacketsPerLd + pk;  // 16 B chunk index in the 128 B row
+          for (int pk = 0; pk < kPair * kPacketsPerLd; ++pk) {
+            const int chunk = l0 * kPacketsPerLd + pk;  // 16 B chunk index in the 128 B row
             const uint32_t addr = slab + lane * 128 + ((chunk ^ (lane & 7)) << 4);
-            uint4 w = pack16<kOut>(&v[pk * kValsPerPacket]);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w.x), "r"(w.y),
-                         "r"(w.z), "r"(w.w)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[pk].x), "r"(w[pk].y),
+                         "r"(w[pk].z), "r"(w[pk].w)
                          : "memory");
           }
         }
@@ -201,7 +220,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
   } else {
     const bool row_ok = grow < p.m;
     const bool vec_ok = ((p.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(p.c) % 16) == 0);
-    for (int cs = 0; cs < p.block_n; cs += 32) {
+    for (int cs = cbeg; cs < cend; cs += 32) {
       if (col0 + cs >= p.n) break;
       uint32_t r[32];
       tmem_ld_32x32(lane_taddr + cs, r);
@@ -237,8 +256,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
 // region the compiler cannot prove uniformity and wraps every such instruction in an
 // ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" loop, which made the first version of this kernel
 // issue-bound (~870 cycles per K-block instead of 512; profiles/r1_notes.md).
-template <int kCta, bool kF8>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int kCta, bool kF8, int kNSub>
+__global__ void __launch_bounds__(kMaxThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -249,22 +268,23 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
-  const uint32_t b_stage_bytes = static_cast<uint32_t>(p.b_rows_per_cta) * kStageRowBytes;
+  constexpr int n_sub = kNSub;  // accumulators per tile (compile-time: a predicated-off tcgen05.mma is not free)
+  const int acc_stages = p.acc_stages;
+  const uint32_t b_sub_bytes = static_cast<uint32_t>(p.b_sub_bytes);
+  const uint32_t b_stage_bytes = b_sub_bytes * n_sub;
   const uint32_t smem_a = smem_base;
   const uint32_t smem_b = smem_a + stages * kABytesPerStage;
   const uint32_t smem_epi = smem_b + stages * b_stage_bytes;
-  const uint32_t smem_bar = smem_epi + kEpiWarps * kEpiBufsPerWarp * kEpiBufBytes;
+  const uint32_t smem_bar = smem_epi + kEpiSlabs * kEpiBufBytes;
   const uint32_t bar_full = smem_bar;                    // [stages]
   const uint32_t bar_empty = bar_full + 8 * stages;      // [stages]
   const uint32_t bar_tfull = bar_empty + 8 * stages;     // [2]
   const uint32_t bar_tempty = bar_tfull + 16;            // [2]
   const uint32_t smem_tptr = bar_tempty + 16;            // u32 TMEM base address
   const uint32_t stage_tx_bytes = (kABytesPerStage + b_stage_bytes) * kCta;
-  const uint32_t tmem_cols = (2u * p.block_n <= 32u)    ? 32u
-                             : (2u * p.block_n <= 64u)  ? 64u
-                             : (2u * p.block_n <= 128u) ? 128u
-                             : (2u * p.block_n <= 256u) ? 256u
-                                                        : 512u;
+  const uint32_t acc_cols = static_cast<uint32_t>(p.block_n) * acc_stages;
+  const uint32_t tmem_cols = acc_cols <= 32u ? 32u : acc_cols <= 64u ? 64u : acc_cols <= 128u ? 128u
+                             : acc_cols <= 256u ? 256u : 512u;
 
   if (warp == 0) {
     if (elect_one()) {
@@ -279,8 +299,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         mbar_init(bar_empty + 8 * s, 1);  // one tcgen05.commit
       }
       for (int a = 0; a < 2; ++a) {
-        mbar_init(bar_tfull + 8 * a, 1);                    // one tcgen05.commit
-        mbar_init(bar_tempty + 8 * a, kEpiWarps * kCta);    // one arrive per epilogue warp (per CTA)
+        mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
+        mbar_init(bar_tempty + 8 * a, p.epi_warps * kCta);    // one arrive per epilogue warp (per CTA)
       }
       fence_mbar_init();
     }
@@ -339,11 +359,17 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
             else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
           }
-          for (int j = 0; j < p.b_boxes; ++j) {
-            const int c0 = p.b_mn_major ? row_b + j * kspan : k0;
-            const int c1 = p.b_mn_major ? k0 : row_b + j * b_rows_per_box;
-            if constexpr (kCta == 2) tma_load_2d_pair(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
-            else tma_load_2d(dst_b + j * p.b_box_bytes, &p.tm_b, full, c0, c1, pol);
+          // accumulator h of the tile covers tile columns [h*umma_n, (h+1)*umma_n)
+#pragma unroll
+          for (int h = 0; h < n_sub; ++h) {
+            const int rb = row_b + h * p.umma_n;
+            for (int j = 0; j < p.b_boxes; ++j) {
+              const int c0 = p.b_mn_major ? rb + j * kspan : k0;
+              const int c1 = p.b_mn_major ? k0 : rb + j * b_rows_per_box;
+              const uint32_t dst = dst_b + h * b_sub_bytes + j * p.b_box_bytes;
+              if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol);
+              else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol);
+            }
           }
         }
         __syncwarp();
@@ -359,70 +385,120 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       const uint64_t hi_b = static_cast<uint64_t>(p.desc_hi_b) << 32 | p.desc_lbo_b;
       const uint32_t kadv_a = p.kadv_a, kadv_b = p.kadv_b;
       const uint32_t a_lo0 = (smem_a & 0x3FFFFu) >> 4, b_lo0 = (smem_b & 0x3FFFFu) >> 4;
-      const uint32_t a_step = kABytesPerStage >> 4, b_step = b_stage_bytes >> 4;
+      const uint32_t a_step = kABytesPerStage >> 4, b_step = b_stage_bytes >> 4, b_sub = b_sub_bytes >> 4;
+      const uint32_t umma_n = p.umma_n;
       int s = 0;
       uint32_t ph = 0;
-      int it = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
-        const int as = it & 1;
-        const uint32_t aph = (it >> 1) & 1u;
-        mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * p.block_n;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
-          tc_fence_after();
-          if (elected) {
-            const uint32_t a_lo = a_lo0 + s * a_step;
-            const uint32_t b_lo = b_lo0 + s * b_step;
+      int as = 0;
+      uint32_t aph = 0;
+      auto issue_kblock = [&](int stage, uint32_t d_tmem, uint32_t b_extra, bool first_kb) {
+        const uint32_t a_lo = a_lo0 + stage * a_step;
+        const uint32_t b_lo = b_lo0 + stage * b_step + b_extra;
 #pragma unroll
-            for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
-              const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
-              const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
-              umma_ss<kCta, kF8>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
-            umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
-          }
-          __syncwarp();
-          if (++s == stages) { s = 0; ph ^= 1u; }
+        for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
+          const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
+          const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
+          umma_ss<kCta, kF8>(d_tmem, da, db, idesc, (first_kb && k == 0) ? 0u : 1u);
         }
-        if (elected) umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
-        __syncwarp();
+      };
+      if constexpr (kNSub == 1) {
+        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+          mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * p.block_n;
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
+            tc_fence_after();
+            if (elected) {
+              issue_kblock(s, d_tmem, 0u, kb == 0);
+              umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
+            }
+            __syncwarp();
+            if (++s == stages) { s = 0; ph ^= 1u; }
+          }
+          if (elected) umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
+          __syncwarp();
+          if (++as == acc_stages) { as = 0; aph ^= 1u; }
+        }
+      } else {
+        // Two accumulators per tile sharing every A stage (they fill TMEM, so there is no second
+        // buffer: the epilogue of a tile is exposed).  tmem_full/empty[h] belong to accumulator h; the
+        // epilogue hands accumulator 0 back first.  (Letting accumulator 0 of the next tile run ahead
+        // while accumulator 1 drains was measured: no gain on a power-capped part — profiles/r1_notes.md.)
+        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+          mbar_wait(bar_tempty, aph ^ 1u, 1);
+          mbar_wait(bar_tempty + 8, aph ^ 1u, 4);
+          tc_fence_after();
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(bar_full + 8 * s, ph, 2);
+            tc_fence_after();
+            if (elected) {
+              const uint32_t a_lo = a_lo0 + s * a_step;
+              const uint32_t b_lo = b_lo0 + s * b_step;
+#pragma unroll
+              for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
+                const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
+                const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+                umma_ss<kCta, kF8>(tmem_base, da, hi_b | ((b_lo + k * kadv_b) & 0x3FFFu), idesc, acc);
+                umma_ss<kCta, kF8>(tmem_base + umma_n, da, hi_b | ((b_lo + b_sub + k * kadv_b) & 0x3FFFu), idesc, acc);
+              }
+              umma_commit<kCta>(bar_empty + 8 * s);
+              if (kb + 1 == nkb) {
+                umma_commit<kCta>(bar_tfull);
+                umma_commit<kCta>(bar_tfull + 8);
+              }
+            }
+            __syncwarp();
+            if (++s == stages) { s = 0; ph ^= 1u; }
+          }
+          aph ^= 1u;
+        }
       }
     }
   } else if (warp >= kEpiWarp0) {
     // ===================================================== epilogue warps
-    const int q = warp - kEpiWarp0;  // == warp % 4: the TMEM lane quarter this warp may read
-    const uint32_t my_stage = smem_epi + q * kEpiBufsPerWarp * kEpiBufBytes;
+    const int ew = warp - kEpiWarp0;
+    const int q = ew & 3;            // == warp % 4: the TMEM lane quarter this warp may read
+    const int chalf = ew >> 2;       // with 8 epilogue warps: which half of the tile's columns
+    const int nslabs = kEpiSlabs / p.epi_warps;  // 2 or 1 staging slabs per warp
+    const uint32_t my_stage = smem_epi + ew * nslabs * kEpiBufBytes;
     const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, 0) : bar_tempty;
-    int it = 0;
+    // Column range of this warp inside ONE accumulator (all warps drain accumulator 0, then 1).
+    const int acc_width = (kNSub == 2) ? p.umma_n : p.block_n;
+    const int ccols = acc_width / (p.epi_warps >> 2);
+    int as = 0;
+    uint32_t aph = 0;
     int slab_iter = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
+    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       int tm, tn;
       tile_coord(t, tm, tn);
-      const int as = it & 1;
-      const uint32_t aph = (it >> 1) & 1u;
       const int row0 = (tm * kCta + (int)cta_rank) * kBlockM;
       const int col0 = tn * p.block_n;
-      mbar_wait(bar_tfull + 8 * as, aph, 3);
-      tc_fence_after();
-      const uint32_t acc = tmem_base + as * p.block_n;
-      if (row0 < p.m) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
-        switch (p.out_kind) {
-          case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
-          case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
-          case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
-          case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
-          default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, col0, my_stage, slab_iter); break;
+#pragma unroll
+      for (int h = 0; h < kNSub; ++h) {
+        const int bi = (kNSub == 2) ? h : as;  // barrier / accumulator slot
+        mbar_wait(bar_tfull + 8 * bi, aph, 3);
+        tc_fence_after();
+        const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
+        const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
+        if (row0 < p.m) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
+          switch (p.out_kind) {
+            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+          }
+        }
+        // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * bi);
+          else mbar_arrive(bar_tempty + 8 * bi);
         }
       }
-      // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * as);
-        else mbar_arrive(bar_tempty + 8 * as);
-      }
+      if constexpr (kNSub == 2) { aph ^= 1u; } else if (++as == acc_stages) { as = 0; aph ^= 1u; }
     }
     if (p.epi_tma && lane == 0) tma_store_wait_all<0>();
   }

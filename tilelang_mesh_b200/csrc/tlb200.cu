@@ -6,6 +6,7 @@
 // No allocation, no retained pointers, thread-local error text.
 #include "tlb200.h"
 
+#include <array>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -41,8 +42,7 @@ int g_sm_count[kMaxDevices] = {0};
 bool g_dev_ready[kMaxDevices] = {false};
 
 constexpr int kSmemLimit = 232448;  // 227 KiB opt-in per block on sm_100
-constexpr int kSmemFixed = 1024 /*alignment slack*/ + kEpiWarps * kEpiBufsPerWarp * kEpiBufBytes +
-                           (2 * kMaxStages + 4) * 8 + 16;
+constexpr int kSmemFixed = 1024 /*alignment slack*/ + kEpiSlabs * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16;
 
 int dtype_bytes(int dt) {
   switch (dt) {
@@ -107,6 +107,7 @@ struct Resolved {
   int es, ob;             // operand / output element bytes
   int span;               // elements per 128 B of an operand row
   bool a_mn, b_mn;
+  int n_sub, umma_n, acc_stages, epi_warps;
   int b_rows_per_cta;
   int num_k_blocks;
   bool epi_tma;
@@ -143,19 +144,38 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (cg != 1 && cg != 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", cg);
   if (sm_count > 0 && sm_count < 2) cg = 1;
   int bn = d->cfg_block_n;
-  // The epilogue drains TMEM 32 columns at a time, so tiles are whole multiples of 32 columns;
-  // an N-major B is staged in whole 128 B spans per CTA.
+  // A tile is n_sub accumulators of umma_n (<= 256) columns each.  The epilogue drains TMEM 32
+  // columns at a time, so umma_n is a whole multiple of 32; an N-major B is staged in whole 128 B
+  // spans per CTA.  Tiles wider than 256 columns (two accumulators sharing one A stage: 25 % less
+  // L2->SM traffic) fill the 512 TMEM columns, so their accumulator is single-buffered.
   const int n_step = r->b_mn ? r->span * cg : 32;
-  const int n_min = n_step;
   if (bn == 0) {
     bn = 256;
-    while (bn / 2 >= d->n && bn / 2 >= n_min) bn /= 2;
+    while (bn / 2 >= d->n && bn / 2 >= n_step) bn /= 2;
+    // Large problems: 512-wide tiles (two accumulators sharing one A stage).  Less L2->SM and
+    // shared-memory traffic per flop means less power and, on a power-capped part, higher clocks;
+    // worth it once every cluster still gets several tiles (the accumulator is single-buffered,
+    // so each tile exposes one epilogue).
+    const long long wide_tiles = static_cast<long long>((d->m + kBlockM * cg - 1) / (kBlockM * cg)) * ((d->n + 511) / 512);
+    const int clusters = (sm_count > 0 ? sm_count : 148) / cg;
+    if (cg == 2 && bn == 256 && d->n >= 512 && wide_tiles >= 3LL * clusters && d->k >= 2048 && 512 % (2 * n_step) == 0) bn = 512;
   }
-  if (bn < n_min || bn > 256 || bn % n_step)
-    return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need a multiple of %d in [%d,256])", bn, cg,
-                r->b_mn ? ", N-major B" : "", n_step, n_min);
-  r->b_rows_per_cta = bn / cg;
-  const int per_stage = kABytesPerStage + r->b_rows_per_cta * kStageRowBytes;
+  r->n_sub = bn > 256 ? 2 : 1;
+  r->umma_n = bn / r->n_sub;
+  if (bn < n_step || bn > 512 || bn % r->n_sub || r->umma_n % n_step)
+    return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need a multiple of %d in [%d,256], or of %d in (256,512])",
+                bn, cg, r->b_mn ? ", N-major B" : "", n_step, n_step, 2 * n_step);
+  r->acc_stages = (2 * bn <= 512) ? 2 : 1;
+  int ew = d->reserved[0];  // cfg_epi_warps
+  if (ew == 0) {  // 8 warps drain a 512-wide tile unless its halves do not split into whole 128-byte slabs
+    const int half = r->umma_n / 2;
+    ew = (bn > 256 && half % 32 == 0 && half % (128 / r->ob) == 0) ? 8 : 4;
+  }
+  if (ew != 4 && ew != 8) return fail("tlb200: cfg_epi_warps must be 0, 4 or 8 (got %d)", ew);
+  if ((r->umma_n / (ew / 4)) % 32) return fail("tlb200: block_n=%d cannot be split over %d epilogue warps", bn, ew);
+  r->epi_warps = ew;
+  r->b_rows_per_cta = r->umma_n / cg;
+  const int per_stage = kABytesPerStage + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
   int stages = d->cfg_stages;
   const int max_stages = (kSmemLimit - kSmemFixed) / per_stage;
   if (stages == 0) stages = max_stages < kMaxStages ? max_stages : kMaxStages;
@@ -175,13 +195,13 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (clusters > tiles) clusters = tiles;
   if (clusters < 1) clusters = 1;
   p.grid = static_cast<int>(clusters) * cg;
-  p.threads = kThreads;
+  p.threads = 128 + 32 * r->epi_warps;
   p.smem_bytes = kSmemFixed + stages * per_stage;
-  p.raster = d->cfg_raster > 0 ? d->cfg_raster : (16 / cg);
+  p.raster = d->cfg_raster > 0 ? d->cfg_raster : (bn > 256 ? 16 : 16 / cg);
   int epi = d->cfg_epilogue;
   const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0);
   // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
-  const bool slab_ok = bn % (128 / r->ob) == 0;
+  const bool slab_ok = (r->umma_n / (r->epi_warps / 4)) % (128 / r->ob) == 0;
   if (epi == 0) epi = (tma_ok && slab_ok) ? 2 : 1;
   if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C and row pitch");
   if (epi == 2 && !slab_ok)
@@ -189,8 +209,11 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (epi != 1 && epi != 2) return fail("tlb200: cfg_epilogue must be 0, 1 or 2");
   p.epilogue = epi;
   r->epi_tma = epi == 2;
-  p.tmem_cols = 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512;
-  p.instr_desc = instr_desc_impl(kBlockM * cg, bn, 32 / r->es, d->ab_dtype, TLB200_FLOAT32, !r->a_mn, !r->b_mn, 1, 1);
+  const int acc_cols = bn * r->acc_stages;
+  p.tmem_cols = acc_cols <= 32 ? 32 : acc_cols <= 64 ? 64 : acc_cols <= 128 ? 128 : acc_cols <= 256 ? 256 : 512;
+  p.umma_n = r->umma_n;
+  p.epi_warps = r->epi_warps;
+  p.instr_desc = instr_desc_impl(kBlockM * cg, r->umma_n, 32 / r->es, d->ab_dtype, TLB200_FLOAT32, !r->a_mn, !r->b_mn, 1, 1);
   if (p.instr_desc == 0) return fail("tlb200: cannot encode instruction descriptor");
   return 0;
 }
@@ -230,6 +253,24 @@ __global__ void fill_zero_kernel(void* c, long long ldc, int m, int n) {
     const long long r = i / n, col = i - r * n;
     store_scalar<kOut>(c, r * ldc + col, 0.f);
   }
+}
+
+typedef void (*GemmKernelFn)(const GemmKernelParams);
+GemmKernelFn pick_kernel(int cg, bool f8, int n_sub) {
+  if (cg == 2) {
+    if (f8) return n_sub == 2 ? gemm_tcgen05_kernel<2, true, 2> : gemm_tcgen05_kernel<2, true, 1>;
+    return n_sub == 2 ? gemm_tcgen05_kernel<2, false, 2> : gemm_tcgen05_kernel<2, false, 1>;
+  }
+  if (f8) return n_sub == 2 ? gemm_tcgen05_kernel<1, true, 2> : gemm_tcgen05_kernel<1, true, 1>;
+  return n_sub == 2 ? gemm_tcgen05_kernel<1, false, 2> : gemm_tcgen05_kernel<1, false, 1>;
+}
+std::array<const void*, 8> all_kernels() {
+  std::array<const void*, 8> k;
+  int i = 0;
+  for (int cg = 1; cg <= 2; ++cg)
+    for (int f8 = 0; f8 < 2; ++f8)
+      for (int ns = 1; ns <= 2; ++ns) k[i++] = reinterpret_cast<const void*>(pick_kernel(cg, f8 != 0, ns));
+  return k;
 }
 
 int out_kind_of(int dt) {
@@ -366,10 +407,11 @@ int tlb200_init(int device) {
       g_encode = reinterpret_cast<EncodeTiledFn>(fn);
     }
     // Same step as the generated init(): raise the dynamic shared memory limit (wrapper.py:15-21).
-    if ((e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(gemm_tcgen05_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) {
+    e = cudaSuccess;
+    for (const void* fn : all_kernels()) {
+      if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) break;
+    }
+    if (e != cudaSuccess) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
     }
@@ -436,10 +478,15 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   kp.tiles_m = pl.tiles_m; kp.tiles_n = pl.tiles_n;
   kp.raster = pl.raster;
   kp.block_n = pl.block_n;
+  kp.umma_n = r.umma_n;
+  kp.n_sub = r.n_sub;
+  kp.acc_stages = r.acc_stages;
+  kp.epi_warps = r.epi_warps;
   kp.stages = pl.stages;
   kp.k_elems_per_block = bk;
   kp.a_mn_major = r.a_mn; kp.b_mn_major = r.b_mn;
   kp.b_rows_per_cta = r.b_rows_per_cta;
+  kp.b_sub_bytes = r.b_rows_per_cta * kStageRowBytes;
   kp.idesc = pl.instr_desc;
   // Shared-memory matrix descriptors, 128B swizzle (layout_type 2), SBO = 8 rows x 128 B.
   // K-major: LBO is ignored by the hardware for swizzled layouts (reference sets 16 B,
@@ -462,7 +509,7 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(pl.grid, 1, 1);
-  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.blockDim = dim3(pl.threads, 1, 1);
   cfg.dynamicSmemBytes = pl.smem_bytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -472,11 +519,7 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  const bool f8 = r.es == 1;
-  if (pl.cta_group == 2) e = f8 ? cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2, true>, kp)
-                                : cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<2, false>, kp);
-  else e = f8 ? cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1, true>, kp)
-              : cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<1, false>, kp);
+  e = cudaLaunchKernelEx(&cfg, pick_kernel(pl.cta_group, r.es == 1, r.n_sub), kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);

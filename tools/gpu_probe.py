@@ -61,6 +61,21 @@ case("c1_8k", 8192, 8192, 8192, out="bf16", data="randn", timeit=True, cta_group
 case("c2_8k", 8192, 8192, 8192, out="bf16", data="randn", timeit=True, cta_group=2)
 case("c2_8k_fp8", 8192, 8192, 8192, ab="e4m3", out="bf16", data="randn", timeit=True, cta_group=2)
 case("auto_8k", 8192, 8192, 8192, out="bf16", data="randn", timeit=True)
+# --- 512-wide tiles (two accumulators per tile, single-buffered TMEM)
+case("w512_c2", 1024, 1024, 512, cta_group=2, block_n=512)
+case("w512_c2_bf16", 1024, 2048, 512, out="bf16", cta_group=2, block_n=512)
+case("w512_c2_tails", 700, 900, 136, out="bf16", cta_group=2, block_n=512)
+case("w512_c2_direct", 700, 900, 136, out="bf16", cta_group=2, block_n=512, epilogue=1)
+case("w512_c2_e4", 1024, 1024, 512, out="bf16", cta_group=2, block_n=512, epi_warps=4)
+case("w512_c1", 512, 1024, 512, cta_group=1, block_n=512)
+case("w384_c2", 512, 768, 256, cta_group=2, block_n=384)
+case("w512_fp8", 1024, 1024, 1024, ab="e4m3", out="bf16", cta_group=2, block_n=512)
+case("w512_nn", 512, 1024, 256, ta=False, tb=False, cta_group=2, block_n=512)
+case("w512_tt", 512, 1024, 256, ta=True, tb=False, cta_group=2, block_n=512)
+case("w512_rand", 2048, 2048, 2048, out="bf16", data="randn", cta_group=2, block_n=512)
+case("w512_8k", 8192, 8192, 8192, out="bf16", data="randn", timeit=True, cta_group=2, block_n=512)
+case("w512_8k_e4", 8192, 8192, 8192, out="bf16", data="randn", timeit=True, cta_group=2, block_n=512, epi_warps=4)
+case("w512_8k_fp8", 8192, 8192, 8192, ab="e4m3", out="bf16", data="randn", timeit=True, cta_group=2, block_n=512)
 
 
 def run_case(name):
