@@ -102,8 +102,10 @@ int tlb200_init(int device);
 int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                 void* stream);
 
-/* Same contract through HOST buffers: stages A and B to the device, runs
- * tlb200_gemm and copies C back, all on `stream`, then synchronises it.
+/* Same contract through HOST buffers (pinned memory for full speed): stages B,
+ * then A in row panels, to the device; runs tlb200_gemm per panel on `stream`
+ * while the next panel is copied in and the previous panel's C is copied out
+ * (two internal copy streams created by tlb200_init), then synchronises.
  * `workspace` is a caller-owned device buffer of at least
  * tlb200_gemm_host_workspace_bytes(desc) bytes (the library never allocates).
  * This is the host-buffer form of the reference's adapter call path

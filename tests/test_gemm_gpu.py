@@ -236,8 +236,8 @@ def test_launches_on_callers_stream_and_counts():
     assert lib.tlb200_launch_count() == n0 + 2
 
 
-def test_host_buffer_entry_point():
-    m, n, k = 512, 384, 256
+@pytest.mark.parametrize("m,n,k", [(512, 384, 256), (4100, 640, 320)], ids=["one_panel", "row_panels"])
+def test_host_buffer_entry_point(m, n, k):
     a = torch.randint(-3, 4, (m, k)).float().bfloat16().pin_memory()
     b = torch.randint(-3, 4, (n, k)).float().bfloat16().pin_memory()
     c = torch.empty(m, n, dtype=torch.bfloat16).pin_memory()

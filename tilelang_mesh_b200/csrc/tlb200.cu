@@ -40,6 +40,14 @@ std::mutex g_init_mu;
 constexpr int kMaxDevices = 64;
 int g_sm_count[kMaxDevices] = {0};
 bool g_dev_ready[kMaxDevices] = {false};
+// Host-buffer path: per device one copy-in and one copy-out stream plus an event ring, created at
+// init (streams/events are driver objects, not device memory; the library still allocates none).
+constexpr int kMaxPanels = 16;
+struct HostPipe {
+  cudaStream_t in = nullptr, out = nullptr;
+  cudaEvent_t fork = nullptr, loaded[kMaxPanels] = {}, done[kMaxPanels] = {}, drained = nullptr;
+};
+HostPipe g_pipe[kMaxDevices];
 
 constexpr int kSmemLimit = 232448;  // 227 KiB opt-in per block on sm_100
 constexpr int kSmemFixed = 1024 /*alignment slack*/ + kEpiSlabs * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16;
@@ -158,7 +166,11 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     // so each tile exposes one epilogue).
     const long long wide_tiles = static_cast<long long>((d->m + kBlockM * cg - 1) / (kBlockM * cg)) * ((d->n + 511) / 512);
     const int clusters = (sm_count > 0 ? sm_count : 148) / cg;
-    if (cg == 2 && bn == 256 && d->n >= 512 && wide_tiles >= 3LL * clusters && d->k >= 2048 && 512 % (2 * n_step) == 0) bn = 512;
+    // 16-bit operands only: with 8-bit operands a tile's MMA time halves while its exposed epilogue
+    // does not, and the double-buffered 256-wide tile measures faster (profiles/r1_notes.md).
+    if (cg == 2 && r->es == 2 && bn == 256 && d->n >= 512 && wide_tiles >= 3LL * clusters && d->k >= 2048 &&
+        512 % (2 * n_step) == 0)
+      bn = 512;
   }
   r->n_sub = bn > 256 ? 2 : 1;
   r->umma_n = bn / r->n_sub;
@@ -197,7 +209,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.grid = static_cast<int>(clusters) * cg;
   p.threads = 128 + 32 * r->epi_warps;
   p.smem_bytes = kSmemFixed + stages * per_stage;
-  p.raster = d->cfg_raster > 0 ? d->cfg_raster : (bn > 256 ? 16 : 16 / cg);
+  p.raster = d->cfg_raster > 0 ? d->cfg_raster : ((bn > 256 || r->es == 1) ? 16 : 16 / cg);
   int epi = d->cfg_epilogue;
   const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0);
   // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
@@ -415,6 +427,17 @@ int tlb200_init(int device) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
     }
+    HostPipe& hp = g_pipe[device];
+    if (!hp.in) {
+      bool ok = cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking) == cudaSuccess &&
+                cudaStreamCreateWithFlags(&hp.out, cudaStreamNonBlocking) == cudaSuccess &&
+                cudaEventCreateWithFlags(&hp.fork, cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventCreateWithFlags(&hp.drained, cudaEventDisableTiming) == cudaSuccess;
+      for (int i = 0; ok && i < kMaxPanels; ++i)
+        ok = cudaEventCreateWithFlags(&hp.loaded[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&hp.done[i], cudaEventDisableTiming) == cudaSuccess;
+      if (!ok) { rc = fail("tlb200_init: cannot create copy streams/events: %s", cudaGetErrorString(cudaGetLastError())); break; }
+    }
     g_dev_ready[device] = true;
   } while (0);
   if (prev >= 0 && prev != device) cudaSetDevice(prev);
@@ -546,24 +569,63 @@ int64_t tlb200_gemm_host_workspace_bytes(const tlb200_gemm_desc* d) {
 int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, void* hc, void* ws,
                      int64_t ws_bytes, void* stream_v) {
   g_err[0] = 0;
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
   const int64_t need = tlb200_gemm_host_workspace_bytes(d);
   if (need < 0) return fail("tlb200_gemm_host: bad descriptor");
   if (ws_bytes < need || (!ws && need > 0)) return fail("tlb200_gemm_host: workspace %lld B < required %lld B", (long long)ws_bytes, (long long)need);
   if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_host: workspace must be 256-byte aligned");
+  if (d->m == 0 || d->n == 0) return 0;
+  if (!hc || (d->k > 0 && (!ha || !hb))) return fail("tlb200_gemm_host: null host pointer");
   const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
   const long long ab = extent_bytes(d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, d->lda, es);
   const long long bb = extent_bytes(d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, d->ldb, es);
-  const long long cb = extent_bytes(d->m, d->n, d->ldc, ob);
   char* da = static_cast<char*>(ws);
   char* db = da + round256(ab);
   char* dc = db + round256(bb);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  HostPipe& hp = g_pipe[dev];
   cudaError_t e;
-  if (ab && (e = cudaMemcpyAsync(da, ha, ab, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return fail("tlb200_gemm_host: H2D A: %s", cudaGetErrorString(e));
-  if (bb && (e = cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, stream)) != cudaSuccess) return fail("tlb200_gemm_host: H2D B: %s", cudaGetErrorString(e));
-  if (int rc = tlb200_gemm(d, da, db, dc, stream_v)) return rc;
-  if (cb && (e = cudaMemcpyAsync(hc, dc, cb, cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail("tlb200_gemm_host: D2H C: %s", cudaGetErrorString(e));
-  if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail("tlb200_gemm_host: %s", cudaGetErrorString(e));
+#define TLB_CK(call, what) if ((e = (call)) != cudaSuccess) return fail("tlb200_gemm_host: %s: %s", what, cudaGetErrorString(e))
+  // Everything is ordered after the caller's stream; B (needed by every panel) goes first.
+  TLB_CK(cudaEventRecord(hp.fork, stream), "fork");
+  TLB_CK(cudaStreamWaitEvent(hp.in, hp.fork, 0), "fork");
+  TLB_CK(cudaStreamWaitEvent(hp.out, hp.fork, 0), "fork");
+  if (bb) TLB_CK(cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, hp.in), "H2D B");
+  // Row panels of A / C (contiguous when A is [M,K]): panel p+1 is copied in while panel p is
+  // multiplied and panel p-1 is copied out, so PCIe runs in both directions under the GEMM.
+  int panels = 1;
+  if (!d->trans_a && d->k > 0) {
+    panels = d->m / 1024;
+    if (panels > kMaxPanels) panels = kMaxPanels;
+    if (panels < 1) panels = 1;
+  }
+  const int rows_per = ((d->m + panels - 1) / panels + 127) / 128 * 128;
+  int p = 0;
+  for (int r0 = 0; r0 < d->m; r0 += rows_per, ++p) {
+    const int rows = (d->m - r0 < rows_per) ? d->m - r0 : rows_per;
+    tlb200_gemm_desc pd = *d;
+    long long a_off = 0, a_bytes = ab;
+    if (panels > 1) {
+      pd.m = rows;
+      a_off = static_cast<long long>(r0) * d->lda * es;
+      a_bytes = extent_bytes(rows, d->k, d->lda, es);
+    }
+    const long long c_off = static_cast<long long>(r0) * d->ldc * ob;
+    const long long c_bytes = extent_bytes(rows, d->n, d->ldc, ob);
+    if (d->k > 0 && a_bytes)
+      TLB_CK(cudaMemcpyAsync(da + a_off, static_cast<const char*>(ha) + a_off, a_bytes, cudaMemcpyHostToDevice, hp.in), "H2D A");
+    TLB_CK(cudaEventRecord(hp.loaded[p], hp.in), "record");
+    TLB_CK(cudaStreamWaitEvent(stream, hp.loaded[p], 0), "wait");
+    if (int rc = tlb200_gemm(&pd, da + a_off, db, dc + c_off, stream_v)) return rc;
+    TLB_CK(cudaEventRecord(hp.done[p], stream), "record");
+    TLB_CK(cudaStreamWaitEvent(hp.out, hp.done[p], 0), "wait");
+    TLB_CK(cudaMemcpyAsync(static_cast<char*>(hc) + c_off, dc + c_off, c_bytes, cudaMemcpyDeviceToHost, hp.out), "D2H C");
+  }
+  TLB_CK(cudaEventRecord(hp.drained, hp.out), "record");
+  TLB_CK(cudaStreamWaitEvent(stream, hp.drained, 0), "join");
+  TLB_CK(cudaStreamSynchronize(stream), "synchronize");
+#undef TLB_CK
   return 0;
 }
 
