@@ -78,7 +78,9 @@ typedef struct tlb200_gemm_desc {
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
   int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */
-  int32_t reserved[3];   /* reserved[0] = cfg_epi_warps: 0 auto, 4 or 8 epilogue warps; rest must be 0 */
+  int32_t reserved[3];   /* [0] = cfg_epi_warps: 0 auto, 4 or 8 epilogue warps;
+                          * [1] = cfg_split_k: 0 auto, 1 off, n = at most n K slices (needs a workspace);
+                          * [2] must be 0 */
 } tlb200_gemm_desc;
 
 /* The configuration the library resolved for a descriptor (for reports/tests). */
@@ -88,6 +90,9 @@ typedef struct tlb200_gemm_plan {
   int32_t raster, epilogue, tmem_cols;
   uint32_t instr_desc;
   int32_t umma_n, epi_warps; /* N of one tcgen05.mma (block_n / accumulators per tile); epilogue warps */
+  int32_t split_k;           /* K slices per tile (1 = no split-K) */
+  int32_t reserved0;
+  int64_t workspace_bytes;   /* device scratch tlb200_gemm_ex needs for this plan (0 when split_k == 1) */
 } tlb200_gemm_plan;
 
 /* Replaces the generated `int init()` (wrapper.py:40-44): binds the CUDA
@@ -101,6 +106,18 @@ int tlb200_init(int device);
  * the CURRENT device.  A, B, C are device pointers.  Asynchronous. */
 int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                 void* stream);
+
+/* tlb200_gemm with a caller-owned device workspace (scratch memory; 256-byte
+ * aligned).  With a workspace of at least tlb200_gemm_workspace_bytes(desc)
+ * bytes the library may cut K into slices (split-K, the reference's
+ * examples/gemm_splitk idea) when the output alone has too few tiles to fill
+ * the GPU: slices are accumulated in fp32 in the workspace and summed in slice
+ * order by a second kernel.  workspace == NULL behaves exactly like
+ * tlb200_gemm.  The workspace may be reused by the next call on the same
+ * stream; calls on different streams need different workspaces. */
+int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
+int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
+                   void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Same contract through HOST buffers (pinned memory for full speed): stages B,
  * then A in row panels, to the device; runs tlb200_gemm per panel on `stream`

@@ -37,7 +37,7 @@ def test_struct_layout_matches_header(built_lib):
     # 8 int32 + 3 int64 + float + uint32 + 5 int32 + 3 reserved, natural alignment
     assert ctypes.sizeof(_abi.GemmDesc) == 96
     assert _abi.GemmDesc.lda.offset == 32 and _abi.GemmDesc.alpha.offset == 56
-    assert ctypes.sizeof(_abi.GemmPlan) == 64
+    assert ctypes.sizeof(_abi.GemmPlan) == 80 and _abi.GemmPlan.workspace_bytes.offset == 72
 
 
 def test_instr_desc_bit_exact_vs_oracle(built_lib):
@@ -85,20 +85,41 @@ def test_plan_headline_configs(built_lib):
     p8 = G.plan(8192, 8192, 8192, torch.float8_e4m3fn, torch.bfloat16)  # C3
     assert p8["block_k"] == 128 and p8["instr_desc"] == D.tcgen5_instr_desc(256, 256, 32, "float8_e4m3", "float32")
     pq = G.plan(1024, 1024, 1024, torch.float16, torch.float16, False, False, cta_group=1)  # C1 shape, NN
-    assert pq["instr_desc"] == D.tcgen5_instr_desc(128, 256, 16, "float16", "float32", True, False)
-    assert pq["block_n"] == 256 and pq["threads"] == 256  # small problems keep double-buffered 256-wide tiles
-    for m, n, k in ((16384, 14336, 4096), (16384, 4096, 14336)):  # C4
+    assert pq["instr_desc"] == D.tcgen5_instr_desc(128, pq["umma_n"], 16, "float16", "float32", True, False)
+    assert pq["block_n"] <= 256 and pq["threads"] == 256  # small problems: double-buffered tiles, enough of them
+    assert pq["tiles_m"] * pq["tiles_n"] >= 64
+    for m, n, k in ((16384, 14336, 4096), (16384, 4096, 14336)):  # C4: wide tiles only where K is deep enough
         p4 = G.plan(m, n, k)
-        assert p4["block_n"] == 512 and p4["tiles_m"] * p4["tiles_n"] == (m // 256) * (n // 512)
+        assert p4["cta_group"] == 2 and p4["block_n"] == (512 if k > 8000 else 256)
+        assert p4["tiles_m"] * p4["tiles_n"] == (m // 256) * (n // p4["block_n"])
     assert G.plan(8192, 8192, 8192, block_n=256)["stages"] == 6
 
 
 def test_plan_small_and_ragged(built_lib):
-    p = G.plan(100, 40, 72, cta_group=0)
-    assert p["cta_group"] == 1 and p["block_n"] == 64 and p["tiles_m"] == 1 and p["tiles_n"] == 1
-    assert p["epilogue"] == 2  # ldc = 40 bf16 = 80 B: TMA-store capable
-    p = G.plan(300, 200, 136)
+    for m, n, k in ((100, 40, 72), (300, 200, 136), (1, 8, 8), (129, 257, 136), (513, 1000, 264)):
+        p = G.plan(m, n, k)
+        assert p["tiles_m"] * p["block_m"] >= m and p["tiles_n"] * p["block_n"] >= n  # tiles cover the output
+        assert (p["tiles_m"] - 1) * p["block_m"] < m and (p["tiles_n"] - 1) * p["block_n"] < n
+        assert p["block_n"] % 32 == 0 and p["grid"] % p["cta_group"] == 0 and p["grid"] <= 148
+        assert p["epilogue"] == (2 if (n * 2) % 16 == 0 and p["umma_n"] % 64 == 0 else 1)
+    assert G.plan(100, 40, 72)["cta_group"] == 1  # M <= 128: a pair would leave one CTA idle
+    p = G.plan(300, 200, 136, cta_group=2, block_n=256)
     assert p["cta_group"] == 2 and p["tiles_m"] == 2 and p["tiles_n"] == 1
+
+
+def test_plan_split_k(built_lib):
+    # decode-like skinny shape: 16 tiles for 148 SMs and K = 14336 -> K is cut into slices
+    p = G.plan(128, 4096, 14336)
+    assert p["split_k"] >= 4 and p["workspace_bytes"] == p["split_k"] * 128 * 4096 * 4
+    assert p["grid"] == min(148, p["tiles_m"] * p["tiles_n"] * p["split_k"])
+    assert G.plan(128, 4096, 14336, split_k=1)["split_k"] == 1
+    assert G.plan(256, 256, 16384)["split_k"] > 1
+    assert G.plan(8192, 8192, 8192)["split_k"] == 1 and G.plan(8192, 8192, 8192)["workspace_bytes"] == 0
+    assert G.plan(128, 4096, 512)["split_k"] == 1  # K too shallow to be worth a second pass
+    d = G.make_desc(128, 4096, 14336, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 14336, 14336, 4096)
+    assert built_lib.tlb200_gemm_workspace_bytes(ctypes.byref(d)) == p["workspace_bytes"]
+    with pytest.raises(RuntimeError, match="cfg_split_k"):
+        G.plan(128, 128, 1024, split_k=65)
 
 
 def test_plan_rejects_bad_arguments(built_lib):

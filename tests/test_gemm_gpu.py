@@ -200,6 +200,47 @@ def test_tuning_knobs_do_not_change_results(cfg):
     assert bit_equal(G.gemm(a, b, **cfg), base)  # same K order per element => identical bits
 
 
+# ------------------------------------------------------------------ split-K (scratch workspace)
+@pytest.mark.parametrize("m,n,k", [(128, 4096, 14336), (256, 256, 16384), (100, 520, 4112), (384, 1024, 8192)])
+@pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.float32)])
+def test_split_k_matches_unsplit(m, n, k, dt, out):
+    assert G.plan(m, n, k, dt, out, split_k=4)["split_k"] > 1
+    a, b = operands(m, n, k, dt, kind="int")
+    c = G.gemm(a, b, out_dtype=out, alpha=0.5, relu=True, split_k=4)   # split-K through tlb200_gemm_ex
+    base = G.gemm(a, b, out_dtype=out, alpha=0.5, relu=True, split_k=1)
+    assert bit_equal(c, base)                                        # exact inputs: any summation order gives the same bits
+    assert bit_equal(c.cpu(), torch.relu(0.5 * (a.float() @ b.float().t())).to(out).cpu())
+    a, b = operands(m, n, k, dt)
+    check_tolerance(G.gemm(a, b, out_dtype=torch.bfloat16), a, b)
+    for s in (2, 5):
+        check_tolerance(G.gemm(a, b, out_dtype=torch.bfloat16, split_k=s, cta_group=1, block_n=128), a, b)
+
+
+def test_split_k_workspace_contract():
+    m, n, k = 128, 1024, 8192
+    a, b = operands(m, n, k, torch.bfloat16, kind="int")
+    c = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    lib = _abi.load()
+    d = G.make_desc(m, n, k, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, k, k, n, split_k=4)
+    need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(d))
+    assert need == 4 * 128 * 1024 * 4
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    n0 = lib.tlb200_launch_count()
+    assert lib.tlb200_gemm_ex(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), need, st) == 0
+    assert lib.tlb200_launch_count() == n0 + 2  # GEMM + reduce
+    assert torch.equal(c.float(), (a.float() @ b.float().t()).bfloat16().float())
+    # explicit split with too small a workspace is an error; with no workspace through tlb200_gemm too
+    assert lib.tlb200_gemm_ex(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), need - 256, st) != 0
+    assert "workspace" in _abi.last_error()
+    assert lib.tlb200_gemm(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), st) != 0
+    # automatic split silently runs unsplit when the workspace is too small
+    d0 = G.make_desc(m, n, k, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, k, k, n)
+    n0 = lib.tlb200_launch_count()
+    assert lib.tlb200_gemm_ex(ctypes.byref(d0), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), 1024, st) == 0
+    assert lib.tlb200_launch_count() == n0 + 1
+
+
 # ------------------------------------------------------------------ boundary behaviour
 def test_argument_errors():
     a, b = operands(64, 64, 64, torch.bfloat16)

@@ -63,10 +63,13 @@ class GemmPlan(ctypes.Structure):
         ("instr_desc", ctypes.c_uint32),
         ("umma_n", ctypes.c_int32),
         ("epi_warps", ctypes.c_int32),
+        ("split_k", ctypes.c_int32),
+        ("reserved0", ctypes.c_int32),
+        ("workspace_bytes", ctypes.c_int64),
     ]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("reserved")}
 
 
 # Every symbol include/tlb200.h declares: (restype, argtypes)
@@ -74,6 +77,9 @@ SYMBOLS = {
     "tlb200_init": (ctypes.c_int, [ctypes.c_int]),
     "tlb200_gemm": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                    ctypes.c_void_p, ctypes.c_void_p]),
+    "tlb200_gemm_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
+    "tlb200_gemm_ex": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                      ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "tlb200_gemm_host_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
     "tlb200_gemm_host": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,

@@ -52,6 +52,9 @@ struct alignas(64) GemmKernelParams {
   long long ldc;  // elements
   int m, n;
   int num_k_blocks;
+  int split_k;        // K slices per tile (1 = none).  Slice s covers K-blocks [s*kb_per_split, ...)
+  int kb_per_split;
+  int split_row_pitch; // split-K partial sums: slice s stores its tile rows at row + s*split_row_pitch of the workspace
   int tiles_m, tiles_n;  // in units of (kBlockM * cta_group) rows, block_n columns
   int raster;            // tile rows per raster group
   int block_n;           // tile width = n_sub * umma_n
@@ -153,7 +156,7 @@ __device__ __forceinline__ void store_scalar(void* c, long long idx, float v) {
 // tmem_acc = TMEM address of the accumulator (lane 0, first column).
 template <int kOut>
 __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_t tmem_acc, int q,
-                                              int lane, int row0, int col0, int cbeg, int cend,
+                                              int lane, int row0, int row_off, int col0, int cbeg, int cend,
                                               uint32_t stage_smem, int nslabs, int& slab_iter) {
   constexpr int kOB = OutTraits<kOut>::kBytes;
   constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
@@ -212,7 +215,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
       __syncwarp();
       if (lane == 0) {
-        if (row0 + q * 32 < p.m) tma_store_2d(&p.tm_c, slab, col0 + cs, row0 + q * 32);
+        if (row0 + q * 32 < p.m) tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
         tma_store_commit();
       }
       ++slab_iter;
@@ -233,7 +236,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       }
       if (row_ok) {
         const int gcol = col0 + cs;
-        const long long base = static_cast<long long>(grow) * p.ldc + gcol;
+        const long long base = static_cast<long long>(grow + row_off) * p.ldc + gcol;
         if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0) {
           uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.c) + base * kOB);
 #pragma unroll
@@ -314,12 +317,14 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int tiles_mn = p.tiles_m * p.tiles_n;
+  const int num_tiles = tiles_mn * p.split_k;  // work items: (K slice, tile)
   const int cluster_id = blockIdx.x / kCta;
   const int num_clusters = gridDim.x / kCta;
   const int nkb = p.num_k_blocks;
 
-  auto tile_coord = [&](int t, int& tm, int& tn) {
+  auto tile_coord = [&](int w, int& tm, int& tn) {
+    const int t = w % tiles_mn;
     const int group = p.raster * p.tiles_n;
     const int g = t / group;
     const int first = g * p.raster;
@@ -327,6 +332,11 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const int within = t - g * group;
     tm = first + within % rows;
     tn = within / rows;
+  };
+  // K-block range [kb0, kb1) of work item w
+  auto k_range = [&](int w, int& kb0, int& kb1) {
+    kb0 = (w / tiles_mn) * p.kb_per_split;
+    kb1 = min(nkb, kb0 + p.kb_per_split);
   };
 
   if (warp == 0) {
@@ -343,7 +353,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       tile_coord(t, tm, tn);
       const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
       const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta;
-      for (int kb = 0; kb < nkb; ++kb) {
+      int kb0, kb1;
+      k_range(t, kb0, kb1);
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
         if (elected) {
           const uint32_t full = bar_full + 8 * s;
@@ -406,11 +418,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * p.block_n;
-          for (int kb = 0; kb < nkb; ++kb) {
+          int kb0, kb1;
+          k_range(t, kb0, kb1);
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
             tc_fence_after();
             if (elected) {
-              issue_kblock(s, d_tmem, 0u, kb == 0);
+              issue_kblock(s, d_tmem, 0u, kb == kb0);
               umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
             }
             __syncwarp();
@@ -429,7 +443,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           mbar_wait(bar_tempty, aph ^ 1u, 1);
           mbar_wait(bar_tempty + 8, aph ^ 1u, 4);
           tc_fence_after();
-          for (int kb = 0; kb < nkb; ++kb) {
+          int kb0, kb1;
+          k_range(t, kb0, kb1);
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(bar_full + 8 * s, ph, 2);
             tc_fence_after();
             if (elected) {
@@ -438,12 +454,12 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
 #pragma unroll
               for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
                 const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
-                const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+                const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
                 umma_ss<kCta, kF8>(tmem_base, da, hi_b | ((b_lo + k * kadv_b) & 0x3FFFu), idesc, acc);
                 umma_ss<kCta, kF8>(tmem_base + umma_n, da, hi_b | ((b_lo + b_sub + k * kadv_b) & 0x3FFFu), idesc, acc);
               }
               umma_commit<kCta>(bar_empty + 8 * s);
-              if (kb + 1 == nkb) {
+              if (kb + 1 == kb1) {
                 umma_commit<kCta>(bar_tfull);
                 umma_commit<kCta>(bar_tfull + 8);
               }
@@ -474,6 +490,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       tile_coord(t, tm, tn);
       const int row0 = (tm * kCta + (int)cta_rank) * kBlockM;
       const int col0 = tn * p.block_n;
+      const int row_off = (t / tiles_mn) * p.split_row_pitch;
 #pragma unroll
       for (int h = 0; h < kNSub; ++h) {
         const int bi = (kNSub == 2) ? h : as;  // barrier / accumulator slot
@@ -483,11 +500,11 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
         if (row0 < p.m) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
           switch (p.out_kind) {
-            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
           }
         }
         // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.

@@ -119,9 +119,12 @@ struct Resolved {
   int b_rows_per_cta;
   int num_k_blocks;
   bool epi_tma;
+  // split-K: the main kernel writes fp32 partial tiles into a workspace, a second kernel reduces
+  int split_k, kb_per_split, m_pad;
+  long long ws_ld, ws_bytes;
 };
 
-int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r) {
+int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -147,31 +150,57 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
 
   tlb200_gemm_plan& p = r->plan;
   memset(&p, 0, sizeof(p));
-  int cg = d->cfg_cta_group;
-  if (cg == 0) cg = (d->m > kBlockM) ? 2 : 1;
-  if (cg != 1 && cg != 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", cg);
-  if (sm_count > 0 && sm_count < 2) cg = 1;
-  int bn = d->cfg_block_n;
+  if (d->cfg_cta_group < 0 || d->cfg_cta_group > 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", d->cfg_cta_group);
+  if (d->reserved[1] < 0 || d->reserved[1] > 64) return fail("tlb200: cfg_split_k must be in [0,64] (got %d)", d->reserved[1]);
   // A tile is n_sub accumulators of umma_n (<= 256) columns each.  The epilogue drains TMEM 32
   // columns at a time, so umma_n is a whole multiple of 32; an N-major B is staged in whole 128 B
   // spans per CTA.  Tiles wider than 256 columns (two accumulators sharing one A stage: 25 % less
   // L2->SM traffic) fill the 512 TMEM columns, so their accumulator is single-buffered.
-  const int n_step = r->b_mn ? r->span * cg : 32;
-  if (bn == 0) {
-    bn = 256;
-    while (bn / 2 >= d->n && bn / 2 >= n_step) bn /= 2;
-    // Large problems: 512-wide tiles (two accumulators sharing one A stage).  Less L2->SM and
-    // shared-memory traffic per flop means less power and, on a power-capped part, higher clocks;
-    // worth it once every cluster still gets several tiles (the accumulator is single-buffered,
-    // so each tile exposes one epilogue).
-    const long long wide_tiles = static_cast<long long>((d->m + kBlockM * cg - 1) / (kBlockM * cg)) * ((d->n + 511) / 512);
-    const int clusters = (sm_count > 0 ? sm_count : 148) / cg;
-    // 16-bit operands only: with 8-bit operands a tile's MMA time halves while its exposed epilogue
-    // does not, and the double-buffered 256-wide tile measures faster (profiles/r1_notes.md).
-    if (cg == 2 && r->es == 2 && bn == 256 && d->n >= 512 && wide_tiles >= 3LL * clusters && d->k >= 2048 &&
-        512 % (2 * n_step) == 0)
-      bn = 512;
+  int cg = d->cfg_cta_group, bn = d->cfg_block_n, auto_split = 1;
+  const int sms_all = sm_count > 0 ? sm_count : 148;
+  if (cg == 0 || bn == 0) {
+    // Automatic plan: minimise a small cycle model calibrated on B200 (tools/sweep.py,
+    // profiles/r1_notes.md) over {cta_group} x {block_n} x {split_k}.
+    //   K-block cycles per CTA = 2*block_n / eff(cta_group, block_n)   (512 for a 256-wide tile)
+    //   eff: how well the operand feed keeps the tensor pipe busy for that tile shape (measured at
+    //   4096^3); wide tiles get a bonus for their lower power per flop but expose one epilogue per tile.
+    struct Cand { int cg, bn; double eff; };
+    const Cand cands[] = {{2, 512, 1.07}, {2, 256, 1.0}, {1, 256, 0.85}, {2, 128, 0.70}, {1, 128, 0.73},
+                          {1, 64, 0.40}, {2, 64, 0.37}, {1, 32, 0.20}};
+    const int nkb = (d->k + r->span - 1) / r->span;
+    double best = 1e300;
+    int best_cg = 0, best_bn = 0, best_split = 1;
+    for (const Cand& c : cands) {
+      if (d->cfg_cta_group && c.cg != d->cfg_cta_group) continue;
+      if (d->cfg_block_n && c.bn != d->cfg_block_n) continue;
+      if (c.cg == 2 && (d->m <= kBlockM || sms_all < 2)) continue;
+      if (c.bn == 512 && (r->es != 2 || d->n < 512)) continue;  // 8-bit operands: double-buffered tiles measure faster
+      if (c.bn > 32 && c.bn / 2 >= d->n && c.bn != d->cfg_block_n) continue;  // tile twice wider than the matrix
+      const int step = r->b_mn ? r->span * c.cg : 32;
+      if ((c.bn > 256 ? c.bn / 2 : c.bn) % step) continue;
+      if (d->cfg_epilogue == 2 && (c.bn > 256 ? c.bn / 2 : c.bn) % (128 / r->ob)) continue;  // TMA-store slabs are 128 B wide
+      const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) * ((d->n + c.bn - 1) / c.bn);
+      const long long clusters = sms_all / c.cg;
+      for (int split = 1; split <= 32; split *= 2) {
+        if (split > 1 && (!allow_split || d->reserved[1] == 1 || nkb / split < 8 || tiles * split > 2 * clusters)) break;
+        if (d->reserved[1] > 1 && split > d->reserved[1]) break;
+        const long long items = tiles * split;
+        const long long waves = (items + clusters - 1) / clusters;
+        const double kb = static_cast<double>((nkb + split - 1) / split);
+        double tile = kb * 2.0 * c.bn / c.eff + (c.bn > 256 ? 8000.0 : 0.0);
+        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn);
+        if (split > 1) total += 5000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
+        if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; }
+      }
+    }
+    if (best_cg == 0) {  // nothing matched the constraints: fall back to the smallest legal tile
+      best_cg = d->cfg_cta_group ? d->cfg_cta_group : 1;
+      best_bn = d->cfg_block_n ? d->cfg_block_n : (r->b_mn ? r->span * best_cg : 32);
+    }
+    cg = best_cg; bn = best_bn; auto_split = best_split;
   }
+  if (sms_all < 2) cg = 1;
+  const int n_step = r->b_mn ? r->span * cg : 32;
   r->n_sub = bn > 256 ? 2 : 1;
   r->umma_n = bn / r->n_sub;
   if (bn < n_step || bn > 512 || bn % r->n_sub || r->umma_n % n_step)
@@ -204,7 +233,31 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   const long long tiles = static_cast<long long>(p.tiles_m) * p.tiles_n;
   const int sms = sm_count > 0 ? sm_count : 148;
   long long clusters = sms / cg;
-  if (clusters > tiles) clusters = tiles;
+  // Split-K (examples/gemm_splitk in the reference): when the output has too few tiles to occupy the
+  // machine and K is deep, K is cut into slices computed by different clusters into an fp32
+  // workspace and summed by a second kernel in slice order (deterministic).
+  int split = d->reserved[1];  // cfg_split_k: 0 auto, 1 off, n = n slices (fewer if K is short)
+  if (split == 0) {
+    split = auto_split;
+    if (split == 1 && allow_split && (d->cfg_cta_group != 0 && d->cfg_block_n != 0) && tiles * 2 <= clusters && r->num_k_blocks >= 16) {
+      long long s2 = clusters / tiles;  // fully explicit tile: simple fill rule
+      if (s2 > r->num_k_blocks / 8) s2 = r->num_k_blocks / 8;
+      if (s2 > 32) s2 = 32;
+      if (s2 >= 2) split = static_cast<int>(s2);
+    }
+  } else if (split > 1 && (d->cfg_cta_group == 0 || d->cfg_block_n == 0)) {
+    split = auto_split > 1 ? auto_split : split;
+  }
+  if (split > r->num_k_blocks) split = r->num_k_blocks > 0 ? r->num_k_blocks : 1;
+  r->kb_per_split = split > 1 ? (r->num_k_blocks + split - 1) / split : (r->num_k_blocks > 0 ? r->num_k_blocks : 1);
+  r->split_k = split > 1 ? (r->num_k_blocks + r->kb_per_split - 1) / r->kb_per_split : 1;
+  r->m_pad = p.tiles_m * p.block_m;
+  r->ws_ld = (static_cast<long long>(d->n) + 3) / 4 * 4;
+  r->ws_bytes = r->split_k > 1 ? static_cast<long long>(r->split_k) * r->m_pad * r->ws_ld * 4 : 0;
+  p.split_k = r->split_k;
+  p.workspace_bytes = r->ws_bytes;
+  const long long work_items = tiles * r->split_k;
+  if (clusters > work_items) clusters = work_items;
   if (clusters < 1) clusters = 1;
   p.grid = static_cast<int>(clusters) * cg;
   p.threads = 128 + 32 * r->epi_warps;
@@ -265,6 +318,48 @@ __global__ void fill_zero_kernel(void* c, long long ldc, int m, int n) {
     const long long r = i / n, col = i - r * n;
     store_scalar<kOut>(c, r * ldc + col, 0.f);
   }
+}
+
+// Split-K second pass: C[m,n] = cast(relu?(alpha * sum_s ws[s*m_pad + m, n])), slices summed in order.
+template <int kOut>
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_ld, int m_pad, int split_k, void* c,
+                                     long long ldc, int m, int n, float alpha, int relu) {
+  const int n4 = (n + 3) / 4;
+  const long long total = static_cast<long long>(m) * n4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / n4;
+    const int col = static_cast<int>(i - row * n4) * 4;
+    float4 acc = *reinterpret_cast<const float4*>(ws + row * ws_ld + col);  // ws_ld is a multiple of 4
+    for (int s = 1; s < split_k; ++s) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + (static_cast<long long>(s) * m_pad + row) * ws_ld + col);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    float o[4] = {acc.x * alpha, acc.y * alpha, acc.z * alpha, acc.w * alpha};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (relu) o[j] = fmaxf(o[j], 0.f);
+      if (col + j < n) store_scalar<kOut>(c, row * ldc + col + j, o[j]);
+    }
+  }
+}
+
+int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_k, void* c, long long ldc, int m, int n,
+                         float alpha, bool relu, int out_kind, cudaStream_t stream) {
+  const long long total = static_cast<long long>(m) * ((n + 3) / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  const int g = static_cast<int>(blocks), rl = relu ? 1 : 0;
+  switch (out_kind) {
+    case kOutF16: splitk_reduce_kernel<kOutF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+    case kOutBF16: splitk_reduce_kernel<kOutBF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+    case kOutF32: splitk_reduce_kernel<kOutF32><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+    case kOutE4M3: splitk_reduce_kernel<kOutE4M3><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+    default: splitk_reduce_kernel<kOutE5M2><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
+  return 0;
 }
 
 typedef void (*GemmKernelFn)(const GemmKernelParams);
@@ -380,7 +475,7 @@ uint64_t tlb200_smem_desc(uint32_t smem_addr, int lbo16, int sbo16, int base_off
 
 int tlb200_gemm_plan_query(const tlb200_gemm_desc* desc, int sm_count, tlb200_gemm_plan* out) {
   Resolved r;
-  int rc = resolve(desc, sm_count, nullptr, &r);
+  int rc = resolve(desc, sm_count, nullptr, &r, true);  // the plan tlb200_gemm_ex follows when given a workspace
   if (rc) return rc;
   if (out) *out = r.plan;
   return 0;
@@ -444,12 +539,24 @@ int tlb200_init(int device) {
   return rc;
 }
 
-int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
+static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
+                     void* stream_v) {
   g_err[0] = 0;
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
-  if (int rc = resolve(d, g_sm_count[dev], c, &r)) return rc;
+  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr)) return rc;
+  if (r.split_k > 1) {
+    if (!ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
+    if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
+    if (ws_bytes < r.ws_bytes) {
+      if (d->reserved[1] > 1) return fail("tlb200_gemm_ex: split-K x%d needs a %lld-byte workspace, got %lld", r.split_k, r.ws_bytes, (long long)ws_bytes);
+      tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
+      d1.reserved[1] = 1;
+      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, false)) return rc;
+    }
+  }
+  const bool split = r.split_k > 1;
   if (d->m == 0 || d->n == 0) return 0;
   if (!c || (d->k > 0 && (!a || !b))) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
   if (d->k > 0 && ((reinterpret_cast<uintptr_t>(a) % 16) || (reinterpret_cast<uintptr_t>(b) % 16)))
@@ -491,11 +598,21 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
     if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->k, d->n, d->ldb, r.span, bk, "B[K,N]")) return rc;
     kp.b_boxes = r.b_rows_per_cta / r.span; kp.b_box_bytes = bk * kStageRowBytes;
   }
-  if (r.epi_tma) {
+  // Split-K: the GEMM kernel stores fp32 partial tiles into the workspace, slice s at rows
+  // [s*m_pad, s*m_pad + M) of a [split_k*m_pad, ws_ld] matrix (m_pad = whole tiles, so a slice's
+  // out-of-range tile rows stay inside its own region).
+  const bool ws_tma = (r.umma_n / (r.epi_warps / 4)) % 32 == 0;
+  if (split) {
+    if (ws_tma)
+      if (int rc = encode_2d(&kp.tm_c, TLB200_FLOAT32, ws, static_cast<long long>(r.split_k) * r.m_pad, d->n, r.ws_ld, 32, 32, "workspace")) return rc;
+  } else if (r.epi_tma) {
     if (int rc = encode_2d(&kp.tm_c, d->c_dtype, c, d->m, d->n, d->ldc, 128 / r.ob, 32, "C[M,N]")) return rc;
   }
-  kp.c = c;
-  kp.ldc = d->ldc;
+  kp.c = split ? ws : c;
+  kp.ldc = split ? r.ws_ld : d->ldc;
+  kp.split_k = r.split_k;
+  kp.kb_per_split = r.kb_per_split;
+  kp.split_row_pitch = split ? r.m_pad : 0;
   kp.m = d->m; kp.n = d->n;
   kp.num_k_blocks = r.num_k_blocks;
   kp.tiles_m = pl.tiles_m; kp.tiles_n = pl.tiles_n;
@@ -523,11 +640,11 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
   kp.desc_lbo_b = (r.b_mn ? static_cast<uint32_t>(kp.b_box_bytes >> 4) : 1u) << 16;
   kp.kadv_a = r.a_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
   kp.kadv_b = r.b_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
-  kp.out_kind = out_kind;
+  kp.out_kind = split ? static_cast<int>(kOutF32) : out_kind;
   kp.is_f8 = r.es == 1;
-  kp.epi_tma = r.epi_tma;
-  kp.relu = (d->epilogue & TLB200_EPI_RELU) ? 1 : 0;
-  kp.alpha = d->alpha;
+  kp.epi_tma = split ? ws_tma : r.epi_tma;
+  kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
+  kp.alpha = split ? 1.0f : d->alpha;
 
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -547,7 +664,32 @@ int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);
   g_launches++;
+  if (split) {
+    if (int rc = launch_splitk_reduce(static_cast<const float*>(ws), r.ws_ld, r.m_pad, r.split_k, c, d->ldc, d->m, d->n, d->alpha,
+                                      (d->epilogue & TLB200_EPI_RELU) != 0, out_kind, stream))
+      return rc;
+    g_launches++;
+  }
   return 0;
+}
+
+int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
+  return gemm_impl(d, a, b, c, nullptr, 0, stream_v);
+}
+
+int tlb200_gemm_ex(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
+                   void* stream_v) {
+  if (ws && ws_bytes < 0) return fail("tlb200_gemm_ex: negative workspace size");
+  return gemm_impl(d, a, b, c, ws, ws_bytes, stream_v);
+}
+
+int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* d) {
+  int dev = -1;
+  cudaGetDevice(&dev);
+  const int sms = (dev >= 0 && dev < kMaxDevices && g_sm_count[dev] > 0) ? g_sm_count[dev] : 148;
+  Resolved r;
+  if (resolve(d, sms, nullptr, &r, true)) return -1;
+  return r.ws_bytes;
 }
 
 static long long extent_bytes(long long rows, long long cols, long long ld, int eb) {

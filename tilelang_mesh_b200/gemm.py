@@ -26,6 +26,18 @@ _TORCH2TLB = {
 _AB_DTYPES = (torch.float16, torch.bfloat16, torch.float8_e4m3fn, torch.float8_e5m2)
 
 _inited_devices = set()
+_workspaces = {}  # (device index, stream handle) -> torch.uint8 scratch for split-K partial sums
+
+
+def _workspace(dev: int, stream: int, nbytes: int) -> torch.Tensor:
+    """Scratch memory is owned by the caller of the C ABI — here torch, one growing buffer per
+    (device, stream) so that calls on different streams never share it."""
+    key = (dev, stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=torch.device("cuda", dev))
+        _workspaces[key] = ws
+    return ws
 
 
 def _ensure_init(device_index: int):
@@ -46,7 +58,7 @@ def _row_pitch(t: torch.Tensor, name: str) -> int:
 
 
 def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha=1.0, relu=False,
-              cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0) -> _abi.GemmDesc:
+              cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0, split_k=0) -> _abi.GemmDesc:
     d = _abi.GemmDesc()
     d.abi_version = _abi.ABI_VERSION
     d.m, d.n, d.k = int(m), int(n), int(k)
@@ -58,6 +70,7 @@ def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha
     d.cfg_cta_group, d.cfg_block_n, d.cfg_stages = int(cta_group), int(block_n), int(stages)
     d.cfg_raster, d.cfg_epilogue = int(raster), int(epilogue)
     d.reserved[0] = int(epi_warps)
+    d.reserved[1] = int(split_k)
     return d
 
 
@@ -103,7 +116,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
     lib = _abi.load()
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
-        rc = lib.tlb200_gemm(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), stream)
+        need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc))
+        if need > 0:  # the plan wants split-K: hand it scratch memory
+            ws = _workspace(dev, stream, need)
+            rc = lib.tlb200_gemm_ex(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(),
+                                    ws.numel(), stream)
+        else:
+            rc = lib.tlb200_gemm(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), stream)
     _abi.check(rc, "tlb200_gemm")
     return c
 
