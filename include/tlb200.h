@@ -119,6 +119,40 @@ int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                    void* workspace, int64_t workspace_bytes, void* stream);
 
+/* No counterpart in the reference: an allocation-free form of tlb200_gemm_ex.
+ *
+ * Who needs it: callers that are handed tensor pointers and a stream and nothing
+ * else, and are not allowed to obtain device memory themselves.  The typical
+ * case is a wrapper that must keep the reference's generated signature
+ * `call(A, B, C, stream)` (seam 2): that signature has no
+ * workspace argument, and the host framework above it owns every byte of
+ * device memory through its own pool, so a cudaMalloc from inside the call is
+ * either forbidden by policy or would bypass the pool's accounting.  Latency-
+ * critical serving loops that freeze their memory layout after start-up are in
+ * the same position.
+ *
+ * What it does: the split-K partial sums go into a scratch array that is part
+ * of the library image itself (TLB200_STATIC_SCRATCH_BYTES, reserved on every
+ * GPU that loads the library, for the lifetime of the process).  The call makes
+ * no cudaMalloc / cudaFree and uses no allocating library routine.  Problems
+ * whose plan needs no split-K run exactly as tlb200_gemm does.  A plan whose
+ * partial sums do not fit the static scratch is REJECTED with an error that
+ * names both sizes (set cfg_split_k lower, or use tlb200_gemm_ex with your own
+ * workspace); nothing is silently truncated.
+ *
+ * Rules of use:
+ *  - The first call on each device looks up the device address of the scratch
+ *    array (a one-time set-up step on the then-current device).  Make that first
+ *    call during start-up, before any stream capture begins.
+ *  - All calls on one device share the one array and it keeps whatever the
+ *    previous call left in it.  Nothing in it has to start at zero: every slice
+ *    overwrites its whole partial tile before the reduction reads it.  Two calls
+ *    that can overlap on the GPU (different streams, no ordering between them)
+ *    race on the array - order them, or give one of them tlb200_gemm_ex. */
+#define TLB200_STATIC_SCRATCH_BYTES (32u << 20)
+int tlb200_gemm_static_scratch(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
+                               void* stream);
+
 /* Same contract through HOST buffers (pinned memory for full speed): stages B,
  * then A in row panels, to the device; runs tlb200_gemm per panel on `stream`
  * while the next panel is copied in and the previous panel's C is copied out

@@ -19,6 +19,7 @@ ABI_VERSION = 1
 # tlb200_dtype
 FLOAT16, BFLOAT16, FLOAT8_E4M3, FLOAT8_E5M2, FLOAT32 = 0, 1, 2, 3, 4
 EPI_NONE, EPI_RELU = 0, 1
+STATIC_SCRATCH_BYTES = 32 << 20  # TLB200_STATIC_SCRATCH_BYTES
 
 
 class GemmDesc(ctypes.Structure):
@@ -80,6 +81,8 @@ SYMBOLS = {
     "tlb200_gemm_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
     "tlb200_gemm_ex": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                       ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "tlb200_gemm_static_scratch": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
+                                                  ctypes.c_void_p, ctypes.c_void_p]),
     "tlb200_gemm_host_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
     "tlb200_gemm_host": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,

@@ -683,6 +683,41 @@ int tlb200_gemm_ex(const tlb200_gemm_desc* d, const void* a, const void* b, void
   return gemm_impl(d, a, b, c, ws, ws_bytes, stream_v);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Allocation-free split-K: the partial sums live in an array that is part of this library's device
+// image.  `g_static_scratch` below is only a host-side handle for that array: it is not a device
+// address and must never be handed to a kernel.  The real address differs per GPU and is obtained
+// once per device with cudaGetSymbolAddress while that device is current.
+static __device__ __align__(256) unsigned char g_static_scratch[TLB200_STATIC_SCRATCH_BYTES];
+static void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_static_scratch_mu;
+
+int tlb200_gemm_static_scratch(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
+  g_err[0] = 0;
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[dev]) {  // first call on this device: resolve the array's device address
+      void* p = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+      if (e != cudaSuccess || !p)
+        return fail("tlb200_gemm_static_scratch: cannot resolve the static scratch array on device %d: %s", dev,
+                    cudaGetErrorString(e));
+      g_static_scratch_ptr[dev] = p;
+    }
+    scratch = g_static_scratch_ptr[dev];
+  }
+  Resolved r;
+  if (int rc = resolve(d, g_sm_count[dev], c, &r, true)) return rc;
+  if (r.ws_bytes > static_cast<long long>(TLB200_STATIC_SCRATCH_BYTES))
+    return fail("tlb200_gemm_static_scratch: this plan (split-K x%d of %dx%d) needs %lld bytes of scratch but the static "
+                "scratch array holds %u; lower cfg_split_k or call tlb200_gemm_ex with a workspace of your own",
+                r.split_k, d->m, d->n, r.ws_bytes, static_cast<unsigned>(TLB200_STATIC_SCRATCH_BYTES));
+  return gemm_impl(d, a, b, c, scratch, static_cast<int64_t>(TLB200_STATIC_SCRATCH_BYTES), stream_v);
+}
+
 int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* d) {
   int dev = -1;
   cudaGetDevice(&dev);
