@@ -119,6 +119,19 @@ int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                    void* workspace, int64_t workspace_bytes, void* stream);
 
+/* tlb200_gemm whose C tiles are stored into n_c matrices at once (n_c <= 8):
+ * c_list[0] is the local C, the others are the same window of C in PEER GPUs'
+ * memory (addresses mapped into this process, e.g. CUDA IPC / symmetric
+ * memory).  Every epilogue slab is written by TMA to all destinations, so an
+ * N-sharded contraction materialises the full C on every GPU over NVLink while
+ * the tensor pipe keeps working - the GEMM and its all-gather are ONE kernel
+ * (the reference has no multi-GPU path; this serves north_star's optional
+ * N-sharded variant).  All destinations share ldc, shape and dtype.  The
+ * caller synchronises the GPUs afterwards (stream completion on every rank +
+ * a cross-rank barrier) before reading. */
+int tlb200_gemm_bcast(const tlb200_gemm_desc* desc, const void* a, const void* b, void* const* c_list,
+                      int n_c, void* stream);
+
 /* No counterpart in the reference: an allocation-free form of tlb200_gemm_ex.
  *
  * Who needs it: callers that are handed tensor pointers and a stream and nothing

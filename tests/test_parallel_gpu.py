@@ -41,6 +41,12 @@ def _worker(rank, world, port, q):
         full_n = sn.run(A, B[sn.lo:sn.hi].contiguous())
         torch.cuda.synchronize()
         R.assert_allclose(full_n, want, 1e-2, 1e-2)
+        # fused: the epilogue stores into every rank's C over NVLink (no NCCL on the data path)
+        sf = ShardedGemm(M, N, K, mode="N", fused=True)
+        for _ in range(2):
+            full_f = sf.run(A, B[sf.lo:sf.hi].contiguous())
+            torch.cuda.synchronize()
+            ok = ok and torch.equal(full_f.view(torch.int16), full_n.view(torch.int16))
         # every rank holds the same gathered result
         ref = full_n.clone()
         dist.broadcast(ref, src=0)

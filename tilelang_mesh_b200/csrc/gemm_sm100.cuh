@@ -40,6 +40,7 @@ constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple
 constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
 constexpr int kEpiSlabs = 8;               // slabs per CTA: 4 warps x 2 or 8 warps x 1 (32 KiB)
 constexpr int kMaxStages = 12;
+constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
 
 enum OutKind : int { kOutF16 = 0, kOutBF16 = 1, kOutE4M3 = 2, kOutE5M2 = 3, kOutF32 = 4 };
@@ -48,6 +49,9 @@ struct alignas(64) GemmKernelParams {
   CUtensorMap tm_a;  // operand A boxes
   CUtensorMap tm_b;  // operand B boxes
   CUtensorMap tm_c;  // C store boxes (32 rows x 128 B), valid iff epi_tma
+  CUtensorMap tm_c_peer[kMaxPeerDst];  // additional destinations of every C store (peer GPUs' copies of C)
+  void* c_peer[kMaxPeerDst];
+  int n_peer;        // number of additional destinations (0 = single-GPU store)
   void* c;
   long long ldc;  // elements
   int m, n;
@@ -215,7 +219,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
       __syncwarp();
       if (lane == 0) {
-        if (row0 + q * 32 < p.m) tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
+        if (row0 + q * 32 < p.m) {
+          tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
+          // fused all-gather: the same slab goes straight into every peer GPU's C over NVLink
+          for (int g = 0; g < p.n_peer; ++g) tma_store_2d(&p.tm_c_peer[g], slab, col0 + cs, row_off + row0 + q * 32);
+        }
         tma_store_commit();
       }
       ++slab_iter;
@@ -237,14 +245,17 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       if (row_ok) {
         const int gcol = col0 + cs;
         const long long base = static_cast<long long>(grow + row_off) * p.ldc + gcol;
-        if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0) {
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.c) + base * kOB);
+        for (int g = -1; g < p.n_peer; ++g) {  // g == -1: the local C; others: peer GPUs' copies
+          void* cdst = g < 0 ? p.c : p.c_peer[g];
+          if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0 && (reinterpret_cast<uintptr_t>(cdst) % 16) == 0) {
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(cdst) + base * kOB);
 #pragma unroll
-          for (int pk = 0; pk < kPacketsPerLd; ++pk) dst[pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
-        } else {
+            for (int pk = 0; pk < kPacketsPerLd; ++pk) dst[pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
+          } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (gcol + i < p.n) store_scalar<kOut>(p.c, base + i, v[i]);
+            for (int i = 0; i < 32; ++i)
+              if (gcol + i < p.n) store_scalar<kOut>(cdst, base + i, v[i]);
+          }
         }
       }
       __syncwarp();  // tcgen05.ld is .sync.aligned: re-converge after the predicated stores
@@ -293,7 +304,10 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     if (elect_one()) {
       tma_prefetch_desc(&p.tm_a);
       tma_prefetch_desc(&p.tm_b);
-      if (p.epi_tma) tma_prefetch_desc(&p.tm_c);
+      if (p.epi_tma) {
+        tma_prefetch_desc(&p.tm_c);
+        for (int g = 0; g < p.n_peer; ++g) tma_prefetch_desc(&p.tm_c_peer[g]);
+      }
     }
   } else if (warp == 1) {
     if (elect_one()) {

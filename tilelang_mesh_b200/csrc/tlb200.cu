@@ -540,7 +540,7 @@ int tlb200_init(int device) {
 }
 
 static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
-                     void* stream_v) {
+                     void* stream_v, void* const* peers = nullptr, int n_peer = 0) {
   g_err[0] = 0;
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
@@ -607,7 +607,11 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
       if (int rc = encode_2d(&kp.tm_c, TLB200_FLOAT32, ws, static_cast<long long>(r.split_k) * r.m_pad, d->n, r.ws_ld, 32, 32, "workspace")) return rc;
   } else if (r.epi_tma) {
     if (int rc = encode_2d(&kp.tm_c, d->c_dtype, c, d->m, d->n, d->ldc, 128 / r.ob, 32, "C[M,N]")) return rc;
+    for (int g = 0; g < n_peer; ++g)
+      if (int rc = encode_2d(&kp.tm_c_peer[g], d->c_dtype, peers[g], d->m, d->n, d->ldc, 128 / r.ob, 32, "peer C[M,N]")) return rc;
   }
+  kp.n_peer = n_peer;
+  for (int g = 0; g < n_peer; ++g) kp.c_peer[g] = peers[g];
   kp.c = split ? ws : c;
   kp.ldc = split ? r.ws_ld : d->ldc;
   kp.split_k = r.split_k;
@@ -675,6 +679,18 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
 
 int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
   return gemm_impl(d, a, b, c, nullptr, 0, stream_v);
+}
+
+int tlb200_gemm_bcast(const tlb200_gemm_desc* d, const void* a, const void* b, void* const* c_list, int n_c, void* stream_v) {
+  if (!c_list || n_c < 1 || n_c > 1 + kMaxPeerDst) return fail("tlb200_gemm_bcast: n_c must be in [1,%d] (got %d)", 1 + kMaxPeerDst, n_c);
+  for (int g = 0; g < n_c; ++g) {
+    if (!c_list[g]) return fail("tlb200_gemm_bcast: destination %d is null", g);
+    // one epilogue mode serves every destination: they must agree on 16-byte alignment
+    if ((reinterpret_cast<uintptr_t>(c_list[g]) % 16) != (reinterpret_cast<uintptr_t>(c_list[0]) % 16))
+      return fail("tlb200_gemm_bcast: destination %d is aligned differently from destination 0", g);
+  }
+  if (d && d->reserved[1] > 1) return fail("tlb200_gemm_bcast: split-K cannot be combined with multiple destinations");
+  return gemm_impl(d, a, b, c_list[0], nullptr, 0, stream_v, c_list + 1, n_c - 1);
 }
 
 int tlb200_gemm_ex(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,

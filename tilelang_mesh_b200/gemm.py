@@ -127,6 +127,28 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
     return c
 
 
+def gemm_bcast(a: torch.Tensor, b: torch.Tensor, dst_ptrs, ldc: int, c_dtype: torch.dtype, *, alpha: float = 1.0,
+               relu: bool = False, **cfg) -> None:
+    """C = A[M,K] @ B[N,K]^T stored into SEVERAL matrices at once (tlb200_gemm_bcast): ``dst_ptrs[0]`` is the
+    local destination, the rest are the same window of C in peer GPUs' memory (raw addresses valid in this
+    process, e.g. from torch symmetric memory).  Row pitch ``ldc`` (elements) and dtype are shared."""
+    if not (a.is_cuda and b.is_cuda) or a.dtype != b.dtype or a.dtype not in _AB_DTYPES:
+        raise ValueError("gemm_bcast: A and B must be CUDA tensors of the same supported dtype")
+    if a.shape[1] != b.shape[1]:
+        raise ValueError(f"gemm_bcast: T.gemm K shape check failed: K_A = {a.shape[1]}, K_B = {b.shape[1]}")
+    m, k, n = a.shape[0], a.shape[1], b.shape[0]
+    dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    desc = make_desc(m, n, k, _TORCH2TLB[a.dtype], _TORCH2TLB[c_dtype], False, True, _row_pitch(a, "A"), _row_pitch(b, "B"),
+                     ldc, alpha, relu, **cfg)
+    arr = (ctypes.c_void_p * len(dst_ptrs))(*[int(p) for p in dst_ptrs])
+    lib = _abi.load()
+    with torch.cuda.device(dev):
+        rc = lib.tlb200_gemm_bcast(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), arr, len(dst_ptrs),
+                                   torch.cuda.current_stream(dev).cuda_stream)
+    _abi.check(rc, "tlb200_gemm_bcast")
+
+
 def plan(m, n, k, ab_dtype=torch.bfloat16, c_dtype=torch.bfloat16, trans_a=False, trans_b=True,
          sm_count=148, **cfg) -> dict:
     """Resolve the tile plan for a problem without touching a GPU."""

@@ -40,7 +40,7 @@ class ShardedGemm:
     """C[M,N] = A[M,K] @ B[N,K]^T sharded over the ranks of `group`."""
 
     def __init__(self, M: int, N: int, K: int, mode: str = "M", group=None, panel_rows: int = 8192,
-                 local_gemm: Optional[Callable] = None):
+                 local_gemm: Optional[Callable] = None, fused: bool = False, dtype: torch.dtype = torch.bfloat16):
         if mode not in ("M", "N"):
             raise ValueError("mode must be 'M' (row-sharded A/C, no collective) or 'N' (row-sharded B + all-gather)")
         self.M, self.N, self.K, self.mode, self.group = M, N, K, mode, group
@@ -55,6 +55,18 @@ class ShardedGemm:
         self.lo, self.hi = shard_bounds(dim, self.world, self.rank)
         if mode == "N" and N % self.world:
             raise ValueError(f"mode 'N' needs N ({N}) divisible by the world size ({self.world}) for the all-gather")
+        # fused = the GEMM kernel's epilogue stores every C tile into all ranks' copies of C over NVLink
+        # (tlb200_gemm_bcast): compute and all-gather are one kernel, no NCCL call on the data path.
+        self.fused = bool(fused) and mode == "N" and self.world > 1
+        self._symm_out = self._symm_hdl = None
+        if self.fused:
+            if self.world > 8:
+                raise ValueError("fused all-gather supports at most 8 ranks (one NVSwitch domain)")
+            import torch.distributed._symmetric_memory as symm_mem
+            dev = torch.device("cuda", torch.cuda.current_device())
+            self._symm_out = symm_mem.empty((M, N), dtype=dtype, device=dev)
+            grp = group if group is not None else dist.group.WORLD
+            self._symm_hdl = symm_mem.rendezvous(self._symm_out, grp)
 
     # shapes this rank must hold
     def local_shapes(self):
@@ -83,7 +95,22 @@ class ShardedGemm:
             return full[:self.M]
         return self._run_n_sharded(a, b)
 
+    def _run_n_fused(self, a, b):
+        from . import gemm as G
+        out, hdl = self._symm_out, self._symm_hdl
+        if a.dtype != out.dtype:
+            raise ValueError(f"fused all-gather was set up for {out.dtype}, got {a.dtype}")
+        off = self.lo * out.element_size()
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        order = [self.rank] + [g for g in range(self.world) if g != self.rank]  # destination 0 = local copy
+        hdl.barrier(channel=0)  # nobody may still be reading the previous result
+        G.gemm_bcast(a, b, [ptrs[g] + off for g in order], ldc=self.N, c_dtype=out.dtype)
+        hdl.barrier(channel=1)  # every rank's stores have landed everywhere
+        return out
+
     def _run_n_sharded(self, a, b):
+        if self.fused:
+            return self._run_n_fused(a, b)
         G, ncol = self.world, self.hi - self.lo
         out = torch.empty((self.M, self.N), dtype=a.dtype, device=a.device)
         if G == 1:
