@@ -81,6 +81,7 @@ struct alignas(64) GemmKernelParams {
   int is_f8;
   int epi_tma;
   int relu;
+  int l2_policy;
   float alpha;
 };
 
@@ -220,7 +221,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       __syncwarp();
       if (lane == 0) {
         if (row0 + q * 32 < p.m) {
-          tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
+          // C is write-once: evict_first keeps the operands in L2
+          if (p.l2_policy != 1) tma_store_2d_hint(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
+          else tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
           // fused all-gather: the same slab goes straight into every peer GPU's C over NVLink
           for (int g = 0; g < p.n_peer; ++g) tma_store_2d(&p.tm_c_peer[g], slab, col0 + cs, row_off + row0 + q * 32);
         }
@@ -356,7 +359,10 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   if (warp == 0) {
     // ===================================================== TMA producer (one elected lane issues)
     const bool elected = elect_one();
-    const uint64_t pol = policy_evict_normal();
+    // Operands are re-read by other tiles of the raster group: keep them in L2 (evict_last measured +1.5 % bf16,
+    // +3 % fp8 sustained over evict_normal; profiles/r1_notes.md).  l2_policy 1 restores evict_normal.
+    const uint64_t pol_a = p.l2_policy == 1 ? policy_evict_normal() : policy_evict_last();
+    const uint64_t pol_b = pol_a;
     const int kspan = p.k_elems_per_block;
     const int a_rows_per_box = p.a_box_bytes / kStageRowBytes;
     const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
@@ -382,8 +388,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           for (int j = 0; j < p.a_boxes; ++j) {
             const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
             const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
-            if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
-            else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
+            if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
+            else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
           }
           // accumulator h of the tile covers tile columns [h*umma_n, (h+1)*umma_n)
 #pragma unroll
@@ -393,8 +399,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
               const int c0 = p.b_mn_major ? rb + j * kspan : k0;
               const int c1 = p.b_mn_major ? k0 : rb + j * b_rows_per_box;
               const uint32_t dst = dst_b + h * b_sub_bytes + j * p.b_box_bytes;
-              if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol);
-              else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol);
+              if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol_b);
+              else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol_b);
             }
           }
         }

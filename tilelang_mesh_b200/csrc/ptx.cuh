@@ -146,6 +146,13 @@ __device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t src, int
                "r"(src), "r"(c0), "r"(c1)
                : "memory");
 }
+// Same with an L2 eviction-priority hint (C is written once and never re-read by this kernel).
+__device__ __forceinline__ void tma_store_2d_hint(const void* desc, uint32_t src, int c0, int c1, uint64_t policy) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(
+                   reinterpret_cast<uint64_t>(desc)),
+               "r"(src), "r"(c0), "r"(c1), "l"(policy)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
@@ -161,6 +168,11 @@ __device__ __forceinline__ void tma_store_wait_all() {
 __device__ __forceinline__ uint64_t policy_evict_last() {
   uint64_t p;
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
   return p;
 }
 __device__ __forceinline__ uint64_t policy_evict_normal() {

@@ -46,9 +46,7 @@ def run(name, fn):
           sm_mhz_med_2nd_half=clk[len(clk)//2] if clk else None, power_w_med=round(pw[len(pw)//2],1) if pw else None)), flush=True)
     time.sleep(1.5)
 
-variants = [("auto", {}), ("w512_r16", dict(cta_group=2, block_n=512, raster=16)), ("w512_r8", dict(cta_group=2, block_n=512, raster=8)),
-            ("w512_r32", dict(cta_group=2, block_n=512, raster=32)), ("w512_e4", dict(cta_group=2, block_n=512, epi_warps=4)),
-            ("w512_s3", dict(cta_group=2, block_n=512, stages=3)), ("n256", dict(cta_group=2, block_n=256)), ("n256_r16", dict(cta_group=2, block_n=256, raster=16))]
+variants = [("auto", {}), ("normal", dict(l2_policy=1)), ("C_evict_first", dict(l2_policy=2)), ("auto_again", {})]
 extra = [v for v in sys.argv[3:]]
 if dt == "bf16":
     run("cublas", lambda: torch.matmul(a, b.t(), out=c))
