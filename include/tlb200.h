@@ -108,13 +108,18 @@ int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void
                 void* stream);
 
 /* tlb200_gemm with a caller-owned device workspace (scratch memory; 256-byte
- * aligned).  With a workspace of at least tlb200_gemm_workspace_bytes(desc)
- * bytes the library may cut K into slices (split-K, the reference's
- * examples/gemm_splitk idea) when the output alone has too few tiles to fill
- * the GPU: slices are accumulated in fp32 in the workspace and summed in slice
- * order by a second kernel.  workspace == NULL behaves exactly like
- * tlb200_gemm.  The workspace may be reused by the next call on the same
- * stream; calls on different streams need different workspaces. */
+ * aligned) of at least tlb200_gemm_workspace_bytes(desc) bytes.  Two things
+ * use it:
+ *  - split-K (the reference's examples/gemm_splitk idea): when the output has
+ *    too few tiles to fill the GPU, K is cut into slices accumulated in fp32 in
+ *    the workspace and summed in slice order by a second kernel;
+ *  - operands TMA cannot address (row pitch or base not a multiple of 16 bytes,
+ *    e.g. K = 763 fp16 - the reference's test_pad_* cases, which it serves
+ *    with SIMT copies, src/op/copy.cc:823-855) are first re-pitched into it.
+ * workspace == NULL behaves exactly like tlb200_gemm (which rejects such
+ * operands).  The workspace may be reused by the next call on the same
+ * stream; calls on different streams need different workspaces.
+ * tlb200_gemm_workspace_bytes assumes 16-byte aligned base addresses. */
 int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                    void* workspace, int64_t workspace_bytes, void* stream);

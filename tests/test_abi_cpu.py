@@ -123,8 +123,8 @@ def test_plan_split_k(built_lib):
 
 
 def test_plan_rejects_bad_arguments(built_lib):
-    with pytest.raises(RuntimeError, match="16 bytes"):
-        G.plan(128, 128, 100)  # K*2 bytes not a multiple of 16 -> TMA cannot address it
+    p = G.plan(128, 128, 100)  # K*2 bytes not a multiple of 16: operands are re-pitched through the workspace
+    assert p["workspace_bytes"] == 2 * 128 * 128 * 2 and p["split_k"] == 1
     with pytest.raises(RuntimeError, match="cfg_block_n"):
         G.plan(128, 128, 128, block_n=48, cta_group=2)
     with pytest.raises(RuntimeError, match="multiple of 128"):

@@ -200,6 +200,31 @@ def test_tuning_knobs_do_not_change_results(cfg):
     assert bit_equal(G.gemm(a, b, **cfg), base)  # same K order per element => identical bits
 
 
+# ------------------------------------------------------------------ operands TMA cannot address directly
+# testing/python/kernel/test_tilelang_kernel_gemm.py:250-300 (test_pad_*): odd extents, NN layout
+@pytest.mark.parametrize("m,n,k,out", [(512 - 8, 1024 - 32, 768 - 24, torch.float16), (512 - 9, 1024 - 7, 768 - 5, torch.float16),
+                                       (512 + 19, 1024 + 17, 768 + 15, torch.float32)], ids=["pad_aligned", "pad", "pad_f32"])
+def test_reference_pad_cases_nn(m, n, k, out):
+    a, b = operands(m, n, k, torch.float16, False, False)
+    c = G.gemm(a, b, trans_a=False, trans_b=False, out_dtype=out)
+    R.assert_allclose(c, R.matmul_fp32(a, b, False, False).to(out), rtol=1e-2, atol=1e-2)
+    a, b = operands(m, n, k, torch.float16, False, False, "int")
+    assert torch.equal(G.gemm(a, b, trans_a=False, trans_b=False, out_dtype=torch.float32), a.float() @ b.float())
+
+
+@pytest.mark.parametrize("ta,tb", [(False, True), (True, False), (True, True)], ids=["nt", "tt", "tn"])
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float8_e4m3fn])
+def test_unaligned_pitches_and_bases(ta, tb, dt):
+    m, n, k = 203, 333, 1001
+    a, b = operands(m, n, k, dt, ta, tb, "int")
+    want = R.matmul_fp32(a, b, ta, tb)
+    assert torch.equal(G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=torch.float32), want)
+    # views whose base is not 16-byte aligned
+    big_a = rand((a.shape[0] + 1, a.shape[1] + 3), dt, "int")
+    av = big_a[1:, 3:]
+    assert torch.equal(G.gemm(av, b, trans_a=ta, trans_b=tb, out_dtype=torch.float32), R.matmul_fp32(av, b, ta, tb))
+
+
 # ------------------------------------------------------------------ split-K (scratch workspace)
 @pytest.mark.parametrize("m,n,k", [(128, 4096, 14336), (256, 256, 16384), (100, 520, 4112), (384, 1024, 8192)])
 @pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.float32)])
@@ -254,10 +279,11 @@ def test_argument_errors():
         G.gemm(a, b, torch.empty(64, 32, device="cuda", dtype=torch.bfloat16))
     with pytest.raises(ValueError, match="contiguous"):
         G.gemm(a.t(), b)
-    a100, b100 = operands(64, 64, 100, torch.bfloat16)
-    with pytest.raises(RuntimeError, match="multiple of 16 bytes"):
-        G.gemm(a100, b100)
     lib = _abi.load()
+    a100, b100 = operands(64, 64, 100, torch.bfloat16)  # 200-byte rows: not addressable by TMA without a workspace
+    d100 = G.make_desc(64, 64, 100, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 100, 100, 64)
+    assert lib.tlb200_gemm(ctypes.byref(d100), a100.data_ptr(), b100.data_ptr(), a.data_ptr(), None) != 0
+    assert "multiple of 16 bytes" in _abi.last_error()
     d = G.make_desc(64, 64, 64, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 64, 64, 64)
     assert lib.tlb200_gemm(ctypes.byref(d), None, b.data_ptr(), a.data_ptr(), None) != 0
     assert "null tensor pointer" in _abi.last_error()

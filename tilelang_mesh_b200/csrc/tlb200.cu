@@ -121,10 +121,15 @@ struct Resolved {
   bool epi_tma;
   // split-K: the main kernel writes fp32 partial tiles into a workspace, a second kernel reduces
   int split_k, kb_per_split, m_pad;
-  long long ws_ld, ws_bytes;
+  long long ws_ld, ws_bytes;  // ws_bytes = aligned operand copies + split-K partial sums
+  // operands TMA cannot address (row pitch or base not a multiple of 16 bytes) are first copied into the
+  // workspace with a 128-byte-multiple pitch (the reference falls back to SIMT copies: src/op/copy.cc:823-855)
+  bool copy_a, copy_b;
+  long long lda_c, ldb_c, a_copy_bytes, b_copy_bytes, split_bytes;
 };
 
-int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false) {
+int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false,
+            const void* a_ptr = nullptr, const void* b_ptr = nullptr) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -142,11 +147,21 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (d->lda < a_cols) return fail("tlb200: lda=%lld < %lld", (long long)d->lda, a_cols);
   if (d->ldb < b_cols) return fail("tlb200: ldb=%lld < %lld", (long long)d->ldb, b_cols);
   if (d->ldc < d->n) return fail("tlb200: ldc=%lld < n=%d", (long long)d->ldc, d->n);
-  // TMA needs 16-byte row pitches (same constraint as the reference's bulk copy,
-  // src/op/copy.cc:1489-1499: strides in bytes, % 16, < 2^40).
-  if (d->k > 0 && d->m > 0 && d->n > 0 && ((d->lda * r->es) % 16 || (d->ldb * r->es) % 16))
-    return fail("tlb200: operand row pitch must be a multiple of 16 bytes (lda=%lld ldb=%lld, %d-byte elements)",
+  // TMA needs 16-byte row pitches and bases (same constraint as the reference's bulk copy,
+  // src/op/copy.cc:1489-1499: strides in bytes, % 16, < 2^40).  Operands that violate it are staged
+  // through the workspace; without one they are rejected.
+  const bool live = d->k > 0 && d->m > 0 && d->n > 0;
+  r->copy_a = live && ((d->lda * r->es) % 16 || reinterpret_cast<uintptr_t>(a_ptr) % 16);
+  r->copy_b = live && ((d->ldb * r->es) % 16 || reinterpret_cast<uintptr_t>(b_ptr) % 16);
+  if ((r->copy_a || r->copy_b) && !allow_split)
+    return fail("tlb200: operand row pitch and base must be a multiple of 16 bytes for TMA (lda=%lld ldb=%lld, %d-byte elements); "
+                "call tlb200_gemm_ex with a workspace and the operands are re-pitched first",
                 (long long)d->lda, (long long)d->ldb, r->es);
+  const long long a_rows = r->a_mn ? d->k : d->m, b_rows = r->b_mn ? d->k : d->n;
+  r->lda_c = r->copy_a ? (a_cols * r->es + 127) / 128 * 128 / r->es : d->lda;
+  r->ldb_c = r->copy_b ? (b_cols * r->es + 127) / 128 * 128 / r->es : d->ldb;
+  r->a_copy_bytes = r->copy_a ? (a_rows * r->lda_c * r->es + 255) / 256 * 256 : 0;
+  r->b_copy_bytes = r->copy_b ? (b_rows * r->ldb_c * r->es + 255) / 256 * 256 : 0;
 
   tlb200_gemm_plan& p = r->plan;
   memset(&p, 0, sizeof(p));
@@ -253,7 +268,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   r->split_k = split > 1 ? (r->num_k_blocks + r->kb_per_split - 1) / r->kb_per_split : 1;
   r->m_pad = p.tiles_m * p.block_m;
   r->ws_ld = (static_cast<long long>(d->n) + 3) / 4 * 4;
-  r->ws_bytes = r->split_k > 1 ? static_cast<long long>(r->split_k) * r->m_pad * r->ws_ld * 4 : 0;
+  r->split_bytes = r->split_k > 1 ? static_cast<long long>(r->split_k) * r->m_pad * r->ws_ld * 4 : 0;
+  r->ws_bytes = r->a_copy_bytes + r->b_copy_bytes + r->split_bytes;
   p.split_k = r->split_k;
   p.workspace_bytes = r->ws_bytes;
   const long long work_items = tiles * r->split_k;
@@ -359,6 +375,33 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+// Copies a row-major [rows, cols] operand to a 128-byte-multiple row pitch so that TMA can address it.
+template <typename T>
+__global__ void repitch_kernel(const T* __restrict__ src, long long ld_src, T* __restrict__ dst, long long ld_dst,
+                               long long rows, long long cols) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols, c = i - r * cols;
+    dst[r * ld_dst + c] = src[r * ld_src + c];
+  }
+}
+
+int launch_repitch(const void* src, long long ld_src, void* dst, long long ld_dst, long long rows, long long cols, int es,
+                   cudaStream_t stream) {
+  long long blocks = (rows * cols + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks < 1) blocks = 1;
+  if (es == 2)
+    repitch_kernel<uint16_t><<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const uint16_t*>(src), ld_src,
+                                                                          static_cast<uint16_t*>(dst), ld_dst, rows, cols);
+  else
+    repitch_kernel<uint8_t><<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const uint8_t*>(src), ld_src,
+                                                                        static_cast<uint8_t*>(dst), ld_dst, rows, cols);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail("tlb200: operand re-pitch launch: %s", cudaGetErrorString(e));
   return 0;
 }
 
@@ -545,22 +588,22 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
-  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr)) return rc;
-  if (r.split_k > 1) {
-    if (!ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
+  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b)) return rc;
+  if (r.split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
+  if (r.ws_bytes > 0) {
     if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
-    if (ws_bytes < r.ws_bytes) {
-      if (d->reserved[1] > 1) return fail("tlb200_gemm_ex: split-K x%d needs a %lld-byte workspace, got %lld", r.split_k, r.ws_bytes, (long long)ws_bytes);
+    if (ws_bytes < r.ws_bytes && r.split_k > 1 && d->reserved[1] <= 1) {
       tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
       d1.reserved[1] = 1;
-      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, false)) return rc;
+      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, true, a, b)) return rc;
     }
+    if (ws_bytes < r.ws_bytes)
+      return fail("tlb200_gemm_ex: this call needs a %lld-byte workspace (%lld for re-pitched operands, %lld for split-K x%d), got %lld",
+                  r.ws_bytes, r.a_copy_bytes + r.b_copy_bytes, r.split_bytes, r.split_k, (long long)ws_bytes);
   }
   const bool split = r.split_k > 1;
   if (d->m == 0 || d->n == 0) return 0;
   if (!c || (d->k > 0 && (!a || !b))) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
-  if (d->k > 0 && ((reinterpret_cast<uintptr_t>(a) % 16) || (reinterpret_cast<uintptr_t>(b) % 16)))
-    return fail("tlb200_gemm: operand base addresses must be 16-byte aligned for TMA");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   const int out_kind = out_kind_of(d->c_dtype);
   cudaError_t e;
@@ -582,20 +625,34 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   GemmKernelParams kp;
   memset(&kp, 0, sizeof(kp));
   const int bk = r.span;  // K elements per stage
+  // Workspace layout: [re-pitched A][re-pitched B][split-K partial sums]
+  char* wsb = static_cast<char*>(ws);
+  if (r.copy_a) {
+    if (int rc = launch_repitch(a, d->lda, wsb, r.lda_c, r.a_mn ? d->k : d->m, r.a_mn ? d->m : d->k, r.es, stream)) return rc;
+    a = wsb;
+    g_launches++;
+  }
+  if (r.copy_b) {
+    if (int rc = launch_repitch(b, d->ldb, wsb + r.a_copy_bytes, r.ldb_c, r.b_mn ? d->k : d->n, r.b_mn ? d->n : d->k, r.es, stream)) return rc;
+    b = wsb + r.a_copy_bytes;
+    g_launches++;
+  }
+  if (ws) ws = wsb + r.a_copy_bytes + r.b_copy_bytes;  // from here on: the split-K region
+  const long long lda = r.lda_c, ldb = r.ldb_c;
   // A
   if (!r.a_mn) {
-    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, d->lda, bk, kBlockM, "A[M,K]")) return rc;
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, kBlockM, "A[M,K]")) return rc;
     kp.a_boxes = 1; kp.a_box_bytes = kABytesPerStage;
   } else {
-    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->k, d->m, d->lda, r.span, bk, "A[K,M]")) return rc;
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->k, d->m, lda, r.span, bk, "A[K,M]")) return rc;
     kp.a_boxes = kBlockM / r.span; kp.a_box_bytes = bk * kStageRowBytes;
   }
   // B
   if (!r.b_mn) {
-    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->n, d->k, d->ldb, bk, r.b_rows_per_cta, "B[N,K]")) return rc;
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->n, d->k, ldb, bk, r.b_rows_per_cta, "B[N,K]")) return rc;
     kp.b_boxes = 1; kp.b_box_bytes = r.b_rows_per_cta * kStageRowBytes;
   } else {
-    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->k, d->n, d->ldb, r.span, bk, "B[K,N]")) return rc;
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->k, d->n, ldb, r.span, bk, "B[K,N]")) return rc;
     kp.b_boxes = r.b_rows_per_cta / r.span; kp.b_box_bytes = bk * kStageRowBytes;
   }
   // Split-K: the GEMM kernel stores fp32 partial tiles into the workspace, slice s at rows

@@ -93,6 +93,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
         raise ValueError(f"gemm: A is {a.dtype} but B is {b.dtype}")
     if a.dtype not in _AB_DTYPES:
         raise ValueError(f"gemm: unsupported operand dtype {a.dtype}")
+    if a.data_ptr() % 16:  # TMA bases are 16-byte aligned; an odd view offset costs one torch copy
+        a = a.clone(memory_format=torch.contiguous_format)
+    if b.data_ptr() % 16:
+        b = b.clone(memory_format=torch.contiguous_format)
     lda, ldb = _row_pitch(a, "A"), _row_pitch(b, "B")
     m, ka = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
     n, kb = (b.shape[0], b.shape[1]) if trans_b else (b.shape[1], b.shape[0])
@@ -118,7 +122,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
         need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc))
-        if need > 0:  # the plan wants split-K: hand it scratch memory
+        if need > 0:  # split-K partial sums and/or re-pitched copies of operands TMA cannot address
             ws = _workspace(dev, stream, need)
             rc = lib.tlb200_gemm_ex(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(),
                                     ws.numel(), stream)
