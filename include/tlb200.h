@@ -40,7 +40,9 @@ typedef enum tlb200_dtype {
   TLB200_BFLOAT16 = 1,     /* "bfloat16"     */
   TLB200_FLOAT8_E4M3 = 2,  /* "float8_e4m3"  (torch.float8_e4m3fn) */
   TLB200_FLOAT8_E5M2 = 3,  /* "float8_e5m2"  */
-  TLB200_FLOAT32 = 4       /* "float32"/"float" (output / accumulator only) */
+  TLB200_FLOAT32 = 4,      /* "float32"/"float": output; as operand type it is multiplied as TF32 (kind::tf32) */
+  TLB200_INT8 = 5,         /* "int8" operands (kind::i8, int32 accumulate) */
+  TLB200_INT32 = 6         /* "int32" output of int8 operands (exact) */
 } tlb200_dtype;
 
 /* Epilogue flags (fused into the TMEM->global drain). */

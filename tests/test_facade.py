@@ -40,6 +40,15 @@ def test_recognize_benchmark_style_program():
     assert plan["cta_group"] == 2 and plan["block_n"] == 512 and plan["umma_n"] == 256
 
 
+def test_recognize_int8_and_float32_programs():
+    p = tilelang.compile(P.nt_fragment(512, 1024, 768, 128, 128, 64, "int8", "int32", accum="int32"), out_idx=[2]).program
+    assert (p.in_dtype, p.out_dtype, p.accum_dtype) == ("int8", "int32", "int32")
+    p = tilelang.compile(P.nt_fragment(512, 1024, 768, 64, 128, 32, "float32"), out_idx=[2]).program
+    assert (p.in_dtype, p.out_dtype, p.accum_dtype) == ("float32", "float32", "float32")
+    with pytest.raises(NotImplementedError, match="int8 operands accumulate in int32"):
+        tilelang.compile(P.nt_fragment(128, 128, 128, dtype="int8", out_dtype="int32"))
+
+
 def test_recognize_quickstart_c1_descriptor():
     # configs[0] (C1): 1024^3 fp16 NN + relu, C passed by the caller (no out_idx)
     k = tilelang.compile(P.nn_relu(1024, 1024, 1024))

@@ -91,6 +91,18 @@ def test_fp8_program_calc_diff():
     assert R.calc_diff(c, ref) < 1e-3
 
 
+def test_reference_dtype_cases_f32_and_int8():
+    # testing/python/kernel/test_tilelang_kernel_gemm.py: test_gemm_f32f32f32_nt / test_gemm_i8i8i32_nt at 512x1024x768
+    kf = tilelang.compile(P.nt_fragment(512, 1024, 768, 64, 128, 32, "float32"), out_idx=[2])
+    a = torch.randn(512, 768, device="cuda")
+    b = torch.randn(1024, 768, device="cuda")
+    R.assert_allclose(kf(a, b), a @ b.T, 1e-2, 1e-2)
+    ki = tilelang.compile(P.nt_fragment(512, 1024, 768, 128, 128, 64, "int8", "int32", accum="int32"), out_idx=[2])
+    a8 = torch.randint(-128, 128, (512, 768), device="cuda", dtype=torch.int8)
+    b8 = torch.randint(-128, 128, (1024, 768), device="cuda", dtype=torch.int8)
+    assert torch.equal(ki(a8, b8).cpu(), a8.cpu().int() @ b8.cpu().int().T)
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

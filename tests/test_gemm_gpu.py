@@ -200,6 +200,39 @@ def test_tuning_knobs_do_not_change_results(cfg):
     assert bit_equal(G.gemm(a, b, **cfg), base)  # same K order per element => identical bits
 
 
+# ------------------------------------------------------------------ tf32 and int8 operands
+# testing/python/kernel/test_tilelang_kernel_gemm.py:156-247: f32f32f32 nn/nt/tn and i8i8i32 nt/tn at 512x1024x768
+@pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)], ids=["nn", "nt", "tn", "tt"])
+@pytest.mark.parametrize("cg", [1, 2])
+def test_float32_operands_run_as_tf32(ta, tb, cg):
+    m, n, k = 512, 1024, 768
+    a = torch.randn((k, m) if ta else (m, k), device="cuda")
+    b = torch.randn((n, k) if tb else (k, n), device="cuda")
+    c = G.gemm(a, b, trans_a=ta, trans_b=tb, cta_group=cg)
+    assert c.dtype == torch.float32
+    R.assert_allclose(c, R.matmul_fp32(a, b, ta, tb), rtol=1e-2, atol=1e-2)
+    ai = torch.randint(-3, 4, a.shape, device="cuda").float()
+    bi = torch.randint(-3, 4, b.shape, device="cuda").float()
+    assert torch.equal(G.gemm(ai, bi, trans_a=ta, trans_b=tb, cta_group=cg), R.matmul_fp32(ai, bi, ta, tb))  # exact in tf32
+
+
+@pytest.mark.parametrize("ta,tb", [(False, True), (True, False), (False, False)], ids=["nt", "tn", "nn"])
+@pytest.mark.parametrize("out", [torch.int32, torch.float32, torch.bfloat16])
+def test_int8_operands_int32_accumulate(ta, tb, out):
+    m, n, k = 512, 1024, 768
+    a = torch.randint(-128, 128, (k, m) if ta else (m, k), device="cuda", dtype=torch.int8)
+    b = torch.randint(-128, 128, (n, k) if tb else (k, n), device="cuda", dtype=torch.int8)
+    want = (a.cpu().int().t() if ta else a.cpu().int()) @ (b.cpu().int().t() if tb else b.cpu().int())
+    c = G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=out)
+    if out == torch.int32:
+        assert torch.equal(c.cpu(), want)  # bit-exact integer arithmetic
+        assert torch.equal(G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=out, relu=True).cpu(), want.clamp_min(0))
+    else:
+        assert torch.equal(c.cpu(), want.float().to(out))
+    with pytest.raises(RuntimeError, match="alpha"):
+        G.gemm(a, b, trans_a=ta, trans_b=tb, out_dtype=torch.int32, alpha=0.5)
+
+
 # ------------------------------------------------------------------ operands TMA cannot address directly
 # testing/python/kernel/test_tilelang_kernel_gemm.py:250-300 (test_pad_*): odd extents, NN layout
 @pytest.mark.parametrize("m,n,k,out", [(512 - 8, 1024 - 32, 768 - 24, torch.float16), (512 - 9, 1024 - 7, 768 - 5, torch.float16),

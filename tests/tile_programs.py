@@ -7,7 +7,8 @@ import tilelang
 import tilelang.language as T
 
 
-def nt_fragment(M, N, K, bM=128, bN=128, bK=32, dtype="float16", out_dtype=None, stages=3, threads=128, raster=True):
+def nt_fragment(M, N, K, bM=128, bN=128, bK=32, dtype="float16", out_dtype=None, stages=3, threads=128, raster=True,
+                accum="float"):
     out_dtype = out_dtype or dtype
 
     @T.prim_func
@@ -15,7 +16,7 @@ def nt_fragment(M, N, K, bM=128, bN=128, bK=32, dtype="float16", out_dtype=None,
         with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=threads) as (bx, by):
             a_s = T.alloc_shared((bM, bK), dtype)
             b_s = T.alloc_shared((bN, bK), dtype)
-            acc = T.alloc_fragment((bM, bN), "float")
+            acc = T.alloc_fragment((bM, bN), accum)
             c_s = T.alloc_shared((bM, bN), out_dtype)
             T.use_swizzle(panel_size=10, enable=raster)
             T.annotate_layout({c_s: tilelang.layout.make_swizzled_layout(c_s)})

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("TLB200_LIB") or os.path.join(_HERE, "lib", "libtlb200
 ABI_VERSION = 1
 
 # tlb200_dtype
-FLOAT16, BFLOAT16, FLOAT8_E4M3, FLOAT8_E5M2, FLOAT32 = 0, 1, 2, 3, 4
+FLOAT16, BFLOAT16, FLOAT8_E4M3, FLOAT8_E5M2, FLOAT32, INT8, INT32 = 0, 1, 2, 3, 4, 5, 6
 EPI_NONE, EPI_RELU = 0, 1
 STATIC_SCRATCH_BYTES = 32 << 20  # TLB200_STATIC_SCRATCH_BYTES
 

@@ -43,7 +43,7 @@ constexpr int kMaxStages = 12;
 constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
 
-enum OutKind : int { kOutF16 = 0, kOutBF16 = 1, kOutE4M3 = 2, kOutE5M2 = 3, kOutF32 = 4 };
+enum OutKind : int { kOutF16 = 0, kOutBF16 = 1, kOutE4M3 = 2, kOutE5M2 = 3, kOutF32 = 4, kOutI32 = 6 };
 
 struct alignas(64) GemmKernelParams {
   CUtensorMap tm_a;  // operand A boxes
@@ -78,7 +78,7 @@ struct alignas(64) GemmKernelParams {
   uint32_t desc_lbo_a, desc_lbo_b; // (LBO >> 4) << 16: the leading-byte-offset field of the lower word
   uint32_t kadv_a, kadv_b;         // (bytes >> 4) to advance desc.lo per MMA along K
   int out_kind;
-  int is_f8;
+  int acc_int;  // accumulators hold int32 (int8 operands)
   int epi_tma;
   int relu;
   int l2_policy;
@@ -98,6 +98,8 @@ template <>
 struct OutTraits<kOutE5M2> { static constexpr int kBytes = 1; };
 template <>
 struct OutTraits<kOutF32> { static constexpr int kBytes = 4; };
+template <>
+struct OutTraits<kOutI32> { static constexpr int kBytes = 4; };
 
 // Convert 16/sizeof(out) consecutive fp32 values to one 16-byte packet, round-to-nearest-even
 // (reference epilogue: __float22bfloat162_rn / __float22half2_rn in generated code; fp8 through
@@ -123,7 +125,7 @@ __device__ __forceinline__ uint4 pack16(const float* v) {
     r.y = *reinterpret_cast<uint32_t*>(&p1);
     r.z = *reinterpret_cast<uint32_t*>(&p2);
     r.w = *reinterpret_cast<uint32_t*>(&p3);
-  } else if constexpr (kOut == kOutF32) {
+  } else if constexpr (kOut == kOutF32 || kOut == kOutI32) {  // I32: v[] carries the raw integer bits
     r.x = __float_as_uint(v[0]);
     r.y = __float_as_uint(v[1]);
     r.z = __float_as_uint(v[2]);
@@ -148,11 +150,25 @@ __device__ __forceinline__ void store_scalar(void* c, long long idx, float v) {
     reinterpret_cast<__nv_bfloat16*>(c)[idx] = __float2bfloat16_rn(v);
   } else if constexpr (kOut == kOutF16) {
     reinterpret_cast<__half*>(c)[idx] = __float2half_rn(v);
-  } else if constexpr (kOut == kOutF32) {
+  } else if constexpr (kOut == kOutF32 || kOut == kOutI32) {
     reinterpret_cast<float*>(c)[idx] = v;
   } else {
     constexpr __nv_fp8_interpretation_t kI = (kOut == kOutE4M3) ? __NV_E4M3 : __NV_E5M2;
     reinterpret_cast<uint8_t*>(c)[idx] = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, kI);
+  }
+}
+
+// One accumulator element -> the value to be cast: alpha, relu; int32 accumulators (int8 operands) are
+// converted to float unless the output is int32 too, in which case the raw integer bits are carried.
+template <int kOut>
+__device__ __forceinline__ float epi_value(uint32_t raw, float alpha, bool relu, bool acc_int) {
+  if constexpr (kOut == kOutI32) {
+    int xi = static_cast<int>(raw);
+    if (relu) xi = max(xi, 0);
+    return __int_as_float(xi);
+  } else {
+    float x = (acc_int ? static_cast<float>(static_cast<int>(raw)) : __uint_as_float(raw)) * alpha;
+    return relu ? fmaxf(x, 0.f) : x;
   }
 }
 
@@ -171,6 +187,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
   const uint32_t lane_taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
   const float alpha = p.alpha;
   const bool relu = p.relu != 0;
+  const bool acc_int = p.acc_int != 0;
 
   if (p.epi_tma) {
     // Per 128-byte-wide slab: TMEM loads (two x32 loads in flight) and the cast run BEFORE waiting
@@ -194,8 +211,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
             float v[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-              float x = __uint_as_float(r[h][i]) * alpha;
-              v[i] = relu ? fmaxf(x, 0.f) : x;
+              v[i] = epi_value<kOut>(r[h][i], alpha, relu, acc_int);
             }
 #pragma unroll
             for (int pk = 0; pk < kPacketsPerLd; ++pk) w[h * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
@@ -242,8 +258,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       float v[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        float x = __uint_as_float(r[i]) * alpha;
-        v[i] = relu ? fmaxf(x, 0.f) : x;
+        v[i] = epi_value<kOut>(r[i], alpha, relu, acc_int);
       }
       if (row_ok) {
         const int gcol = col0 + cs;
@@ -273,7 +288,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
 // region the compiler cannot prove uniformity and wraps every such instruction in an
 // ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" loop, which made the first version of this kernel
 // issue-bound (~870 cycles per K-block instead of 512; profiles/r1_notes.md).
-template <int kCta, bool kF8, int kNSub>
+template <int kCta, int kKind, int kNSub>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -430,7 +445,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
           const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
           const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
-          umma_ss<kCta, kF8>(d_tmem, da, db, idesc, (first_kb && k == 0) ? 0u : 1u);
+          umma_ss<kCta, kKind>(d_tmem, da, db, idesc, (first_kb && k == 0) ? 0u : 1u);
         }
       };
       if constexpr (kNSub == 1) {
@@ -475,8 +490,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
               for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
                 const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
                 const uint32_t acc = (kb != kb0 || k != 0) ? 1u : 0u;
-                umma_ss<kCta, kF8>(tmem_base, da, hi_b | ((b_lo + k * kadv_b) & 0x3FFFu), idesc, acc);
-                umma_ss<kCta, kF8>(tmem_base + umma_n, da, hi_b | ((b_lo + b_sub + k * kadv_b) & 0x3FFFu), idesc, acc);
+                umma_ss<kCta, kKind>(tmem_base, da, hi_b | ((b_lo + k * kadv_b) & 0x3FFFu), idesc, acc);
+                umma_ss<kCta, kKind>(tmem_base + umma_n, da, hi_b | ((b_lo + b_sub + k * kadv_b) & 0x3FFFu), idesc, acc);
               }
               umma_commit<kCta>(bar_empty + 8 * s);
               if (kb + 1 == kb1) {
@@ -524,6 +539,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
             case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
             case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutI32: epilogue_tile<kOutI32>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
             default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
           }
         }

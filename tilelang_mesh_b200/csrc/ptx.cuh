@@ -209,40 +209,31 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 
 // ----------------------------------------------------------------------------- tcgen05.mma
 // D[tmem] (+)= A[smem desc] * B[smem desc]; `accumulate` = 0 overwrites D.
-// kF8 selects kind::f8f6f4 (e4m3/e5m2 operands) instead of kind::f16 (fp16/bf16).
-template <int kCta, bool kF8>
+// kKind selects the instruction kind by operand type: fp16/bf16, e4m3/e5m2, fp32 read as tf32, int8.
+enum MmaKind : int { kKindF16 = 0, kKindF8 = 1, kKindTF32 = 2, kKindI8 = 3 };
+
+#define TLB200_UMMA(GROUP, KIND)                                                                   \
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"                                  \
+               "tcgen05.mma.cta_group::" GROUP ".kind::" KIND " [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), \
+               "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)                                \
+               : "memory")
+
+template <int kCta, int kKind>
 __device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
                                         uint32_t idesc, uint32_t accumulate) {
   if constexpr (kCta == 1) {
-    if constexpr (kF8) {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-          "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-          "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-          : "memory");
-    } else {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-          "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-          "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-          : "memory");
-    }
+    if constexpr (kKind == kKindF8) TLB200_UMMA("1", "f8f6f4");
+    else if constexpr (kKind == kKindTF32) TLB200_UMMA("1", "tf32");
+    else if constexpr (kKind == kKindI8) TLB200_UMMA("1", "i8");
+    else TLB200_UMMA("1", "f16");
   } else {
-    if constexpr (kF8) {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-          "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-          "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-          : "memory");
-    } else {
-      asm volatile(
-          "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-          "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-          "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-          : "memory");
-    }
+    if constexpr (kKind == kKindF8) TLB200_UMMA("2", "f8f6f4");
+    else if constexpr (kKind == kKindTF32) TLB200_UMMA("2", "tf32");
+    else if constexpr (kKind == kKindI8) TLB200_UMMA("2", "i8");
+    else TLB200_UMMA("2", "f16");
   }
 }
+#undef TLB200_UMMA
 
 // Make `bar` observe completion of every tcgen05.mma this thread issued so far.
 // (implies tcgen05.fence::before_thread_sync).  For a pair the arrive is multicast to the

@@ -58,13 +58,25 @@ int dtype_bytes(int dt) {
     case TLB200_BFLOAT16: return 2;
     case TLB200_FLOAT8_E4M3:
     case TLB200_FLOAT8_E5M2: return 1;
-    case TLB200_FLOAT32: return 4;
+    case TLB200_INT8: return 1;
+    case TLB200_FLOAT32:
+    case TLB200_INT32: return 4;
     default: return 0;
   }
 }
 bool is_ab_dtype(int dt) {
   return dt == TLB200_FLOAT16 || dt == TLB200_BFLOAT16 || dt == TLB200_FLOAT8_E4M3 ||
-         dt == TLB200_FLOAT8_E5M2;
+         dt == TLB200_FLOAT8_E5M2 || dt == TLB200_FLOAT32 || dt == TLB200_INT8;
+}
+// tcgen05.mma kind of an operand type (fp32 operands are read as tf32)
+int mma_kind_of(int ab) {
+  switch (ab) {
+    case TLB200_FLOAT8_E4M3:
+    case TLB200_FLOAT8_E5M2: return kKindF8;
+    case TLB200_FLOAT32: return kKindTF32;
+    case TLB200_INT8: return kKindI8;
+    default: return kKindF16;
+  }
 }
 
 uint32_t instr_desc_impl(int atom_m, int atom_n, int atom_k, int ab, int c, bool a_k_major,
@@ -76,13 +88,17 @@ uint32_t instr_desc_impl(int atom_m, int atom_n, int atom_k, int ab, int c, bool
     case TLB200_BFLOAT16: fmt = 1; break;
     case TLB200_FLOAT8_E4M3: fmt = 0; break;
     case TLB200_FLOAT8_E5M2: fmt = 1; break;
+    case TLB200_FLOAT32: fmt = 2; break;  // kind::tf32 (the reference's emitter never encodes it; PTX ISA value)
+    case TLB200_INT8: fmt = 1; break;     // kind::i8: 0 = unsigned, 1 = signed
     default: return 0;
   }
   uint32_t cfmt;
   if (c == TLB200_FLOAT16) cfmt = 0;
   else if (c == TLB200_FLOAT32) cfmt = 1;
+  else if (c == TLB200_INT32) cfmt = 2;
   else return 0;
-  if (atom_m % 16 || atom_n % 8 || (atom_k != 16 && atom_k != 32)) return 0;
+  if ((ab == TLB200_INT8) != (c == TLB200_INT32)) return 0;
+  if (atom_m % 16 || atom_n % 8 || (atom_k != 8 && atom_k != 16 && atom_k != 32)) return 0;
   if ((sa != 1 && sa != -1) || (sb != 1 && sb != -1)) return 0;
   uint32_t d = 0;
   d |= (cfmt & 3u) << 4;
@@ -124,7 +140,7 @@ struct Resolved {
   long long ws_ld, ws_bytes;  // ws_bytes = aligned operand copies + split-K partial sums
   // operands TMA cannot address (row pitch or base not a multiple of 16 bytes) are first copied into the
   // workspace with a 128-byte-multiple pitch (the reference falls back to SIMT copies: src/op/copy.cc:823-855)
-  bool copy_a, copy_b;
+  bool copy_a, copy_b, tr_a, tr_b;
   long long lda_c, ldb_c, a_copy_bytes, b_copy_bytes, split_bytes;
 };
 
@@ -137,7 +153,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (d->m < 0 || d->n < 0 || d->k < 0) return fail("tlb200: negative extent (m=%d n=%d k=%d)", d->m, d->n, d->k);
   if (!is_ab_dtype(d->ab_dtype))
     return fail("tlb200: unsupported operand dtype %d (float16, bfloat16, float8_e4m3, float8_e5m2)", d->ab_dtype);
-  if (dtype_bytes(d->c_dtype) == 0) return fail("tlb200: unsupported output dtype %d", d->c_dtype);
+  if (dtype_bytes(d->c_dtype) == 0 || d->c_dtype == TLB200_INT8) return fail("tlb200: unsupported output dtype %d", d->c_dtype);
+  if (d->c_dtype == TLB200_INT32 && d->ab_dtype != TLB200_INT8) return fail("tlb200: int32 output needs int8 operands");
+  if (d->c_dtype == TLB200_INT32 && d->alpha != 1.0f) return fail("tlb200: int32 output cannot be scaled (alpha must be 1)");
   r->es = dtype_bytes(d->ab_dtype);
   r->ob = dtype_bytes(d->c_dtype);
   r->span = 128 / r->es;
@@ -151,22 +169,34 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   // src/op/copy.cc:1489-1499: strides in bytes, % 16, < 2^40).  Operands that violate it are staged
   // through the workspace; without one they are rejected.
   const bool live = d->k > 0 && d->m > 0 && d->n > 0;
-  r->copy_a = live && ((d->lda * r->es) % 16 || reinterpret_cast<uintptr_t>(a_ptr) % 16);
-  r->copy_b = live && ((d->ldb * r->es) % 16 || reinterpret_cast<uintptr_t>(b_ptr) % 16);
-  if ((r->copy_a || r->copy_b) && !allow_split)
+  // fp32 (tf32) operands whose M/N dimension is contiguous would need the 32-byte-atom swizzle variant in
+  // shared memory; they are transposed into K-major form through the workspace instead.
+  r->tr_a = live && d->ab_dtype == TLB200_FLOAT32 && r->a_mn;
+  r->tr_b = live && d->ab_dtype == TLB200_FLOAT32 && r->b_mn;
+  r->copy_a = r->tr_a || (live && ((d->lda * r->es) % 16 || reinterpret_cast<uintptr_t>(a_ptr) % 16));
+  r->copy_b = r->tr_b || (live && ((d->ldb * r->es) % 16 || reinterpret_cast<uintptr_t>(b_ptr) % 16));
+  if ((r->copy_a || r->copy_b) && !allow_split) {
+    if (r->tr_a || r->tr_b)
+      return fail("tlb200: float32 (tf32) operands with a contiguous M/N dimension are transposed through a workspace; "
+                  "call tlb200_gemm_ex with one");
     return fail("tlb200: operand row pitch and base must be a multiple of 16 bytes for TMA (lda=%lld ldb=%lld, %d-byte elements); "
                 "call tlb200_gemm_ex with a workspace and the operands are re-pitched first",
                 (long long)d->lda, (long long)d->ldb, r->es);
-  const long long a_rows = r->a_mn ? d->k : d->m, b_rows = r->b_mn ? d->k : d->n;
-  r->lda_c = r->copy_a ? (a_cols * r->es + 127) / 128 * 128 / r->es : d->lda;
-  r->ldb_c = r->copy_b ? (b_cols * r->es + 127) / 128 * 128 / r->es : d->ldb;
-  r->a_copy_bytes = r->copy_a ? (a_rows * r->lda_c * r->es + 255) / 256 * 256 : 0;
-  r->b_copy_bytes = r->copy_b ? (b_rows * r->ldb_c * r->es + 255) / 256 * 256 : 0;
+  }
+  if (r->tr_a) r->a_mn = false;  // after the transposing copy the kernel sees K-major operands
+  if (r->tr_b) r->b_mn = false;
+  const long long a_rows_c = r->a_mn ? d->k : d->m, a_cols_c = r->a_mn ? d->m : d->k;  // shape of the staged copy
+  const long long b_rows_c = r->b_mn ? d->k : d->n, b_cols_c = r->b_mn ? d->n : d->k;
+  r->lda_c = r->copy_a ? (a_cols_c * r->es + 127) / 128 * 128 / r->es : d->lda;
+  r->ldb_c = r->copy_b ? (b_cols_c * r->es + 127) / 128 * 128 / r->es : d->ldb;
+  r->a_copy_bytes = r->copy_a ? (a_rows_c * r->lda_c * r->es + 255) / 256 * 256 : 0;
+  r->b_copy_bytes = r->copy_b ? (b_rows_c * r->ldb_c * r->es + 255) / 256 * 256 : 0;
 
   tlb200_gemm_plan& p = r->plan;
   memset(&p, 0, sizeof(p));
   if (d->cfg_cta_group < 0 || d->cfg_cta_group > 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", d->cfg_cta_group);
   if (d->reserved[1] < 0 || d->reserved[1] > 64) return fail("tlb200: cfg_split_k must be in [0,64] (got %d)", d->reserved[1]);
+  if (d->reserved[1] > 1 && d->ab_dtype == TLB200_INT8) return fail("tlb200: split-K is not offered for int8 (partial sums are kept in fp32)");
   // A tile is n_sub accumulators of umma_n (<= 256) columns each.  The epilogue drains TMEM 32
   // columns at a time, so umma_n is a whole multiple of 32; an N-major B is staged in whole 128 B
   // spans per CTA.  Tiles wider than 256 columns (two accumulators sharing one A stage: 25 % less
@@ -197,7 +227,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
       const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) * ((d->n + c.bn - 1) / c.bn);
       const long long clusters = sms_all / c.cg;
       for (int split = 1; split <= 32; split *= 2) {
-        if (split > 1 && (!allow_split || d->reserved[1] == 1 || nkb / split < 8 || tiles * split > 2 * clusters)) break;
+        if (split > 1 && (!allow_split || d->ab_dtype == TLB200_INT8 || d->reserved[1] == 1 || nkb / split < 8 || tiles * split > 2 * clusters)) break;
         if (d->reserved[1] > 1 && split > d->reserved[1]) break;
         const long long items = tiles * split;
         const long long waves = (items + clusters - 1) / clusters;
@@ -254,7 +284,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   int split = d->reserved[1];  // cfg_split_k: 0 auto, 1 off, n = n slices (fewer if K is short)
   if (split == 0) {
     split = auto_split;
-    if (split == 1 && allow_split && (d->cfg_cta_group != 0 && d->cfg_block_n != 0) && tiles * 2 <= clusters && r->num_k_blocks >= 16) {
+    if (split == 1 && allow_split && d->ab_dtype != TLB200_INT8 && (d->cfg_cta_group != 0 && d->cfg_block_n != 0) && tiles * 2 <= clusters && r->num_k_blocks >= 16) {
       long long s2 = clusters / tiles;  // fully explicit tile: simple fill rule
       if (s2 > r->num_k_blocks / 8) s2 = r->num_k_blocks / 8;
       if (s2 > 32) s2 = 32;
@@ -294,7 +324,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.tmem_cols = acc_cols <= 32 ? 32 : acc_cols <= 64 ? 64 : acc_cols <= 128 ? 128 : acc_cols <= 256 ? 256 : 512;
   p.umma_n = r->umma_n;
   p.epi_warps = r->epi_warps;
-  p.instr_desc = instr_desc_impl(kBlockM * cg, r->umma_n, 32 / r->es, d->ab_dtype, TLB200_FLOAT32, !r->a_mn, !r->b_mn, 1, 1);
+  p.instr_desc = instr_desc_impl(kBlockM * cg, r->umma_n, 32 / r->es, d->ab_dtype, d->ab_dtype == TLB200_INT8 ? TLB200_INT32 : TLB200_FLOAT32,
+                                 !r->a_mn, !r->b_mn, 1, 1);
   if (p.instr_desc == 0) return fail("tlb200: cannot encode instruction descriptor");
   return 0;
 }
@@ -304,6 +335,7 @@ CUtensorMapDataType tm_dtype(int dt) {
     case TLB200_FLOAT16: return CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
     case TLB200_BFLOAT16: return CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     case TLB200_FLOAT32: return CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    case TLB200_INT32: return CU_TENSOR_MAP_DATA_TYPE_INT32;
     default: return CU_TENSOR_MAP_DATA_TYPE_UINT8;
   }
 }
@@ -389,12 +421,38 @@ __global__ void repitch_kernel(const T* __restrict__ src, long long ld_src, T* _
   }
 }
 
+// dst[c, r] = src[r, c] for 4-byte elements, 32x32 tiles through shared memory (both sides coalesced).
+__global__ void transpose32_kernel(const uint32_t* __restrict__ src, long long ld_src, uint32_t* __restrict__ dst,
+                                   long long ld_dst, long long rows, long long cols) {
+  __shared__ uint32_t tile[32][33];
+  const long long tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+  for (long long t = blockIdx.x; t < tiles_r * tiles_c; t += gridDim.x) {
+    const long long r0 = (t / tiles_c) * 32, c0 = (t % tiles_c) * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y)
+      if (r0 + i < rows && c0 + threadIdx.x < cols) tile[i][threadIdx.x] = src[(r0 + i) * ld_src + c0 + threadIdx.x];
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y)
+      if (c0 + i < cols && r0 + threadIdx.x < rows) dst[(c0 + i) * ld_dst + r0 + threadIdx.x] = tile[threadIdx.x][i];
+    __syncthreads();
+  }
+}
+
+// rows/cols describe the SOURCE as stored; with `transpose` the copy is [cols, rows].
 int launch_repitch(const void* src, long long ld_src, void* dst, long long ld_dst, long long rows, long long cols, int es,
-                   cudaStream_t stream) {
+                   bool transpose, cudaStream_t stream) {
   long long blocks = (rows * cols + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (blocks < 1) blocks = 1;
-  if (es == 2)
+  if (transpose) {
+    if (es != 4) return fail("tlb200: transposing copy is only used for 4-byte operands");
+    long long tb = ((rows + 31) / 32) * ((cols + 31) / 32);
+    if (tb > 148 * 16) tb = 148 * 16;
+    transpose32_kernel<<<static_cast<int>(tb), dim3(32, 8), 0, stream>>>(static_cast<const uint32_t*>(src), ld_src,
+                                                                        static_cast<uint32_t*>(dst), ld_dst, rows, cols);
+  } else if (es == 4)
+    repitch_kernel<uint32_t><<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const uint32_t*>(src), ld_src,
+                                                                          static_cast<uint32_t*>(dst), ld_dst, rows, cols);
+  else if (es == 2)
     repitch_kernel<uint16_t><<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const uint16_t*>(src), ld_src,
                                                                           static_cast<uint16_t*>(dst), ld_dst, rows, cols);
   else
@@ -406,20 +464,26 @@ int launch_repitch(const void* src, long long ld_src, void* dst, long long ld_ds
 }
 
 typedef void (*GemmKernelFn)(const GemmKernelParams);
-GemmKernelFn pick_kernel(int cg, bool f8, int n_sub) {
-  if (cg == 2) {
-    if (f8) return n_sub == 2 ? gemm_tcgen05_kernel<2, true, 2> : gemm_tcgen05_kernel<2, true, 1>;
-    return n_sub == 2 ? gemm_tcgen05_kernel<2, false, 2> : gemm_tcgen05_kernel<2, false, 1>;
-  }
-  if (f8) return n_sub == 2 ? gemm_tcgen05_kernel<1, true, 2> : gemm_tcgen05_kernel<1, true, 1>;
-  return n_sub == 2 ? gemm_tcgen05_kernel<1, false, 2> : gemm_tcgen05_kernel<1, false, 1>;
+template <int kCg, int kKind>
+GemmKernelFn pick_nsub(int n_sub) {
+  return n_sub == 2 ? gemm_tcgen05_kernel<kCg, kKind, 2> : gemm_tcgen05_kernel<kCg, kKind, 1>;
 }
-std::array<const void*, 8> all_kernels() {
-  std::array<const void*, 8> k;
+template <int kCg>
+GemmKernelFn pick_kind(int kind, int n_sub) {
+  switch (kind) {
+    case kKindF8: return pick_nsub<kCg, kKindF8>(n_sub);
+    case kKindTF32: return pick_nsub<kCg, kKindTF32>(n_sub);
+    case kKindI8: return pick_nsub<kCg, kKindI8>(n_sub);
+    default: return pick_nsub<kCg, kKindF16>(n_sub);
+  }
+}
+GemmKernelFn pick_kernel(int cg, int kind, int n_sub) { return cg == 2 ? pick_kind<2>(kind, n_sub) : pick_kind<1>(kind, n_sub); }
+std::array<const void*, 16> all_kernels() {
+  std::array<const void*, 16> k;
   int i = 0;
   for (int cg = 1; cg <= 2; ++cg)
-    for (int f8 = 0; f8 < 2; ++f8)
-      for (int ns = 1; ns <= 2; ++ns) k[i++] = reinterpret_cast<const void*>(pick_kernel(cg, f8 != 0, ns));
+    for (int kind = 0; kind < 4; ++kind)
+      for (int ns = 1; ns <= 2; ++ns) k[i++] = reinterpret_cast<const void*>(pick_kernel(cg, kind, ns));
   return k;
 }
 
@@ -429,6 +493,7 @@ int out_kind_of(int dt) {
     case TLB200_BFLOAT16: return kOutBF16;
     case TLB200_FLOAT8_E4M3: return kOutE4M3;
     case TLB200_FLOAT8_E5M2: return kOutE5M2;
+    case TLB200_INT32: return kOutI32;
     default: return kOutF32;
   }
 }
@@ -614,6 +679,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
       case kOutBF16: fill_zero_kernel<kOutBF16><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
       case kOutF32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
       case kOutE4M3: fill_zero_kernel<kOutE4M3><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+      case kOutI32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;  // same bits
       default: fill_zero_kernel<kOutE5M2><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("tlb200_gemm: fill launch: %s", cudaGetErrorString(e));
@@ -628,12 +694,13 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   // Workspace layout: [re-pitched A][re-pitched B][split-K partial sums]
   char* wsb = static_cast<char*>(ws);
   if (r.copy_a) {
-    if (int rc = launch_repitch(a, d->lda, wsb, r.lda_c, r.a_mn ? d->k : d->m, r.a_mn ? d->m : d->k, r.es, stream)) return rc;
+    // source shape as stored: [K, M] when transpose_A else [M, K]
+    if (int rc = launch_repitch(a, d->lda, wsb, r.lda_c, d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, r.es, r.tr_a, stream)) return rc;
     a = wsb;
     g_launches++;
   }
   if (r.copy_b) {
-    if (int rc = launch_repitch(b, d->ldb, wsb + r.a_copy_bytes, r.ldb_c, r.b_mn ? d->k : d->n, r.b_mn ? d->n : d->k, r.es, stream)) return rc;
+    if (int rc = launch_repitch(b, d->ldb, wsb + r.a_copy_bytes, r.ldb_c, d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, r.es, r.tr_b, stream)) return rc;
     b = wsb + r.a_copy_bytes;
     g_launches++;
   }
@@ -702,7 +769,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.kadv_a = r.a_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
   kp.kadv_b = r.b_mn ? (umma_k * kStageRowBytes) >> 4 : kUmmaKBytes >> 4;
   kp.out_kind = split ? static_cast<int>(kOutF32) : out_kind;
-  kp.is_f8 = r.es == 1;
+  kp.acc_int = d->ab_dtype == TLB200_INT8;
   kp.epi_tma = split ? ws_tma : r.epi_tma;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
@@ -721,7 +788,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  e = cudaLaunchKernelEx(&cfg, pick_kernel(pl.cta_group, r.es == 1, r.n_sub), kp);
+  e = cudaLaunchKernelEx(&cfg, pick_kernel(pl.cta_group, mma_kind_of(d->ab_dtype), r.n_sub), kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);

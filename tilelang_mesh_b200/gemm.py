@@ -22,8 +22,11 @@ _TORCH2TLB = {
     torch.float8_e4m3fn: _abi.FLOAT8_E4M3,
     torch.float8_e5m2: _abi.FLOAT8_E5M2,
     torch.float32: _abi.FLOAT32,
+    torch.int8: _abi.INT8,
+    torch.int32: _abi.INT32,
 }
-_AB_DTYPES = (torch.float16, torch.bfloat16, torch.float8_e4m3fn, torch.float8_e5m2)
+# float32 operands are multiplied as TF32 (kind::tf32); int8 operands accumulate in int32 (kind::i8)
+_AB_DTYPES = (torch.float16, torch.bfloat16, torch.float8_e4m3fn, torch.float8_e5m2, torch.float32, torch.int8)
 
 _inited_devices = set()
 _workspaces = {}  # (device index, stream handle) -> torch.uint8 scratch for split-K partial sums
@@ -103,7 +106,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
     if ka != kb:  # language/gemm.py:78-81
         raise ValueError(f"gemm: T.gemm K shape check failed: K_A = {ka}, K_B = {kb}")
     if c is None:
-        c = torch.empty((m, n), dtype=out_dtype or a.dtype, device=a.device)
+        c = torch.empty((m, n), dtype=out_dtype or (torch.int32 if a.dtype == torch.int8 else a.dtype), device=a.device)
     else:
         if c.device != a.device:
             raise ValueError(f"gemm: C on {c.device} but A on {a.device}")

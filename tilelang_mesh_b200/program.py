@@ -267,13 +267,21 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     extra = [p for p in tr.params if p.param_index not in (A_g.param_index, B_g.param_index, C_g.param_index)]
     if extra:
         _fail(f"extra kernel parameters {[p.name for p in extra]}")
-    if A_s.dtype not in ("float16", "bfloat16", "float8_e4m3", "float8_e5m2"):
+    if A_s.dtype not in ("float16", "bfloat16", "float8_e4m3", "float8_e5m2", "float32", "int8"):
         _fail(f"operand dtype {A_s.dtype}")
-    if C_acc.dtype != "float32":
-        _fail(f"accumulator dtype {C_acc.dtype}: the tcgen05 path accumulates in fp32 "
-              "(north_star; reference allows fp16 accumulate for fp8 only, tcgen5_meta.h:56-58)")
-    if C_g.dtype not in ("float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2"):
-        _fail(f"output dtype {C_g.dtype}")
+    if A_s.dtype == "int8":
+        if C_acc.dtype != "int32":
+            _fail(f"int8 operands accumulate in int32, not {C_acc.dtype}")
+        if C_g.dtype not in ("int32", "float32", "float16", "bfloat16"):
+            _fail(f"output dtype {C_g.dtype} for int8 operands")
+        if C_g.dtype == "int32" and alpha != 1.0:
+            _fail("scaled int32 output")
+    else:
+        if C_acc.dtype != "float32":
+            _fail(f"accumulator dtype {C_acc.dtype}: the tcgen05 path accumulates in fp32 "
+                  "(north_star; reference allows fp16 accumulate for fp8 only, tcgen5_meta.h:56-58)")
+        if C_g.dtype not in ("float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2"):
+            _fail(f"output dtype {C_g.dtype}")
 
     notes = []
     if g.wg_wait not in (0, -1):
