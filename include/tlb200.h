@@ -126,6 +126,17 @@ int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                    void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Grouped contraction (the reference's examples/grouped_gemm: MoE expert
+ * GEMMs): rows of A[sum_rows, K] and C[sum_rows, N] are cut into n_groups
+ * consecutive row groups (group_rows[g] rows each, a HOST array, 0 allowed,
+ * n_groups <= 64) and group g is multiplied by its own B block:
+ *   transpose_B = 1 : B is [n_groups, N, K]      transpose_B = 0 : B is [n_groups, K, N]
+ * (blocks contiguous, ldb = row pitch).  desc.m = sum of group_rows.  One
+ * persistent launch walks the row tiles of all groups; a tile never spans two
+ * groups. */
+int tlb200_gemm_grouped(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
+                        const int32_t* group_rows, int n_groups, void* stream);
+
 /* tlb200_gemm whose C tiles are stored into n_c matrices at once (n_c <= 8):
  * c_list[0] is the local C, the others are the same window of C in PEER GPUs'
  * memory (addresses mapped into this process, e.g. CUDA IPC / symmetric

@@ -258,6 +258,42 @@ def test_unaligned_pitches_and_bases(ta, tb, dt):
     assert torch.equal(G.gemm(av, b, trans_a=ta, trans_b=tb, out_dtype=torch.float32), R.matmul_fp32(av, b, ta, tb))
 
 
+# ------------------------------------------------------------------ grouped contraction (MoE expert GEMMs)
+def torch_gmm(a, b, rows, trans_b):
+    # the reference's checker: examples/grouped_gemm/example_grouped_gemm_fwd.py:8-38
+    out, start = [], 0
+    for g, r in enumerate(rows):
+        bg = b[g].float().t() if trans_b else b[g].float()
+        out.append(a[start:start + r].float() @ bg)
+        start += r
+    return torch.cat(out) if out else a.new_zeros((0, b.shape[1] if trans_b else b.shape[2])).float()
+
+
+@pytest.mark.parametrize("rows", [[64, 128, 512, 33], [300, 0, 1, 700, 256], [4096, 4096], [7] * 40, [129, 255, 257, 511]])
+@pytest.mark.parametrize("trans_b", [False, True], ids=["b_kn", "b_nk"])
+@pytest.mark.parametrize("cfg", [dict(), dict(cta_group=1, block_n=128), dict(cta_group=2, block_n=256)], ids=["auto", "c1", "c2"])
+def test_grouped_gemm(rows, trans_b, cfg):
+    k, n = 512, 768
+    a = rand((sum(rows), k), torch.bfloat16, "int")
+    b = rand((len(rows), n, k) if trans_b else (len(rows), k, n), torch.bfloat16, "int")
+    c = torch.full((sum(rows), n), 7.0, device="cuda", dtype=torch.float32)
+    G.gemm_grouped(a, b, rows, c, trans_b=trans_b, **cfg)
+    assert torch.equal(c, torch_gmm(a, b, rows, trans_b))  # exact inputs: bit-exact
+
+
+def test_grouped_gemm_random_fp16_and_errors():
+    rows = [1000, 24, 3000, 72]  # example_grouped_gemm_fwd.py-style uneven batch sizes
+    k, n = 4096, 2048
+    a = rand((sum(rows), k), torch.float16)
+    b = rand((len(rows), k, n), torch.float16)
+    c = G.gemm_grouped(a, b, rows)
+    R.assert_allclose(c, torch_gmm(a, b, rows, False).half(), 1e-2, 1e-2)
+    with pytest.raises(ValueError, match="sum to"):
+        G.gemm_grouped(a, b, [1, 2, 3, 4])
+    with pytest.raises(RuntimeError, match="n_groups"):
+        G.gemm_grouped(rand((65, 64), torch.float16), rand((65, 64, 64), torch.float16), [1] * 65)
+
+
 # ------------------------------------------------------------------ split-K (scratch workspace)
 @pytest.mark.parametrize("m,n,k", [(128, 4096, 14336), (256, 256, 16384), (100, 520, 4112), (384, 1024, 8192)])
 @pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.float32)])

@@ -81,6 +81,8 @@ SYMBOLS = {
     "tlb200_gemm_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
     "tlb200_gemm_ex": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                       ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "tlb200_gemm_grouped": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.POINTER(ctypes.c_int32), ctypes.c_int, ctypes.c_void_p]),
     "tlb200_gemm_bcast": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                          ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_void_p]),
     "tlb200_gemm_static_scratch": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,

@@ -40,6 +40,7 @@ constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple
 constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
 constexpr int kEpiSlabs = 8;               // slabs per CTA: 4 warps x 2 or 8 warps x 1 (32 KiB)
 constexpr int kMaxStages = 12;
+constexpr int kMaxGroups = 64;   // grouped GEMM: row groups of A/C, each with its own B
 constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
 
@@ -52,6 +53,12 @@ struct alignas(64) GemmKernelParams {
   CUtensorMap tm_c_peer[kMaxPeerDst];  // additional destinations of every C store (peer GPUs' copies of C)
   void* c_peer[kMaxPeerDst];
   int n_peer;        // number of additional destinations (0 = single-GPU store)
+  // grouped GEMM (examples/grouped_gemm): rows [group_row[g], group_row[g+1]) of A and C use B block g.
+  // tiles_m then counts the row tiles of all groups; group_tile[g] is the first row tile of group g.
+  int n_groups;      // 0 = ordinary GEMM
+  int b_group_rows;  // rows of one group's B in the 2-D view TMA sees (N if K-major, K if N-major)
+  int group_row[kMaxGroups + 1];
+  int group_tile[kMaxGroups + 1];
   void* c;
   long long ldc;  // elements
   int m, n;
@@ -177,7 +184,7 @@ __device__ __forceinline__ float epi_value(uint32_t raw, float alpha, bool relu,
 // tmem_acc = TMEM address of the accumulator (lane 0, first column).
 template <int kOut>
 __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_t tmem_acc, int q,
-                                              int lane, int row0, int row_off, int col0, int cbeg, int cend,
+                                              int lane, int row0, int row_limit, int row_off, int col0, int cbeg, int cend,
                                               uint32_t stage_smem, int nslabs, int& slab_iter) {
   constexpr int kOB = OutTraits<kOut>::kBytes;
   constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
@@ -189,7 +196,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
   const bool relu = p.relu != 0;
   const bool acc_int = p.acc_int != 0;
 
-  if (p.epi_tma) {
+  // A TMA store writes the warp's whole 32-row slab: use it only when all 32 rows belong to this tile's
+  // row range (always true for an ordinary GEMM, where the tensor map clips at M; a grouped GEMM's last
+  // row tile of a group falls back to predicated stores).
+  const bool slab_rows_ok = p.n_groups == 0 || row0 + q * 32 + 32 <= row_limit;
+  if (p.epi_tma && slab_rows_ok) {
     // Per 128-byte-wide slab: TMEM loads (two x32 loads in flight) and the cast run BEFORE waiting
     // for the TMA store that last read the slab, so that store's smem read is hidden behind them.
     constexpr int kLdsPerSlab = kColsPerSlab / 32;
@@ -236,7 +247,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
       __syncwarp();
       if (lane == 0) {
-        if (row0 + q * 32 < p.m) {
+        if (row0 + q * 32 < row_limit) {
           // C is write-once: evict_first keeps the operands in L2
           if (p.l2_policy != 1) tma_store_2d_hint(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
           else tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
@@ -248,7 +259,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       ++slab_iter;
     }
   } else {
-    const bool row_ok = grow < p.m;
+    const bool row_ok = grow < row_limit;
     const bool vec_ok = ((p.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(p.c) % 16) == 0);
     for (int cs = cbeg; cs < cend; cs += 32) {
       if (col0 + cs >= p.n) break;
@@ -355,7 +366,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const int num_clusters = gridDim.x / kCta;
   const int nkb = p.num_k_blocks;
 
-  auto tile_coord = [&](int w, int& tm, int& tn) {
+  // Work item -> (row tile, column tile); for a grouped GEMM also the group, the first row of the tile
+  // and the end of the group's rows (the tile's row limit).
+  auto tile_coord = [&](int w, int& tm, int& tn, int& grp, int& row_base, int& row_limit) {
     const int t = w % tiles_mn;
     const int group = p.raster * p.tiles_n;
     const int g = t / group;
@@ -364,6 +377,17 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const int within = t - g * group;
     tm = first + within % rows;
     tn = within / rows;
+    if (p.n_groups == 0) {
+      grp = 0;
+      row_base = tm * kCta * kBlockM;
+      row_limit = p.m;
+    } else {
+      int gi = 0;
+      while (gi + 1 < p.n_groups && p.group_tile[gi + 1] <= tm) ++gi;
+      grp = gi;
+      row_base = p.group_row[gi] + (tm - p.group_tile[gi]) * kCta * kBlockM;
+      row_limit = p.group_row[gi + 1];
+    }
   };
   // K-block range [kb0, kb1) of work item w
   auto k_range = [&](int w, int& kb0, int& kb1) {
@@ -384,10 +408,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     int s = 0;
     uint32_t ph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      int tm, tn;
-      tile_coord(t, tm, tn);
-      const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
-      const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta;
+      int tm, tn, grp, row_base, row_limit;
+      tile_coord(t, tm, tn, grp, row_base, row_limit);
+      const int row_a = row_base + (int)cta_rank * kBlockM;
+      // group g's B is block g of the 2-D view: rows [g*b_group_rows, ...) (K-major) or K offset (N-major)
+      const int b_goff = grp * p.b_group_rows;
+      const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta + (p.b_mn_major ? 0 : b_goff);
+      const int kb_off = p.b_mn_major ? b_goff : 0;
       int kb0, kb1;
       k_range(t, kb0, kb1);
       for (int kb = kb0; kb < kb1; ++kb) {
@@ -412,7 +439,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             const int rb = row_b + h * p.umma_n;
             for (int j = 0; j < p.b_boxes; ++j) {
               const int c0 = p.b_mn_major ? rb + j * kspan : k0;
-              const int c1 = p.b_mn_major ? k0 : rb + j * b_rows_per_box;
+              const int c1 = p.b_mn_major ? k0 + kb_off : rb + j * b_rows_per_box;
               const uint32_t dst = dst_b + h * b_sub_bytes + j * p.b_box_bytes;
               if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol_b);
               else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol_b);
@@ -521,9 +548,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     uint32_t aph = 0;
     int slab_iter = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      int tm, tn;
-      tile_coord(t, tm, tn);
-      const int row0 = (tm * kCta + (int)cta_rank) * kBlockM;
+      int tm, tn, grp, row_base, row_limit;
+      tile_coord(t, tm, tn, grp, row_base, row_limit);
+      const int row0 = row_base + (int)cta_rank * kBlockM;
       const int col0 = tn * p.block_n;
       const int row_off = (t / tiles_mn) * p.split_row_pitch;
 #pragma unroll
@@ -533,14 +560,14 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         tc_fence_after();
         const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
         const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
-        if (row0 < p.m) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
+        if (row0 < row_limit) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
           switch (p.out_kind) {
-            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutI32: epilogue_tile<kOutI32>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutI32: epilogue_tile<kOutI32>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
           }
         }
         // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.

@@ -648,7 +648,8 @@ int tlb200_init(int device) {
 }
 
 static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
-                     void* stream_v, void* const* peers = nullptr, int n_peer = 0) {
+                     void* stream_v, void* const* peers = nullptr, int n_peer = 0, const int32_t* group_rows = nullptr,
+                     int n_groups = 0) {
   g_err[0] = 0;
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
@@ -716,10 +717,10 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   }
   // B
   if (!r.b_mn) {
-    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->n, d->k, ldb, bk, r.b_rows_per_cta, "B[N,K]")) return rc;
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, static_cast<long long>(d->n) * (n_groups > 0 ? n_groups : 1), d->k, ldb, bk, r.b_rows_per_cta, "B[N,K]")) return rc;
     kp.b_boxes = 1; kp.b_box_bytes = r.b_rows_per_cta * kStageRowBytes;
   } else {
-    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->k, d->n, ldb, r.span, bk, "B[K,N]")) return rc;
+    if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, static_cast<long long>(d->k) * (n_groups > 0 ? n_groups : 1), d->n, ldb, r.span, bk, "B[K,N]")) return rc;
     kp.b_boxes = r.b_rows_per_cta / r.span; kp.b_box_bytes = bk * kStageRowBytes;
   }
   // Split-K: the GEMM kernel stores fp32 partial tiles into the workspace, slice s at rows
@@ -744,6 +745,26 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.m = d->m; kp.n = d->n;
   kp.num_k_blocks = r.num_k_blocks;
   kp.tiles_m = pl.tiles_m; kp.tiles_n = pl.tiles_n;
+  int grid = pl.grid;
+  if (n_groups > 0) {  // row tiles are counted per group; a tile never spans two groups
+    kp.n_groups = n_groups;
+    kp.b_group_rows = r.b_mn ? d->k : d->n;
+    int row = 0, tile = 0;
+    for (int g = 0; g < n_groups; ++g) {
+      kp.group_row[g] = row;
+      kp.group_tile[g] = tile;
+      row += group_rows[g];
+      tile += (group_rows[g] + pl.block_m - 1) / pl.block_m;
+    }
+    kp.group_row[n_groups] = row;
+    kp.group_tile[n_groups] = tile;
+    kp.tiles_m = tile;
+    if (tile == 0) return 0;
+    long long clusters = g_sm_count[dev] / pl.cta_group;
+    const long long items = static_cast<long long>(tile) * pl.tiles_n;
+    if (clusters > items) clusters = items;
+    grid = static_cast<int>(clusters < 1 ? 1 : clusters) * pl.cta_group;
+  }
   kp.raster = pl.raster;
   kp.block_n = pl.block_n;
   kp.umma_n = r.umma_n;
@@ -777,7 +798,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
 
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(pl.grid, 1, 1);
+  cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(pl.threads, 1, 1);
   cfg.dynamicSmemBytes = pl.smem_bytes;
   cfg.stream = stream;
@@ -804,6 +825,29 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
 
 int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {
   return gemm_impl(d, a, b, c, nullptr, 0, stream_v);
+}
+
+int tlb200_gemm_grouped(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, const int32_t* group_rows,
+                        int n_groups, void* stream_v) {
+  if (!d) return fail("tlb200_gemm_grouped: null descriptor");
+  if (!group_rows || n_groups < 1 || n_groups > kMaxGroups)
+    return fail("tlb200_gemm_grouped: n_groups must be in [1,%d] (got %d)", kMaxGroups, n_groups);
+  long long total = 0;
+  for (int g = 0; g < n_groups; ++g) {
+    if (group_rows[g] < 0) return fail("tlb200_gemm_grouped: group %d has a negative row count", g);
+    total += group_rows[g];
+  }
+  if (total != d->m) return fail("tlb200_gemm_grouped: group rows sum to %lld but desc.m = %d", total, d->m);
+  if (d->trans_a) return fail("tlb200_gemm_grouped: A must be [sum_rows, K] (transpose_A = 0)");
+  if (d->reserved[1] > 1) return fail("tlb200_gemm_grouped: split-K is not offered for grouped contractions");
+  tlb200_gemm_desc d1 = *d;
+  d1.reserved[1] = 1;
+  if (d1.cfg_block_n == 0 && d1.cfg_cta_group == 0) {  // tiles must not waste rows on small groups
+    long long biggest = 0;
+    for (int g = 0; g < n_groups; ++g) biggest = group_rows[g] > biggest ? group_rows[g] : biggest;
+    d1.cfg_cta_group = biggest > 192 ? 2 : 1;
+  }
+  return gemm_impl(&d1, a, b, c, nullptr, 0, stream_v, nullptr, 0, group_rows, n_groups);
 }
 
 int tlb200_gemm_bcast(const tlb200_gemm_desc* d, const void* a, const void* b, void* const* c_list, int n_c, void* stream_v) {

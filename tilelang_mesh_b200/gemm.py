@@ -135,6 +135,37 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
     return c
 
 
+def gemm_grouped(a: torch.Tensor, b: torch.Tensor, group_rows, c: Optional[torch.Tensor] = None, *, trans_b: bool = False,
+                 out_dtype: Optional[torch.dtype] = None, alpha: float = 1.0, relu: bool = False, **cfg) -> torch.Tensor:
+    """Grouped contraction (examples/grouped_gemm/example_grouped_gemm_fwd.py): rows of ``a`` [sum_rows, K] are
+    cut into consecutive groups of ``group_rows[g]`` rows, group g is multiplied by ``b[g]``
+    ([K, N], or [N, K] with ``trans_b``)."""
+    if a.dim() != 2 or b.dim() != 3 or not (a.is_cuda and b.is_cuda) or a.dtype != b.dtype or a.dtype not in _AB_DTYPES:
+        raise ValueError("gemm_grouped: need CUDA tensors A [sum_rows, K] and B [groups, ., .] of the same supported dtype")
+    rows = [int(x) for x in group_rows]
+    if len(rows) != b.shape[0] or sum(rows) != a.shape[0]:
+        raise ValueError("gemm_grouped: group_rows must have one entry per B block and sum to A's rows")
+    if not b.is_contiguous():
+        raise ValueError("gemm_grouped: B must be contiguous")
+    k = a.shape[1]
+    n, kb = (b.shape[1], b.shape[2]) if trans_b else (b.shape[2], b.shape[1])
+    if kb != k:
+        raise ValueError(f"gemm_grouped: T.gemm K shape check failed: K_A = {k}, K_B = {kb}")
+    if c is None:
+        c = torch.empty((a.shape[0], n), dtype=out_dtype or a.dtype, device=a.device)
+    dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    desc = make_desc(a.shape[0], n, k, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], False, trans_b, _row_pitch(a, "A"),
+                     b.shape[2], _row_pitch(c, "C"), alpha, relu, **cfg)
+    arr = (ctypes.c_int32 * len(rows))(*rows)
+    lib = _abi.load()
+    with torch.cuda.device(dev):
+        rc = lib.tlb200_gemm_grouped(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), arr, len(rows),
+                                     torch.cuda.current_stream(dev).cuda_stream)
+    _abi.check(rc, "tlb200_gemm_grouped")
+    return c
+
+
 def gemm_bcast(a: torch.Tensor, b: torch.Tensor, dst_ptrs, ldc: int, c_dtype: torch.dtype, *, alpha: float = 1.0,
                relu: bool = False, **cfg) -> None:
     """C = A[M,K] @ B[N,K]^T stored into SEVERAL matrices at once (tlb200_gemm_bcast): ``dst_ptrs[0]`` is the
