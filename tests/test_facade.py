@@ -218,6 +218,11 @@ def test_scaled_epilogue_and_partial_k_loop_rejected():
     ("examples/quickstart.py", "M = 1024", "matmul(1024, 1024, 1024, 128, 128, 32)"),
     ("examples/gemm/example_gemm.py", "def main", "matmul(1024, 1024, 1024, 128, 128, 32)"),
     ("examples/gemm_sm100/gemm_tcgen5mma.py", "print(jit_kernel.get_kernel_source())", "jit_kernel"),
+    ("examples/gemm/example_gemm_schedule.py", "def main", "matmul(1024, 1024, 1024, 128, 128, 32)"),
+    ("examples/gemm/example_gemm_autotune.py", "\ndef main(M", "matmul(1024, 1024, 1024, 128, 256, 32, 0, 128, True)"),
+    ("examples/gemm/example_gemm_autotune.py", "\ndef main(M", "get_best_config(1024, 1024, 1024, False).kernel"),
+    ("examples/gemm/example_gemm_persistent.py", "def ref_program",
+     "matmul_non_persistent(1024, 1024, 1024, 128, 256, 32, 128, 3)"),
     ("benchmark/matmul/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
     ("benchmark/matmul_fp8/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
 ])
@@ -232,3 +237,80 @@ def test_reference_programs_trace_unmodified(rel, cut, call):
     assert p.M > 0 and p.accum_dtype == "float32"
     assert kern.plan()["grid"] >= 1
     assert "tcgen05" in kern.get_kernel_source()
+
+
+def test_elementwise_staging_loop_is_a_copy():
+    k = tilelang.compile(P.elementwise_staging(512, 384, 256), out_idx=[2])
+    p = k.program
+    assert (p.M, p.N, p.K, p.trans_A, p.trans_B) == (512, 384, 256, False, False)
+
+    M = N = K = 256
+
+    @T.prim_func
+    def transposing_fill(A: T.Tensor((M, K), "float16"), B: T.Tensor((K, N), "float16"), C: T.Tensor((M, N), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((32, 128), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                for kk, j in T.Parallel(32, 128):
+                    b_s[kk, j] = B[k * 32 + j, bx * 128 + kk]
+                T.gemm(a_s, b_s, acc)
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="must be origin"):
+        tilelang.compile(transposing_fill)
+
+
+def test_persistent_primitive_program():
+    k = tilelang.compile(P.persistent_primitive(1024, 2048, 512), out_idx=[-1])
+    p = k.program
+    assert (p.M, p.N, p.K, p.block_M, p.block_N) == (1024, 2048, 512, 128, 256)
+    # tile domain must cover the output
+    with pytest.raises(NotAGemmProgram, match="grid dimension"):
+        @T.prim_func
+        def short(A: T.Tensor((1024, 64), "float16"), B: T.Tensor((64, 1024), "float16"), C: T.Tensor((1024, 1024), "float16")):
+            with T.Kernel(8, threads=128) as (block_id):
+                a_s = T.alloc_shared((128, 64), "float16")
+                b_s = T.alloc_shared((64, 128), "float16")
+                acc = T.alloc_fragment((128, 128), "float")
+                for tx, ty in T.Persistent([4, 8], 8, block_id):
+                    T.clear(acc)
+                    for k in T.Pipelined(1, num_stages=1):
+                        T.copy(A[tx * 128, k * 64], a_s)
+                        T.copy(B[k * 64, ty * 128], b_s)
+                        T.gemm(a_s, b_s, acc)
+                    T.copy(acc, C[tx * 128, ty * 128])
+        tilelang.compile(short)
+
+
+def test_fp16_accumulate_programs_are_widened():
+    # examples/gemm_fp8/example_tilelang_gemm_fp8_sm100.py:76 runs accum_dtype float16 for fp8 operands
+    k = tilelang.compile(P.tmem_accumulator(256, 256, 256, 64, 256, 32, in_dtype="float8_e4m3", out_dtype="float16",
+                                            accum_dtype="float16"), out_idx=[2])
+    assert k.program.accum_dtype == "float16" and any("widened" in n for n in k.program.notes)
+    with pytest.raises(NotAGemmProgram, match="accumulator dtype"):
+        tilelang.compile(P.tmem_accumulator(256, 256, 256, in_dtype="bfloat16", out_dtype="float16", accum_dtype="float16"))
+
+
+def test_autotuner_builder_form_and_carver_names():
+    from tilelang.autotuner import AutoTuner
+    from tilelang.carver.arch import CUDA
+    from tilelang.carver.roller.rasterization import NoRasterization  # noqa: F401
+    from tilelang.carver.template import MatmulTemplate
+
+    def kernel(bM=None, bN=None, bK=None):
+        return P.nt_fragment(512, 512, 256, bM, bN, bK)
+
+    cfgs = [dict(bM=128, bN=128, bK=32), dict(bM=128, bN=256, bK=64)]
+    tuner = AutoTuner.from_kernel(kernel=kernel, configs=cfgs).set_compile_args(out_idx=[-1], target="auto")
+    tuner = tuner.set_profile_args(ref_prog=lambda a, b: a @ b.T, skip_check=True)
+    if not torch.cuda.is_available():
+        res = tuner.run(warmup=1, rep=2)
+        assert res.config["bM"] == 128 and res.kernel.program.M == 512 and res.latency is None
+    with pytest.raises(NotImplementedError, match="plan"):
+        MatmulTemplate(M=512, N=512, K=256, in_dtype="float16", out_dtype="float16", accum_dtype="float")
+    with pytest.raises(NotImplementedError):
+        CUDA("cuda")

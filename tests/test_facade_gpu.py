@@ -103,6 +103,44 @@ def test_reference_dtype_cases_f32_and_int8():
     assert torch.equal(ki(a8, b8).cpu(), a8.cpu().int() @ b8.cpu().int().T)
 
 
+def test_schedule_and_persistent_example_forms():
+    # examples/gemm/example_gemm_schedule.py (element-wise B staging) and example_gemm_persistent.py (T.Persistent)
+    for prog, dt in ((P.elementwise_staging(1024, 768, 512), torch.float16),
+                     (P.persistent_primitive(1024, 2048, 512), torch.bfloat16)):
+        kern = tilelang.compile(prog, out_idx=[-1])
+        p = kern.program
+        a = torch.randn(p.M, p.K, device="cuda", dtype=dt)
+        b = torch.randn(p.K, p.N, device="cuda", dtype=dt)
+        torch.testing.assert_close(kern(a, b), a @ b, rtol=1e-2, atol=1e-2)
+
+
+def test_fp8_fp16_accumulate_program_widened():
+    # examples/gemm_fp8/example_tilelang_gemm_fp8_sm100.py:75-118: fp8 operands, accum/out float16
+    M, N, K = 1024, 1024, 2048
+    for fp8, tdt in (("float8_e4m3", torch.float8_e4m3fn), ("float8_e5m2", torch.float8_e5m2)):
+        kern = tilelang.compile(P.tmem_accumulator(M, N, K, 64, 256, 32, in_dtype=fp8, out_dtype="float16",
+                                                   accum_dtype="float16", stages=2), out_idx=[2])
+        a = torch.randn(M, K, device="cuda", dtype=torch.float16).to(tdt)
+        b = torch.randn(N, K, device="cuda", dtype=torch.float16).to(tdt)
+        c = kern(a, b)
+        ref = (a.to(torch.half) @ b.T.to(torch.half)).float()
+        assert c.dtype == torch.float16 and float(R.calc_diff(c.float(), ref)) < 1e-3
+
+
+def test_autotuner_builder_form():
+    from tilelang.autotuner import AutoTuner
+
+    def kernel(bM=None, bN=None, bK=None):
+        return P.nt_fragment(1024, 1024, 512, bM, bN, bK)
+
+    res = AutoTuner.from_kernel(kernel=kernel, configs=[dict(bM=128, bN=128, bK=32)]).set_compile_args(
+        out_idx=[-1], target="auto").set_profile_args(ref_prog=lambda a, b: a @ b.T, skip_check=False).run(warmup=1, rep=3)
+    assert res.latency > 0 and res.ref_latency > 0 and res.config["bM"] == 128 and "backend_plan" in res.config
+    a = torch.randn(1024, 512, device="cuda", dtype=torch.float16)
+    b = torch.randn(1024, 512, device="cuda", dtype=torch.float16)
+    torch.testing.assert_close(res.kernel(a, b), a @ b.T, rtol=1e-2, atol=1e-2)
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

@@ -52,7 +52,7 @@ def nn_relu(M, N, K, bM=128, bN=128, bK=32, dtype="float16"):
 
 
 def tmem_accumulator(M, N, K, bM=128, bN=256, bK=128, trans_A=False, trans_B=True, in_dtype="bfloat16",
-                     out_dtype="bfloat16", stages=2, threads=256):
+                     out_dtype="bfloat16", stages=2, threads=256, accum_dtype="float"):
     a_shape, b_shape = ((K, M) if trans_A else (M, K)), ((N, K) if trans_B else (K, N))
     a_tile, b_tile = ((bK, bM) if trans_A else (bM, bK)), ((bN, bK) if trans_B else (bK, bN))
 
@@ -61,9 +61,9 @@ def tmem_accumulator(M, N, K, bM=128, bN=256, bK=128, trans_A=False, trans_B=Tru
         with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=threads) as (bx, by):
             a_s = T.alloc_shared(a_tile, in_dtype)
             b_s = T.alloc_shared(b_tile, in_dtype)
-            c_t = T.alloc_tmem([bM, bN], "float")
+            c_t = T.alloc_tmem([bM, bN], accum_dtype)
             bar = T.alloc_barrier(1)
-            c_l = T.alloc_fragment((bM, bN), "float")
+            c_l = T.alloc_fragment((bM, bN), accum_dtype)
             c_s = T.alloc_shared((bM, bN), out_dtype)
             for k in T.Pipelined(T.ceildiv(K, bK), num_stages=stages):
                 T.copy(A[(k * bK, by * bM) if trans_A else (by * bM, k * bK)], a_s)
@@ -73,5 +73,47 @@ def tmem_accumulator(M, N, K, bM=128, bN=256, bK=128, trans_A=False, trans_B=Tru
             T.copy(c_t, c_l)
             T.copy(c_l, c_s)
             T.copy(c_s, C[by * bM, bx * bN])
+
+    return prog
+
+
+def elementwise_staging(M, N, K, bM=128, bN=128, bK=32, dtype="float16"):
+    """B tile filled element by element inside T.Parallel (the form of examples/gemm/example_gemm_schedule.py)."""
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), dtype), B: T.Tensor((K, N), dtype), C: T.Tensor((M, N), dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=128) as (bx, by):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bK, bN), dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            T.clear(acc)
+            for ko in T.Pipelined(T.ceildiv(K, bK), num_stages=3):
+                T.copy(A[by * bM, ko * bK], a_s)
+                for kk, j in T.Parallel(bK, bN):
+                    b_s[kk, j] = B[ko * bK + kk, bx * bN + j]
+                T.gemm(a_s, b_s, acc)
+            T.copy(acc, C[by * bM, bx * bN])
+
+    return prog
+
+
+def persistent_primitive(M, N, K, bM=128, bN=256, bK=64, dtype="bfloat16", waves=148):
+    """Tile walk written with T.Persistent (the form of examples/gemm/example_gemm_persistent.py:92-110)."""
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), dtype), B: T.Tensor((K, N), dtype), C: T.Tensor((M, N), dtype)):
+        with T.Kernel(waves, threads=256) as (block_id):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bK, bN), dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            c_s = T.alloc_shared((bM, bN), dtype)
+            for tx, ty in T.Persistent([T.ceildiv(M, bM), T.ceildiv(N, bN)], waves, block_id):
+                T.clear(acc)
+                for k in T.Pipelined(T.ceildiv(K, bK), num_stages=3):
+                    T.copy(A[tx * bM, k * bK], a_s)
+                    T.copy(B[k * bK, ty * bN], b_s)
+                    T.gemm(a_s, b_s, acc)
+                T.copy(acc, c_s)
+                T.copy(c_s, C[tx * bM, ty * bN])
 
     return prog

@@ -13,7 +13,8 @@ from __future__ import annotations
 import inspect
 import itertools
 import logging
-from typing import Callable, Optional
+from dataclasses import dataclass
+from typing import Any, Callable, Optional
 
 logger = logging.getLogger("tilelang_mesh_b200")
 
@@ -22,7 +23,22 @@ PLAN_CANDIDATES = [dict(), dict(cta_group=2, block_n=256, raster=8), dict(cta_gr
                    dict(cta_group=1, block_n=128)]
 
 
+@dataclass
+class AutotuneResult:
+    """tilelang/autotuner/param.py:135-151.  `libcode` / `func` stay None: nothing is generated per program."""
+    latency: Optional[float] = None
+    config: Optional[dict] = None
+    ref_latency: Optional[float] = None
+    libcode: Optional[str] = None
+    func: Optional[Callable] = None
+    kernel: Any = None
+
+
 class AutoTuner:
+    """tilelang/autotuner/tuner.py:95-330.  Two ways in, as in the reference: the `@autotune` decorator below,
+    and the builder form `AutoTuner.from_kernel(kernel=fn, configs=[...]).set_compile_args(...)
+    .set_profile_args(...).run(warmup, rep)` (examples/gemm/example_gemm_autotune.py:149-158) where `fn(**config)`
+    returns a @T.prim_func and `run` returns an AutotuneResult."""
 
     def __init__(self, jit_impl, configs, warmup=25, rep=100, timeout=100, supply_type=None, ref_prog=None,
                  supply_prog=None, rtol=1e-2, atol=1e-2, max_mismatched_ratio=0.01, skip_check=False,
@@ -31,10 +47,40 @@ class AutoTuner:
         self.ref_prog, self.skip_check, self.rtol, self.atol = ref_prog, skip_check, rtol, atol
         self.max_mismatched_ratio = max_mismatched_ratio
         self._cache = {}
+        self._compile_args = {}
+
+    @classmethod
+    def from_kernel(cls, kernel: Callable, configs):
+        return cls(kernel, configs)
+
+    def set_compile_args(self, out_idx=None, target="auto", execution_backend="auto", target_host=None, verbose=False,
+                         pass_configs=None):
+        self._compile_args = dict(out_idx=out_idx, target=target, execution_backend=execution_backend,
+                                  target_host=target_host, verbose=verbose, pass_configs=pass_configs)
+        return self
+
+    def set_profile_args(self, warmup=25, rep=100, timeout=30, supply_type=None, ref_prog=None, supply_prog=None,
+                         rtol=1e-2, atol=1e-2, max_mismatched_ratio=0.01, skip_check=False, manual_check_prog=None,
+                         cache_input_tensors=False):
+        self.warmup, self.rep, self.ref_prog, self.skip_check = warmup, rep, ref_prog, skip_check
+        self.rtol, self.atol, self.max_mismatched_ratio = rtol, atol, max_mismatched_ratio
+        return self
+
+    def _as_jit(self):
+        from ..jit import JITImpl, jit
+        if not isinstance(self.jit_impl, JITImpl):
+            self.jit_impl = jit(self.jit_impl, **self._compile_args)
+        return self.jit_impl
+
+    def run(self, warmup: int = 25, rep: int = 100, timeout: int = 30) -> AutotuneResult:
+        """Builder form (tuner.py:288): the kernel function takes only tunables."""
+        self.warmup, self.rep = warmup, rep
+        k = self._tune((), {})
+        return AutotuneResult(latency=k.latency, config=k.config, ref_latency=k.ref_latency, func=k.prim_func, kernel=k)
 
     def _first_valid(self, args, kwargs):
         cfgs = self.configs(args, kwargs) if callable(self.configs) else list(self.configs)
-        sig = self.jit_impl.signature
+        sig = self._as_jit().signature
         last = None
         for cfg in cfgs:
             try:
@@ -45,7 +91,7 @@ class AutoTuner:
                 last = e
         raise RuntimeError(f"autotune: no config yields a valid GEMM tile program (last error: {last})")
 
-    def run(self, *args, **kwargs):
+    def _tune(self, args, kwargs):
         key = (args, tuple(sorted(kwargs.items())))
         if key in self._cache:
             return self._cache[key]
@@ -73,6 +119,8 @@ class AutoTuner:
                     prof.assert_allclose(self.ref_prog, input_tensors=ins, rtol=self.rtol, atol=self.atol,
                                          max_mismatched_ratio=self.max_mismatched_ratio)
             kernel.update_tuner_result(best, dict(cfg, backend_plan=best_hints), ref_lat)
+        else:
+            kernel.update_tuner_result(None, dict(cfg), None)
         self._cache[key] = kernel
         return kernel
 
@@ -89,7 +137,7 @@ def autotune(func: Optional[Callable] = None, *, configs=None, warmup: int = 25,
                           max_mismatched_ratio, skip_check, manual_check_prog, cache_input_tensors)
 
         def wrapper(*args, **kwargs):
-            return tuner.run(*args, **kwargs)
+            return tuner._tune(args, kwargs)
 
         wrapper.__name__ = getattr(jit_impl, "__name__", "autotuned")
         wrapper.tuner, wrapper.jit_impl = tuner, jit_impl

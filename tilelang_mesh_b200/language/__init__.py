@@ -20,7 +20,7 @@ from .expr import BinOp, Call, Const, Expr, Var, as_affine, evaluate, is_const, 
 
 __all__ = [
     "prim_func", "Tensor", "StridedTensor", "Buffer", "Kernel", "alloc_shared", "alloc_fragment", "alloc_local",
-    "alloc_tmem", "alloc_barrier", "Pipelined", "Parallel", "serial", "grid", "unroll", "copy", "gemm", "gemm_v1",
+    "alloc_tmem", "alloc_barrier", "Pipelined", "Persistent", "Parallel", "serial", "grid", "unroll", "copy", "gemm", "gemm_v1",
     "gemm_v2", "clear", "fill", "use_swizzle", "annotate_layout", "mbarrier_wait_parity", "max", "min", "ceildiv",
     "GemmWarpPolicy", "dynamic", "symbolic", "float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2", "int32",
 ]
@@ -128,7 +128,8 @@ class TileBuffer:
 
     def __setitem__(self, idx, value):
         tr = _current_trace()
-        tr.ops.append(ElemStore(self, idx if isinstance(idx, tuple) else (idx,), value, tuple(tr.parallel_vars)))
+        tr.ops.append(ElemStore(self, idx if isinstance(idx, tuple) else (idx,), value, tuple(tr.parallel_vars),
+                                tr.current_loop))
 
     def __repr__(self):
         return f"{self.name}<{self.scope} {self.shape} {self.dtype}>"
@@ -185,6 +186,7 @@ class ElemStore:
     index: Tuple
     value: Any
     parallel_vars: Tuple
+    loop: Optional[Var] = None
 
 
 @dataclass
@@ -210,6 +212,7 @@ class Trace:
     in_parallel: bool = False
     parallel_vars: List[Var] = field(default_factory=list)
     in_kernel: bool = False
+    persistent: Optional[dict] = None
 
     @property
     def current_loop(self) -> Optional[Var]:
@@ -342,8 +345,25 @@ def serial(start, stop=None, step=None, **_):
 unroll = serial
 
 
+def Persistent(domain, wave_size, index, group_size=8):  # noqa: N802
+    """tilelang/language/loop.py:35-54: `for bx, by in T.Persistent([tiles_m, tiles_n], sm_num, block_id)` walks the
+    tile domain with `wave_size` resident blocks (examples/gemm/example_gemm_persistent.py:100-101).  The B200 kernel
+    is persistent by construction, so the loop variables simply become the tile indices of the program."""
+    tr = _current_trace()
+    if tr.persistent is not None:
+        raise NotImplementedError("more than one T.Persistent loop")
+    if not any(index is bv for bv in tr.block_vars):
+        raise NotImplementedError("T.Persistent: `index` must be the T.Kernel block index")
+    names = ["bx", "by", "bz"]
+    vs = tuple(Var("p" + names[i] if i < 3 else f"pb{i}", "block", e) for i, e in enumerate(domain))
+    tr.persistent = dict(domain=tuple(domain), wave_size=wave_size, group_size=group_size)
+    tr.block_vars = tuple(tr.block_vars) + vs
+    yield vs[0] if len(vs) == 1 else vs
+
+
 def Parallel(*extents, coalesced_width=None):  # noqa: N802
-    """tilelang/language/loop.py:12.  Only recognised as an element-wise epilogue over a tile."""
+    """tilelang/language/loop.py:12.  Recognised as an element-wise epilogue over the accumulator tile, or as an
+    element-wise global->shared staging loop (examples/gemm/example_gemm_schedule.py:21-22)."""
     tr = _current_trace()
     vs = tuple(Var(f"p{i}", "parallel", e) for i, e in enumerate(extents))
     tr.in_parallel, tr.parallel_vars = True, list(vs)

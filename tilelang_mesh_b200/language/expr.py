@@ -143,3 +143,30 @@ def as_affine(e) -> Optional[Tuple[Optional[Var], int, int]]:
                 return (rv, rs * lo, ro * lo)
             return (lv, ls * ro, lo * ro)
     return None
+
+
+def as_linear(e) -> Optional[Tuple[Dict[Var, int], int]]:
+    """Match `sum_i var_i * c_i + offset` over any number of variables.  Returns ({var: c}, offset)."""
+    if isinstance(e, (bool, int)):
+        return ({}, int(e))
+    if isinstance(e, Const):
+        return ({}, int(e.value)) if isinstance(e.value, (bool, int)) else None
+    if isinstance(e, Var):
+        return ({e: 1}, 0)
+    if isinstance(e, BinOp):
+        l, r = as_linear(e.a), as_linear(e.b)
+        if l is None or r is None:
+            return None
+        (lt, lo), (rt, ro) = l, r
+        if e.op in "+-":
+            sign = 1 if e.op == "+" else -1
+            out = dict(lt)
+            for v, c in rt.items():
+                out[v] = out.get(v, 0) + sign * c
+            return ({v: c for v, c in out.items() if c != 0}, lo + sign * ro)
+        if e.op == "*":
+            if lt and rt:
+                return None
+            terms, scale, off = (rt, lo, ro) if not lt else (lt, ro, lo)
+            return ({v: c * scale for v, c in terms.items() if c * scale != 0}, off * scale)
+    return None

@@ -22,7 +22,7 @@ from dataclasses import dataclass, field
 from typing import Dict, List, Optional
 
 from . import language as T
-from .language.expr import BinOp, Call, Const, Expr, Var, as_affine, is_const
+from .language.expr import BinOp, Call, Const, Expr, Var, as_affine, as_linear, is_const
 
 
 @dataclass
@@ -82,6 +82,35 @@ def _tile_origin(region, want_vars: Dict[str, Var], what: str):
     return out
 
 
+def _elementwise_staging(o, nm):
+    """`for i, j in T.Parallel(bR, bC): X_shared[i, j] = X[r0 + i, c0 + j]` is a staging copy written element by
+    element (examples/gemm/example_gemm_schedule.py:21-22); rewrite it as the T.copy it means."""
+    tile, src = o.buffer, o.value
+    pv = tuple(o.parallel_vars)
+    if len(o.index) != len(pv) or any(i is not v for i, v in zip(o.index, pv)):
+        _fail(f"element-wise fill of {nm}_shared must index the tile with the T.Parallel variables in order")
+    if tuple(v.extent for v in pv) != tuple(tile.shape):
+        _fail(f"element-wise fill of {nm}_shared does not cover the tile {tile.shape}")
+    if len(src.starts) != len(pv):
+        _fail(f"element-wise fill of {nm}_shared reads a {len(src.starts)}-D element of {src.buffer.name}")
+    starts = []
+    for d, s in enumerate(src.starts):
+        lin = as_linear(s)
+        if lin is None:
+            _fail(f"element-wise fill of {nm}_shared: index {s!r} is not linear")
+        terms, off = lin
+        if terms.pop(pv[d], 0) != 1 or any(v in terms for v in pv):
+            _fail(f"element-wise fill of {nm}_shared: dimension {d} of {src.buffer.name} must be origin + "
+                  f"{pv[d]!r} (got {s!r})")
+        if len(terms) > 1:
+            _fail(f"element-wise fill of {nm}_shared: origin {s!r} mixes several indices")
+        base = off
+        for v, c in terms.items():
+            base = v * c + off
+        starts.append(base)
+    return T.CopyOp(T.BufferRegion(src.buffer, starts, tile.shape), tile, o.loop)
+
+
 def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     tr = func.trace()
     if not tr.in_kernel:
@@ -117,6 +146,8 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     # ---- staging copies: global -> A_shared / B_shared inside the K loop
     def staging(tile, nm):
         cs = [o for o in tr.ops if isinstance(o, T.CopyOp) and _buf(o.dst) is tile]
+        cs += [_elementwise_staging(o, nm) for o in tr.ops
+               if isinstance(o, T.ElemStore) and o.buffer is tile and isinstance(o.value, T.BufferRegion)]
         if len(cs) != 1:
             _fail(f"expected one T.copy into {nm}_shared, found {len(cs)}")
         c = cs[0]
@@ -277,13 +308,20 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
         if C_g.dtype == "int32" and alpha != 1.0:
             _fail("scaled int32 output")
     else:
-        if C_acc.dtype != "float32":
+        if C_acc.dtype == "float16" and A_s.dtype in ("float16", "float8_e4m3", "float8_e5m2"):
+            # The reference lets these operand types accumulate in fp16 (src/op/tcgen5_meta.h:45-58,
+            # examples/gemm_fp8/example_tilelang_gemm_fp8_sm100.py:76).  This backend keeps the fp32
+            # accumulator and rounds once on the way out: closer to the exact product, same output dtype.
+            pass
+        elif C_acc.dtype != "float32":
             _fail(f"accumulator dtype {C_acc.dtype}: the tcgen05 path accumulates in fp32 "
-                  "(north_star; reference allows fp16 accumulate for fp8 only, tcgen5_meta.h:56-58)")
+                  "(north_star; the reference allows fp16 accumulate for fp16/fp8 operands only, tcgen5_meta.h:45-58)")
         if C_g.dtype not in ("float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2"):
             _fail(f"output dtype {C_g.dtype}")
 
     notes = []
+    if C_acc.dtype == "float16":
+        notes.append("accum_dtype float16 widened to float32 (single rounding to the output dtype)")
     if g.wg_wait not in (0, -1):
         notes.append(f"wg_wait={g.wg_wait} ignored (MMA completion is tracked by the kernel's own mbarriers)")
     return GemmProgram(M=M, N=N, K=K, in_dtype=A_s.dtype, out_dtype=C_g.dtype, accum_dtype=C_acc.dtype,
