@@ -150,6 +150,43 @@ int tlb200_gemm_grouped(const tlb200_gemm_desc* desc, const void* a, const void*
 int tlb200_gemm_bcast(const tlb200_gemm_desc* desc, const void* a, const void* b, void* const* c_list,
                       int n_c, void* stream);
 
+/* fp8 contraction with fine-grained scales ("2x accumulation"):
+ *
+ *   C[m, n] = sum_kb scales_a[m, kb] * scales_b[n / 128, kb]
+ *                    * sum_{k in [128 kb, 128 kb + 128)} A[m, k] * B[n, k]
+ *
+ * Replaces the tile program of examples/deepseek_deepgemm/
+ * example_deepgemm_fp8_2xAcc.py:12-83 (`tl_gemm`): A[M, K] and B[N, K] fp8,
+ * K-contiguous; scales_a one fp32 per (row, 128-wide K block), shape
+ * (M, ceil(K/128)) (:34); scales_b one fp32 per (128-row block of B, K block),
+ * shape (ceil(N/128), ceil(K/128)) (:36); the partial sum of every K block is
+ * multiplied by scales_a * scales_b (the product is rounded to fp32 first, as
+ * the program's Scale_C_shared, :71-73) and added to an fp32 accumulator
+ * (:77-78); one rounding to c_dtype at the end (bfloat16 / float16 / float32;
+ * the reference asserts bfloat16 or float32, :24-27).  Scale tensors are
+ * addressed through element strides so both the row-major layout of the
+ * example and DeepGEMM's M-contiguous layout work.  group_k and group_n must
+ * be 128 (the reference's group_size, :29).  cfg_* = 0 selects the default
+ * plan (2-CTA pairs, 256-wide tiles). */
+typedef struct tlb200_blockscaled_desc {
+  int32_t abi_version; /* must be TLB200_ABI_VERSION */
+  int32_t m, n, k;
+  int32_t ab_dtype; /* TLB200_FLOAT8_E4M3 or TLB200_FLOAT8_E5M2 */
+  int32_t c_dtype;  /* TLB200_BFLOAT16, TLB200_FLOAT16 or TLB200_FLOAT32 */
+  int32_t group_n, group_k; /* 128, 128 */
+  int64_t lda, ldb, ldc;    /* row pitches in elements */
+  int64_t sa_stride_m, sa_stride_k; /* scales_a[m, kb] = scales_a[m*sa_stride_m + kb*sa_stride_k] */
+  int64_t sb_stride_n, sb_stride_k; /* scales_b[nb, kb] likewise */
+  int32_t cfg_cta_group; /* 0 auto, 1, 2 */
+  int32_t cfg_block_n;   /* 0 auto, 128, 256 */
+  int32_t cfg_stages;    /* 0 auto */
+  int32_t cfg_raster;    /* 0 auto */
+  int32_t reserved[4];
+} tlb200_blockscaled_desc;
+
+int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* desc, const void* a, const void* b, void* c,
+                            const float* scales_a, const float* scales_b, void* stream);
+
 /* No counterpart in the reference: an allocation-free form of tlb200_gemm_ex.
  *
  * Who needs it: callers that are handed tensor pointers and a stream and nothing

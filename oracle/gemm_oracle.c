@@ -156,3 +156,33 @@ int oracle_gemm(int m, int n, int k, int ab_dtype, int c_dtype, int trans_a, int
   }
   return 0;
 }
+
+/* fp8 contraction with fine-grained scales, the tile program of
+ * examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:43-83 restated per output element:
+ *   for every 128-wide K block kb:  partial = sum_k A[i,k]*B[j,k]        (T.gemm into a cleared C_local, :75,79)
+ *                                   scale   = scales_a[i,kb] * scales_b[j/128,kb]   (Scale_C_shared, :71-73)
+ *                                   acc    += partial * scale            (C_local_accum, :77-78; nvcc contracts
+ *                                                                         the multiply-add into one fmaf)
+ * A is [m,k], B is [n,k] (transpose_B=True, :75); scales are fp32 with element strides. */
+#include <math.h>
+int oracle_gemm_blockscaled(int m, int n, int k, int ab_dtype, int c_dtype, const void* A, long long lda, const void* B,
+                            long long ldb, void* C, long long ldc, const float* sa, long long sa_sm, long long sa_sk,
+                            const float* sb, long long sb_sn, long long sb_sk) {
+  if (m < 0 || n < 0 || k < 0 || (ab_dtype != 2 && ab_dtype != 3) || c_dtype < 0 || c_dtype > 4) return -1;
+  const int nkb = (k + 127) / 128;
+  for (int i = 0; i < m; ++i) {
+    for (int j = 0; j < n; ++j) {
+      float acc = 0.f;
+      for (int kb = 0; kb < nkb; ++kb) {
+        float partial = 0.f;
+        const int k1 = (kb + 1) * 128 < k ? (kb + 1) * 128 : k;
+        for (int kk = kb * 128; kk < k1; ++kk)
+          partial += oracle_decode(ab_dtype, A, (long long)i * lda + kk) * oracle_decode(ab_dtype, B, (long long)j * ldb + kk);
+        const float scale = sa[i * sa_sm + kb * sa_sk] * sb[(j / 128) * sb_sn + kb * sb_sk];
+        acc = fmaf(partial, scale, acc);
+      }
+      oracle_encode(c_dtype, C, (long long)i * ldc + j, acc);
+    }
+  }
+  return 0;
+}

@@ -72,6 +72,37 @@ def c_oracle_gemm(a: torch.Tensor, b: torch.Tensor, out_dtype: torch.dtype, tran
     return c
 
 
+def c_oracle_gemm_blockscaled(a: torch.Tensor, b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor,
+                              out_dtype: torch.dtype) -> torch.Tensor:
+    """Scalar C oracle of the fine-grained-scale fp8 contraction (small sizes only)."""
+    a, b = a.detach().cpu().contiguous(), b.detach().cpu().contiguous()
+    sa, sb = scales_a.detach().cpu().float().contiguous(), scales_b.detach().cpu().float().contiguous()
+    m, k = a.shape
+    n = b.shape[0]
+    c = torch.empty((m, n), dtype=out_dtype)
+    fn = _c().oracle_gemm_blockscaled
+    fn.argtypes = [ctypes.c_int] * 5 + [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong,
+                                        ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong,
+                                        ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_longlong]
+    fn.restype = ctypes.c_int
+    rc = fn(m, n, k, DT[a.dtype], DT[out_dtype], a.data_ptr(), max(k, 1), b.data_ptr(), max(k, 1), c.data_ptr(), n,
+            sa.data_ptr(), sa.stride(0) if sa.numel() else 0, 1, sb.data_ptr(), sb.stride(0) if sb.numel() else 0, 1)
+    if rc != 0:
+        raise ValueError("oracle_gemm_blockscaled: bad arguments")
+    return c
+
+
+def blockscaled_fp32(a: torch.Tensor, b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor) -> torch.Tensor:
+    """The same contraction in fp32 torch ops (any size): dequantise, then one fp32 matmul.  Equal to the
+    oracle up to fp32 summation order; this is what the reference's checker computes per 128x128 block with
+    torch._scaled_mm (example_deepgemm_fp8_2xAcc.py:109-135), without its bf16 rounding of every partial."""
+    m, k = a.shape
+    n = b.shape[0]
+    af = a.float() * scales_a.float().repeat_interleave(128, dim=1)[:, :k]
+    bf = b.float() * scales_b.float().repeat_interleave(128, dim=0)[:n].repeat_interleave(128, dim=1)[:, :k]
+    return af @ bf.t()
+
+
 def matmul_fp32(a: torch.Tensor, b: torch.Tensor, trans_a=False, trans_b=True, alpha: float = 1.0,
                 relu: bool = False) -> torch.Tensor:
     """fp32 reference result (not yet cast to the output type)."""

@@ -223,6 +223,8 @@ def test_scaled_epilogue_and_partial_k_loop_rejected():
     ("examples/gemm/example_gemm_autotune.py", "\ndef main(M", "get_best_config(1024, 1024, 1024, False).kernel"),
     ("examples/gemm/example_gemm_persistent.py", "def ref_program",
      "matmul_non_persistent(1024, 1024, 1024, 128, 256, 32, 128, 3)"),
+    ("examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py", "def ceildiv",
+     'tl_gemm(1024, 1024, 8192, 64, "float8_e4m3", "bfloat16", "float32")'),
     ("benchmark/matmul/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
     ("benchmark/matmul_fp8/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
 ])
@@ -314,3 +316,23 @@ def test_autotuner_builder_form_and_carver_names():
         MatmulTemplate(M=512, N=512, K=256, in_dtype="float16", out_dtype="float16", accum_dtype="float")
     with pytest.raises(NotImplementedError):
         CUDA("cuda")
+
+
+def test_blockscaled_2xacc_program_family():
+    from tilelang_mesh_b200.program import BlockScaledProgram
+    for bn, swap in ((128, False), (64, True), (16, False)):
+        k = tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, bn, "float32", swap_scale_operands=swap))
+        p = k.program
+        assert isinstance(p, BlockScaledProgram) and (p.M, p.N, p.K) == (512, 384, 1024)
+        assert (p.a_param, p.b_param, p.c_param, p.sa_param, p.sb_param) == (0, 1, 2, 3, 4)
+        assert [tuple(kp.shape) for kp in k.params] == [(512, 1024), (384, 1024), (512, 384), (512, 8), (3, 8)]
+        assert "tcgen05" in k.get_kernel_source() and k.plan()["block_k"] == 128
+    # the scale group is the K block: any other block_K changes which products share a scale
+    with pytest.raises(NotAGemmProgram, match="block_K must equal the scale group"):
+        tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, 128, bK=64))
+    with pytest.raises(NotAGemmProgram, match="block_N must divide"):
+        tilelang.compile(P.blockscaled_2xacc(512, 512, 1024, 256))
+    with pytest.raises(NotAGemmProgram, match="fp8"):
+        tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, 128, in_dtype="float16"))
+    with pytest.raises(NotAGemmProgram, match="scales_b must be indexed"):
+        tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, 128, group=64))

@@ -141,6 +141,22 @@ def test_autotuner_builder_form():
     torch.testing.assert_close(res.kernel(a, b), a @ b.T, rtol=1e-2, atol=1e-2)
 
 
+def test_blockscaled_2xacc_program_through_the_facade():
+    # examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:139-172: kernel(A_fp8, B_fp8, C, A_scale, B_scale)
+    M, N, K = 1024, 1024, 8192
+    for bn, out, tdt in ((128, "bfloat16", torch.bfloat16), (32, "float32", torch.float32)):
+        kern = tilelang.compile(P.blockscaled_2xacc(M, N, K, bn, out))
+        torch.manual_seed(42)
+        a = torch.randn(M, K, device="cuda").to(torch.float8_e4m3fn)
+        b = torch.randn(N, K, device="cuda").to(torch.float8_e4m3fn)
+        sa = torch.rand(M, K // 128, device="cuda") + 0.5
+        sb = torch.rand(N // 128, K // 128, device="cuda") + 0.5
+        c = torch.zeros(M, N, device="cuda", dtype=tdt)
+        assert kern(a, b, c, sa, sb) is None
+        assert R.calc_diff(c.float(), R.blockscaled_fp32(a, b, sa, sb)) < 1e-5  # reference bar: < 1e-3
+        assert kern.get_profiler().do_bench(warmup=5, rep=10) > 0
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

@@ -109,6 +109,21 @@ def test_untouched_outside_of_c_window():
         assert (big[:, n:] == -7).all() and (big[m:] == -7).all()
 
 
+@pytest.mark.parametrize("dt,n,pad", [(torch.bfloat16, 500, 12), (torch.float16, 1001, 7), (torch.float32, 333, 3),
+                                      (torch.float32, 334, 6), (torch.bfloat16, 250, 6), (torch.float8_e4m3fn, 1000, 24)])
+def test_padding_right_of_c_untouched_when_row_bytes_not_16_aligned(dt, n, pad):
+    # TMA stores clip at the last column only in whole 16-byte units: such rows must take the predicated stores
+    m, k = 300, 256
+    a, b = operands(m, n, k, torch.bfloat16, kind="int")
+    big = torch.full((m, n + pad), -1.0, device="cuda", dtype=torch.float32).to(dt)
+    G.gemm(a, b, big[:, :n], alpha=2.0 ** -6)
+    assert (big[:, n:].float() == -1).all()
+    want = ((a.float() @ b.float().t()) * 2.0 ** -6).to(dt)
+    assert torch.equal(big[:, :n].float(), want.float())
+    with pytest.raises(RuntimeError, match="row length"):
+        G.gemm(a, b, big[:, :n], epilogue=2)
+
+
 def test_strided_operands():
     m, n, k = 160, 192, 128
     abig = rand((m, k + 64), torch.bfloat16, "int")

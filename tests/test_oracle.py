@@ -131,3 +131,27 @@ def test_c_oracle_integer_inputs_exact():
     b = torch.randint(-3, 4, (24, 64)).float().bfloat16()
     got = R.c_oracle_gemm(a, b, torch.float32)
     assert torch.equal(got, a.float() @ b.float().t())
+
+
+def test_c_oracle_blockscaled_known_answer_and_identity():
+    # examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:43-83 restated.  Known answer by hand: with
+    # A = B = all ones, block kb contributes 128 * sa[m,kb] * sb[n//128,kb] (last block: K - 128*kb ones).
+    m, n, k = 3, 130, 300
+    a = torch.ones(m, k).to(torch.float8_e4m3fn)
+    b = torch.ones(n, k).to(torch.float8_e4m3fn)
+    sa = torch.tensor([[1.0, 2.0, 4.0], [0.5, 0.5, 0.5], [0.0, 1.0, 0.0]])
+    sb = torch.tensor([[1.0, 1.0, 1.0], [2.0, 0.0, 0.25]])
+    c = R.c_oracle_gemm_blockscaled(a, b, sa, sb, torch.float32)
+    cnt = torch.tensor([128.0, 128.0, 44.0])
+    want = torch.stack([(sa * sb[0] * cnt).sum(1), (sa * sb[1] * cnt).sum(1)], dim=1)  # [m, 2 column blocks]
+    assert torch.equal(c[:, :128], want[:, :1].expand(m, 128)) and torch.equal(c[:, 128:], want[:, 1:].expand(m, 2))
+    # random operands: equal to dequantise-then-matmul up to fp32 summation order
+    g = torch.Generator().manual_seed(1)
+    a = torch.randn(40, 384, generator=g).to(torch.float8_e4m3fn)
+    b = torch.randn(140, 384, generator=g).to(torch.float8_e5m2).float().to(torch.float8_e4m3fn)
+    sa = torch.rand(40, 3, generator=g) + 0.5
+    sb = torch.rand(2, 3, generator=g) + 0.5
+    c = R.c_oracle_gemm_blockscaled(a, b, sa, sb, torch.float32)
+    torch.testing.assert_close(c, R.blockscaled_fp32(a, b, sa, sb), rtol=1e-4, atol=1e-4)
+    cb = R.c_oracle_gemm_blockscaled(a, b, sa, sb, torch.bfloat16)
+    assert torch.equal(cb, c.bfloat16())

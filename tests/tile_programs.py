@@ -117,3 +117,40 @@ def persistent_primitive(M, N, K, bM=128, bN=256, bK=64, dtype="bfloat16", waves
                 T.copy(c_s, C[tx * bM, ty * bN])
 
     return prog
+
+
+def blockscaled_2xacc(M, N, K, bN=128, out_dtype="bfloat16", in_dtype="float8_e4m3", bM=128, bK=128, group=128,
+                      swap_scale_operands=False):
+    """fp8 contraction with per-(row, 128 K) and per-(128 N, 128 K) scales, promoted every K block
+    (the form of examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:43-83)."""
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), in_dtype), B: T.Tensor((N, K), in_dtype), C: T.Tensor((M, N), out_dtype),
+             sa: T.Tensor((M, T.ceildiv(K, group)), "float32"),
+             sb: T.Tensor((T.ceildiv(N, group), T.ceildiv(K, group)), "float32")):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=128) as (bx, by):
+            a_s = T.alloc_shared((bM, bK), in_dtype)
+            b_s = T.alloc_shared((bN, bK), in_dtype)
+            c_s = T.alloc_shared((bM, bN), out_dtype)
+            row_scale = T.alloc_shared((bM,), "float32")
+            part = T.alloc_fragment((bM, bN), "float32")
+            acc = T.alloc_fragment((bM, bN), "float32")
+            T.clear(part)
+            T.clear(acc)
+            for k in T.Pipelined(T.ceildiv(K, bK), num_stages=4):
+                T.copy(A[by * bM, k * bK], a_s)
+                T.copy(B[bx * bN, k * bK], b_s)
+                s_b = sb[bx * bN // group, k]
+                for i in T.Parallel(bM):
+                    if swap_scale_operands:
+                        row_scale[i] = s_b * sa[by * bM + i, k]
+                    else:
+                        row_scale[i] = sa[by * bM + i, k] * s_b
+                T.gemm(a_s, b_s, part, transpose_B=True)
+                for i, j in T.Parallel(bM, bN):
+                    acc[i, j] += part[i, j] * row_scale[i]
+                T.clear(part)
+            T.copy(acc, c_s)
+            T.copy(c_s, C[by * bM, bx * bN])
+
+    return prog

@@ -74,6 +74,16 @@ class GemmPlan(ctypes.Structure):
 
 
 # Every symbol include/tlb200.h declares: (restype, argtypes)
+class BlockScaledDesc(ctypes.Structure):
+    """tlb200_blockscaled_desc (include/tlb200.h)."""
+    _fields_ = [("abi_version", ctypes.c_int32), ("m", ctypes.c_int32), ("n", ctypes.c_int32), ("k", ctypes.c_int32),
+                ("ab_dtype", ctypes.c_int32), ("c_dtype", ctypes.c_int32), ("group_n", ctypes.c_int32),
+                ("group_k", ctypes.c_int32), ("lda", ctypes.c_int64), ("ldb", ctypes.c_int64), ("ldc", ctypes.c_int64),
+                ("sa_stride_m", ctypes.c_int64), ("sa_stride_k", ctypes.c_int64), ("sb_stride_n", ctypes.c_int64),
+                ("sb_stride_k", ctypes.c_int64), ("cfg_cta_group", ctypes.c_int32), ("cfg_block_n", ctypes.c_int32),
+                ("cfg_stages", ctypes.c_int32), ("cfg_raster", ctypes.c_int32), ("reserved", ctypes.c_int32 * 4)]
+
+
 SYMBOLS = {
     "tlb200_init": (ctypes.c_int, [ctypes.c_int]),
     "tlb200_gemm": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
@@ -85,6 +95,8 @@ SYMBOLS = {
                                            ctypes.POINTER(ctypes.c_int32), ctypes.c_int, ctypes.c_void_p]),
     "tlb200_gemm_bcast": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                          ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_void_p]),
+    "tlb200_gemm_blockscaled": (ctypes.c_int, [ctypes.POINTER(BlockScaledDesc), ctypes.c_void_p, ctypes.c_void_p,
+                                               ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "tlb200_gemm_static_scratch": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                                   ctypes.c_void_p, ctypes.c_void_p]),
     "tlb200_gemm_host_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),

@@ -16,7 +16,7 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB_DIR = os.path.join(_HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libtlb200.so")
 SOURCES = [os.path.join(CSRC, "tlb200.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, f) for f in ("gemm_sm100.cuh", "ptx.cuh")] + [
+DEPS = SOURCES + [os.path.join(CSRC, f) for f in ("gemm_sm100.cuh", "gemm_blockscaled_sm100.cuh", "ptx.cuh")] + [
     os.path.join(ROOT, "include", "tlb200.h")]
 
 

@@ -89,14 +89,17 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // body runs rarely; the watchdog converts a protocol deadlock into a trap (launch error)
 // instead of a hung GPU.  `tag` identifies the waiting role in the diagnostic.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag) {
-  if (mbar_try_wait(bar, parity)) return;
-  uint64_t t0 = globaltimer_ns();
+  uint64_t t0 = 0;
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3ffu) == 0 && globaltimer_ns() - t0 > TLB200_WATCHDOG_NS) {
-      printf("tlb200 watchdog: block %d thread %d tag %d bar 0x%x parity %u\n", (int)blockIdx.x,
-             (int)threadIdx.x, tag, bar, parity);
-      __trap();
+    if ((++spins & 0x3ffu) == 0) {  // the timer is read only after ~1000 failed polls: %globaltimer is slow
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > TLB200_WATCHDOG_NS) {
+        printf("tlb200 watchdog: block %d thread %d tag %d bar 0x%x parity %u\n", (int)blockIdx.x,
+               (int)threadIdx.x, tag, bar, parity);
+        __trap();
+      }
     }
   }
 }

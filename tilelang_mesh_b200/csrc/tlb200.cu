@@ -13,6 +13,7 @@
 #include <cstring>
 #include <mutex>
 
+#include "gemm_blockscaled_sm100.cuh"
 #include "gemm_sm100.cuh"
 
 namespace {
@@ -310,11 +311,15 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.smem_bytes = kSmemFixed + stages * per_stage;
   p.raster = d->cfg_raster > 0 ? d->cfg_raster : ((bn > 256 || r->es == 1) ? 16 : 16 / cg);
   int epi = d->cfg_epilogue;
-  const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0);
+  // A TMA store clips at the tensor's last column only in whole 16-byte units (measured: tools/pad_probe.py), so a
+  // row whose byte length is not a multiple of 16 must take the predicated stores or the cells right of column n
+  // in a padded C would be overwritten.
+  const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0) &&
+                      ((static_cast<long long>(d->n) * r->ob) % 16 == 0);
   // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
   const bool slab_ok = (r->umma_n / (r->epi_warps / 4)) % (128 / r->ob) == 0;
   if (epi == 0) epi = (tma_ok && slab_ok) ? 2 : 1;
-  if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C and row pitch");
+  if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C, row pitch and row length (n * element size)");
   if (epi == 2 && !slab_ok)
     return fail("tlb200: TMA-store epilogue needs block_n (%d) to be a multiple of %d for %d-byte outputs", bn, 128 / r->ob, r->ob);
   if (epi != 1 && epi != 2) return fail("tlb200: cfg_epilogue must be 0, 1 or 2");
@@ -487,6 +492,12 @@ std::array<const void*, 16> all_kernels() {
   return k;
 }
 
+typedef void (*BlockScaledFn)(const BlockScaledParams);
+BlockScaledFn pick_blockscaled(int cg, int bn) {
+  if (cg == 2) return bn == 128 ? gemm_blockscaled_kernel<2, 128> : gemm_blockscaled_kernel<2, 256>;
+  return bn == 128 ? gemm_blockscaled_kernel<1, 128> : gemm_blockscaled_kernel<1, 256>;
+}
+
 int out_kind_of(int dt) {
   switch (dt) {
     case TLB200_FLOAT16: return kOutF16;
@@ -626,6 +637,10 @@ int tlb200_init(int device) {
     for (const void* fn : all_kernels()) {
       if ((e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit)) != cudaSuccess) break;
     }
+    for (int cg = 1; cg <= 2 && e == cudaSuccess; ++cg)
+      for (int bn = 128; bn <= 256 && e == cudaSuccess; bn += 128)
+        e = cudaFuncSetAttribute(reinterpret_cast<const void*>(pick_blockscaled(cg, bn)),
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (e != cudaSuccess) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
@@ -866,6 +881,116 @@ int tlb200_gemm_ex(const tlb200_gemm_desc* d, const void* a, const void* b, void
                    void* stream_v) {
   if (ws && ws_bytes < 0) return fail("tlb200_gemm_ex: negative workspace size");
   return gemm_impl(d, a, b, c, ws, ws_bytes, stream_v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp8 contraction with per-(row, 128-K) x per-(128-N, 128-K) scales (gemm_blockscaled_sm100.cuh).
+int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* d, const void* a, const void* b, void* c,
+                            const float* scales_a, const float* scales_b, void* stream_v) {
+  g_err[0] = 0;
+  if (!d) return fail("tlb200_gemm_blockscaled: null descriptor");
+  if (d->abi_version != TLB200_ABI_VERSION)
+    return fail("tlb200_gemm_blockscaled: descriptor abi_version %d != library %d", d->abi_version, TLB200_ABI_VERSION);
+  if (d->m < 0 || d->n < 0 || d->k < 0) return fail("tlb200_gemm_blockscaled: negative shape %dx%dx%d", d->m, d->n, d->k);
+  if (d->ab_dtype != TLB200_FLOAT8_E4M3 && d->ab_dtype != TLB200_FLOAT8_E5M2)
+    return fail("tlb200_gemm_blockscaled: operands must be float8_e4m3 or float8_e5m2 (got dtype %d)", d->ab_dtype);
+  if (d->c_dtype != TLB200_BFLOAT16 && d->c_dtype != TLB200_FLOAT16 && d->c_dtype != TLB200_FLOAT32)
+    return fail("tlb200_gemm_blockscaled: output must be bfloat16, float16 or float32 (got dtype %d)", d->c_dtype);
+  if (d->group_n != 128 || d->group_k != 128)
+    return fail("tlb200_gemm_blockscaled: scale groups must be 128 x 128 (got group_n=%d group_k=%d)", d->group_n, d->group_k);
+  if (d->m == 0 || d->n == 0) return 0;
+  if (!c) return fail("tlb200_gemm_blockscaled: null C");
+  if (d->ldc < d->n) return fail("tlb200_gemm_blockscaled: ldc %lld < n %d", (long long)d->ldc, d->n);
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  const int ob = dtype_bytes(d->c_dtype);
+  const int out_kind = out_kind_of(d->c_dtype);
+  if (d->k == 0) {  // empty sum
+    cudaError_t e = cudaMemset2DAsync(c, static_cast<size_t>(d->ldc) * ob, 0, static_cast<size_t>(d->n) * ob, d->m, stream);
+    if (e != cudaSuccess) return fail("tlb200_gemm_blockscaled: clearing C: %s", cudaGetErrorString(e));
+    return 0;
+  }
+  if (!a || !b || !scales_a || !scales_b) return fail("tlb200_gemm_blockscaled: null operand or scale pointer");
+  if (d->lda < d->k || d->ldb < d->k)
+    return fail("tlb200_gemm_blockscaled: lda %lld / ldb %lld smaller than k %d", (long long)d->lda, (long long)d->ldb, d->k);
+  // TMA needs 16-byte aligned bases and row pitches (copy.cc:1489-1499); there is no staging copy on this path.
+  if ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) % 16 || d->lda % 16 || d->ldb % 16)
+    return fail("tlb200_gemm_blockscaled: A and B must be 16-byte aligned with row pitches that are multiples of 16 "
+                "(lda=%lld ldb=%lld)", (long long)d->lda, (long long)d->ldb);
+  if ((reinterpret_cast<uintptr_t>(scales_a) | reinterpret_cast<uintptr_t>(scales_b)) % 4)
+    return fail("tlb200_gemm_blockscaled: scale pointers must be 4-byte aligned");
+
+  int cg = d->cfg_cta_group, bn = d->cfg_block_n;
+  if (cg != 0 && cg != 1 && cg != 2) return fail("tlb200_gemm_blockscaled: cfg_cta_group %d (0, 1 or 2)", cg);
+  if (bn != 0 && bn != 128 && bn != 256) return fail("tlb200_gemm_blockscaled: cfg_block_n %d (0, 128 or 256)", bn);
+  const int sms = g_sm_count[dev];
+  if (bn == 0) {
+    // 256-wide tiles halve the A traffic; fall back to 128 when that leaves SMs without a tile
+    const long long t256 = static_cast<long long>((d->m + 127) / 128) * ((d->n + 255) / 256);
+    bn = (d->n <= 128 || t256 < sms) ? 128 : 256;
+  }
+  // Pairs are available (cfg_cta_group = 2) but not the default: the partial-sum hand-off crosses the cluster
+  // at every K block and measured about half the single-CTA rate (profiles/r1_notes.md).
+  if (cg == 0) cg = 1;
+  const int block_m = kBlockM * cg;
+  const int stage_bytes = kABytesPerStage + (bn / cg) * kStageRowBytes;
+  const int fixed = 1024 + kBsEpiWarps * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16;
+  int stages = d->cfg_stages > 0 ? d->cfg_stages : (kSmemLimit - fixed) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2 || fixed + stages * stage_bytes > kSmemLimit)
+    return fail("tlb200_gemm_blockscaled: %d stages of %d bytes do not fit %d bytes of shared memory", stages, stage_bytes, kSmemLimit);
+
+  BlockScaledParams kp;
+  memset(&kp, 0, sizeof(kp));
+  if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, d->lda, kStageRowBytes, kBlockM, "A")) return rc;
+  if (int rc = encode_2d(&kp.tm_b, d->ab_dtype, b, d->n, d->k, d->ldb, kStageRowBytes, bn / cg, "B")) return rc;
+  // TMA stores clip at the tensor's last column only in whole 16-byte units: a row whose byte length is not a
+  // multiple of 16 takes the predicated-store epilogue so nothing beyond column n is ever written.
+  kp.epi_tma = (reinterpret_cast<uintptr_t>(c) % 16 == 0 && (d->ldc * ob) % 16 == 0 &&
+                (static_cast<long long>(d->n) * ob) % 16 == 0) ? 1 : 0;
+  if (kp.epi_tma)
+    if (int rc = encode_2d(&kp.tm_c, d->c_dtype, c, d->m, d->n, d->ldc, 128 / ob, 32, "C")) return rc;
+  kp.c = c;
+  kp.ldc = d->ldc;
+  kp.sa = scales_a; kp.sb = scales_b;
+  kp.sa_sm = d->sa_stride_m; kp.sa_sk = d->sa_stride_k;
+  kp.sb_sn = d->sb_stride_n; kp.sb_sk = d->sb_stride_k;
+  kp.m = d->m; kp.n = d->n;
+  kp.num_k_blocks = (d->k + kStageRowBytes - 1) / kStageRowBytes;
+  kp.tiles_m = (d->m + block_m - 1) / block_m;
+  kp.tiles_n = (d->n + bn - 1) / bn;
+  kp.raster = d->cfg_raster > 0 ? d->cfg_raster : 8;
+  kp.stages = stages;
+  kp.b_rows_per_cta = bn / cg;
+  kp.idesc = instr_desc_impl(block_m, bn, 32, d->ab_dtype, TLB200_FLOAT32, true, true, 1, 1);
+  kp.desc_hi = static_cast<uint32_t>(smem_desc_impl(0, 0, 1024 >> 4, 0, 0, 2) >> 32);
+  kp.out_kind = out_kind;
+  kp.l2_policy = 0;
+  long long clusters = sms / cg;
+  const long long tiles = static_cast<long long>(kp.tiles_m) * kp.tiles_n;
+  if (clusters > tiles) clusters = tiles;
+  const int grid = static_cast<int>(clusters) * cg;
+  const int smem = fixed + stages * stage_bytes;
+
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(kBsThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cg;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, pick_blockscaled(cg, bn), kp);
+  if (e != cudaSuccess)
+    return fail("tlb200_gemm_blockscaled: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), grid, cg, smem);
+  g_launches++;
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------

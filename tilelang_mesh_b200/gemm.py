@@ -166,6 +166,48 @@ def gemm_grouped(a: torch.Tensor, b: torch.Tensor, group_rows, c: Optional[torch
     return c
 
 
+def gemm_blockscaled(a: torch.Tensor, b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor,
+                     c: Optional[torch.Tensor] = None, *, out_dtype: torch.dtype = torch.bfloat16, cta_group: int = 0,
+                     block_n: int = 0, stages: int = 0, raster: int = 0) -> torch.Tensor:
+    """fp8 contraction with fine-grained scales (examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:12-83):
+    ``c[m, n] = sum_kb scales_a[m, kb] * scales_b[n // 128, kb] * (a[m, kb-th 128 of K] . b[n, same])``.
+    ``a`` [M, K] and ``b`` [N, K] are fp8 (e4m3 or e5m2), ``scales_a`` [M, ceil(K/128)] and ``scales_b``
+    [ceil(N/128), ceil(K/128)] fp32 with any strides."""
+    if a.dim() != 2 or b.dim() != 2 or not (a.is_cuda and b.is_cuda) or a.dtype != b.dtype or \
+            a.dtype not in (torch.float8_e4m3fn, torch.float8_e5m2):
+        raise ValueError("gemm_blockscaled: A [M, K] and B [N, K] must be CUDA fp8 tensors of the same dtype")
+    m, k = a.shape
+    n, kb_ = b.shape
+    if kb_ != k:
+        raise ValueError(f"gemm_blockscaled: T.gemm K shape check failed: K_A = {k}, K_B = {kb_}")
+    nkb, nnb = -(-k // 128), -(-n // 128)
+    for nm, t, shp in (("scales_a", scales_a, (m, nkb)), ("scales_b", scales_b, (nnb, nkb))):
+        if not t.is_cuda or t.dtype != torch.float32 or tuple(t.shape) != shp:
+            raise ValueError(f"gemm_blockscaled: {nm} must be a CUDA float32 tensor of shape {shp}, got "
+                             f"{t.dtype} {tuple(t.shape)}")
+    if c is None:
+        c = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    elif tuple(c.shape) != (m, n) or not c.is_cuda:
+        raise ValueError(f"gemm_blockscaled: C must be a CUDA tensor of shape {(m, n)}")
+    dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    d = _abi.BlockScaledDesc()
+    d.abi_version = _abi.ABI_VERSION
+    d.m, d.n, d.k = m, n, k
+    d.ab_dtype, d.c_dtype = _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype]
+    d.group_n = d.group_k = 128
+    d.lda, d.ldb, d.ldc = _row_pitch(a, "A"), _row_pitch(b, "B"), _row_pitch(c, "C")
+    d.sa_stride_m, d.sa_stride_k = (scales_a.stride(0), scales_a.stride(1)) if scales_a.numel() else (0, 0)
+    d.sb_stride_n, d.sb_stride_k = (scales_b.stride(0), scales_b.stride(1)) if scales_b.numel() else (0, 0)
+    d.cfg_cta_group, d.cfg_block_n, d.cfg_stages, d.cfg_raster = cta_group, block_n, stages, raster
+    lib = _abi.load()
+    with torch.cuda.device(dev):
+        rc = lib.tlb200_gemm_blockscaled(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), scales_a.data_ptr(),
+                                         scales_b.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+    _abi.check(rc, "tlb200_gemm_blockscaled")
+    return c
+
+
 def gemm_bcast(a: torch.Tensor, b: torch.Tensor, dst_ptrs, ldc: int, c_dtype: torch.dtype, *, alpha: float = 1.0,
                relu: bool = False, **cfg) -> None:
     """C = A[M,K] @ B[N,K]^T stored into SEVERAL matrices at once (tlb200_gemm_bcast): ``dst_ptrs[0]`` is the

@@ -14,7 +14,7 @@ from typing import Any, Callable, Dict, List, Optional
 import torch
 
 from .. import language as T
-from ..program import GemmProgram, recognize_gemm
+from ..program import BlockScaledProgram, GemmProgram, recognize
 from ..utils.target import determine_target
 from ..utils.tensor import TensorSupplyType, map_torch_type
 
@@ -62,7 +62,7 @@ class JITKernel:
         self.target = determine_target(target)
         self.execution_backend = "ctypes"  # one adapter: ctypes over the C ABI
         self.verbose, self.pass_configs, self.compile_flags = verbose, dict(pass_configs or {}), compile_flags
-        self.program: GemmProgram = recognize_gemm(func)
+        self.program = recognize(func)  # GemmProgram or BlockScaledProgram
         self._params = [KernelParam(n, map_torch_type(a.dtype), a.shape) for n, a in func.params]
         self._out_idx = _legalize_out_idx(out_idx, len(self._params))
         if any(i != self.program.c_param for i in self._out_idx):
@@ -112,7 +112,11 @@ class JITKernel:
         a, b, c = full[p.a_param], full[p.b_param], full[p.c_param]
         if c is None:
             c = torch.empty(self._params[p.c_param].shape, dtype=self._params[p.c_param].dtype, device=a.device)
-        G.gemm(a, b, c, trans_a=p.trans_A, trans_b=p.trans_B, alpha=p.alpha, relu=p.relu, **self.tile_hints)
+        if isinstance(p, BlockScaledProgram):
+            hints = {k: v for k, v in self.tile_hints.items() if k in ("cta_group", "block_n", "stages", "raster")}
+            G.gemm_blockscaled(a, b, full[p.sa_param], full[p.sb_param], c, **hints)
+        else:
+            G.gemm(a, b, c, trans_a=p.trans_A, trans_b=p.trans_B, alpha=p.alpha, relu=p.relu, **self.tile_hints)
         return c if self._out_idx else None
 
     # ---------------------------------------------------------------- introspection
@@ -127,6 +131,12 @@ class JITKernel:
     def plan(self) -> dict:
         from .. import gemm as G
         p = self.program
+        if isinstance(p, BlockScaledProgram):  # fixed plan: tlb200_gemm_blockscaled's default (tlb200.cu)
+            sms = torch.cuda.get_device_properties(0).multi_processor_count if torch.cuda.is_available() else 148
+            bn = self.tile_hints.get("block_n") or (128 if p.N <= 128 or -(-p.M // 128) * -(-p.N // 256) < sms else 256)
+            cg = self.tile_hints.get("cta_group") or 1
+            return dict(kernel="gemm_blockscaled_kernel", cta_group=cg, block_m=128 * cg, block_n=bn, block_k=128,
+                        tiles_m=-(-p.M // (128 * cg)), tiles_n=-(-p.N // bn), grid=1, threads=384, tmem_cols=2 * bn)
         return G.plan(p.M, p.N, p.K, map_torch_type(p.in_dtype), map_torch_type(p.out_dtype), p.trans_A, p.trans_B,
                       **self.tile_hints)
 
@@ -136,7 +146,8 @@ class JITKernel:
         import os
         from .. import build
         hdr = "// " + self.program.summary() + "\n// plan: " + repr(self.plan()) + "\n"
-        srcs = [os.path.join(build.CSRC, f) for f in ("gemm_sm100.cuh",) + (() if kernel_only else ("ptx.cuh", "tlb200.cu"))]
+        main = "gemm_blockscaled_sm100.cuh" if isinstance(self.program, BlockScaledProgram) else "gemm_sm100.cuh"
+        srcs = [os.path.join(build.CSRC, f) for f in (main,) + (() if kernel_only else ("ptx.cuh", "tlb200.cu"))]
         return hdr + "\n".join(open(s).read() for s in srcs)
 
     @property

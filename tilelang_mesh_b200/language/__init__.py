@@ -74,9 +74,11 @@ def StridedTensor(shape, strides, dtype="float32", *args, **kwargs):  # noqa: N8
 Buffer = Tensor
 
 
-class BufferRegion:
+class BufferRegion(Expr):
     """A window of a buffer: per-dimension (start, extent | None).  `extent None` = inferred later
-    from the other side of a T.copy, like the reference's BufferLoad operands (copy.py:50-81)."""
+    from the other side of a T.copy, like the reference's BufferLoad operands (copy.py:50-81).
+    It is also an expression: `scales_b[bx * block_N // 128, k]` read as a scalar (a BufferLoad in the
+    reference) can be multiplied and stored (example_deepgemm_fp8_2xAcc.py:70-73)."""
 
     def __init__(self, buffer: "TileBuffer", starts: Sequence, extents: Sequence):
         self.buffer, self.starts, self.extents = buffer, tuple(starts), tuple(extents)

@@ -330,3 +330,218 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
                        threads=tr.threads if isinstance(tr.threads, int) else None, relu=relu, alpha=alpha,
                        accumulator="tmem" if C_acc.scope == "shared.tmem" else "fragment", rasterization=tr.swizzle,
                        notes=notes)
+
+
+# ======================================================================================================
+# Second program family: fp8 contraction with fine-grained scales ("2x accumulation"),
+# examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:43-83  ->  tlb200_gemm_blockscaled.
+@dataclass
+class BlockScaledProgram:
+    M: int
+    N: int
+    K: int
+    in_dtype: str
+    out_dtype: str
+    a_param: int
+    b_param: int
+    c_param: int
+    sa_param: int
+    sb_param: int
+    block_M: int
+    block_N: int
+    block_K: int
+    num_stages: int
+    accum_dtype: str = "float32"
+    trans_A: bool = False
+    trans_B: bool = True
+    rasterization: Optional[dict] = None
+    notes: List[str] = field(default_factory=list)
+
+    def summary(self) -> str:
+        return (f"block-scaled gemm {self.M}x{self.N}x{self.K} {self.in_dtype}->{self.out_dtype} NT, scales per "
+                f"(row, 128 K) x (128 N, 128 K), tile-hint {self.block_M}x{self.block_N}x{self.block_K}")
+
+
+GROUP = 128  # the reference's group_size (example_deepgemm_fp8_2xAcc.py:29)
+
+
+def _is_load(x, buf, index):
+    return isinstance(x, T.ElemLoad) and x.buffer is buf and len(x.index) == len(index) and \
+        all(a is b for a, b in zip(x.index, index))
+
+
+def _mul_operands(e):
+    return (e.a, e.b) if isinstance(e, BinOp) and e.op == "*" else None
+
+
+def recognize_blockscaled(func: "T.PrimFunc") -> BlockScaledProgram:
+    tr = func.trace()
+    if not tr.in_kernel:
+        _fail("no T.Kernel frame")
+    gemms = [o for o in tr.ops if isinstance(o, T.GemmOp)]
+    if len(gemms) != 1 or gemms[0].loop is None:
+        _fail("a block-scaled program has exactly one T.gemm inside the K loop")
+    g = gemms[0]
+    kloop = next(li for li in tr.loops if li.var is g.loop)
+    A_s, B_s, C_l = _buf(g.A), _buf(g.B), _buf(g.C)
+    if g.transpose_A or not g.transpose_B:
+        _fail("block-scaled programs are A[M,K] x B[N,K]^T (transpose_B=True)")
+    if isinstance(g.clear_accum, Expr) or g.clear_accum:
+        _fail("block-scaled programs clear the partial accumulator with T.clear after promoting it")
+    if A_s.dtype != B_s.dtype or A_s.dtype not in ("float8_e4m3", "float8_e5m2"):
+        _fail(f"block-scaled operands must be fp8 (got {A_s.dtype}, {B_s.dtype})")
+    if C_l.scope != "local.fragment" or C_l.dtype != "float32":
+        _fail("the partial accumulator must be a float32 fragment")
+    (bM, bK), (bN, bK2) = A_s.shape, B_s.shape
+    if bK != bK2 or tuple(C_l.shape) != (bM, bN):
+        _fail("tile shapes are inconsistent")
+    if bK != GROUP:
+        _fail(f"block_K must equal the scale group ({GROUP}): every K block is promoted with one scale")
+    if bN > GROUP or GROUP % bN:
+        _fail(f"block_N must divide {GROUP}: one scales_b entry per tile")
+
+    def staging(tile, nm):
+        cs = [o for o in tr.ops if isinstance(o, T.CopyOp) and _buf(o.dst) is tile]
+        if len(cs) != 1 or cs[0].loop is not g.loop:
+            _fail(f"expected one T.copy into {nm}_shared inside the K loop")
+        src = _buf(cs[0].src)
+        if not src.is_global or src.dtype != tile.dtype or len(src.shape) != 2:
+            _fail(f"{nm}_shared must be filled from a 2-D global tensor of the same dtype")
+        return src, _tile_origin(cs[0].src, {}, f"T.copy {src.name}->{nm}_shared")
+
+    A_g, a_org = staging(A_s, "A")
+    B_g, b_org = staging(B_s, "B")
+    bvars = list(tr.block_vars)
+
+    def origin(org, blk, nm):
+        (v0, s0, o0), (v1, s1, o1) = org
+        if o0 or o1 or v1 is not g.loop or s1 != bK:
+            _fail(f"{nm}: tile origin must be [block*{blk}, k*{bK}]")
+        if v0 is None and s0 == 0:
+            return None
+        if not any(v0 is bv for bv in bvars) or s0 != blk:
+            _fail(f"{nm}: row index must be block_index*{blk}")
+        return v0
+
+    m_var, n_var = origin(a_org, bM, "A"), origin(b_org, bN, "B")
+    (M, K), (N, K_b) = A_g.shape, B_g.shape
+    if not all(isinstance(v, int) for v in (M, N, K, K_b)) or K != K_b:
+        _fail("static shapes with equal K are required")
+    from .language.expr import evaluate
+    nkb, nnb = -(-K // GROUP), -(-N // GROUP)
+    if int(evaluate(kloop.extent, {})) != nkb:
+        _fail(f"K loop must run ceildiv({K},{bK}) = {nkb} iterations")
+    for v, ext, blk, nm in ((m_var, M, bM, "M"), (n_var, N, bN, "N")):
+        if v is None:
+            if ext > blk:
+                _fail(f"no block index walks {nm}")
+        elif int(evaluate(v.extent, {})) != -(-ext // blk):
+            _fail(f"grid does not cover {nm}")
+
+    # ---- the promotion:  S[i] = scales_a[by*bM + i, k] * scales_b[bx*bN // 128, k];  Acc[i,j] += C_l[i,j] * S[i]
+    in_loop = [o for o in tr.ops if isinstance(o, T.ElemStore) and o.loop is g.loop]
+    acc_st = [o for o in in_loop if len(o.index) == 2]
+    if len(acc_st) != 1:
+        _fail("expected one element-wise promotion `C_accum[i, j] += C_local[i, j] * scale[i]` in the K loop")
+    st = acc_st[0]
+    Acc, (pi, pj) = st.buffer, st.parallel_vars if len(st.parallel_vars) == 2 else (None, None)
+    if pi is None or st.index[0] is not pi or st.index[1] is not pj or (pi.extent, pj.extent) != (bM, bN) or \
+            Acc.scope != "local.fragment" or Acc.dtype != "float32" or tuple(Acc.shape) != (bM, bN):
+        _fail("the promotion must cover a float32 fragment of the tile shape")
+    v = st.value
+    if not (isinstance(v, BinOp) and v.op == "+"):
+        _fail("the promotion must be an accumulation (+=)")
+    prod = v.b if _is_load(v.a, Acc, (pi, pj)) else v.a if _is_load(v.b, Acc, (pi, pj)) else None
+    ops = _mul_operands(prod) if prod is not None else None
+    if ops is None:
+        _fail("the promotion must add C_local[i, j] * scale[i]")
+    part, sc = ops if _is_load(ops[0], C_l, (pi, pj)) else ops[::-1]
+    if not _is_load(part, C_l, (pi, pj)) or not (isinstance(sc, T.ElemLoad) and len(sc.index) == 1 and sc.index[0] is pi):
+        _fail("the promotion must multiply the T.gemm accumulator by a per-row scale buffer")
+    S = sc.buffer
+    s_st = [o for o in in_loop if o.buffer is S]
+    if len(s_st) != 1 or len(s_st[0].parallel_vars) != 1 or s_st[0].index[0] is not s_st[0].parallel_vars[0] or \
+            s_st[0].parallel_vars[0].extent != bM or tuple(S.shape) != (bM,):
+        _fail("the per-row scale buffer must be filled once per K block over block_M rows")
+    si = s_st[0].parallel_vars[0]
+    ops = _mul_operands(s_st[0].value)
+    if ops is None or not all(isinstance(x, T.BufferRegion) and x.buffer.is_global for x in ops):
+        _fail("the per-row scale must be scales_a[row, k] * scales_b[col_block, k]")
+    ra, rb = ops
+
+    def is_row_scale(r):
+        lin = as_linear(r.starts[0]) if len(r.starts) == 2 else None
+        if lin is None or r.starts[1] is not g.loop:
+            return False
+        terms, off = lin
+        want = {si: 1}
+        if m_var is not None:
+            want[m_var] = bM
+        return off == 0 and terms == want
+
+    if not is_row_scale(ra):
+        ra, rb = rb, ra
+    if not is_row_scale(ra):
+        _fail("scales_a must be indexed [by * block_M + i, k]")
+    e = rb.starts[0] if len(rb.starts) == 2 else None
+    ok_b = e is not None and rb.starts[1] is g.loop
+    if ok_b:
+        if isinstance(e, BinOp) and e.op == "//" and is_const(e.b, GROUP):
+            lin = as_linear(e.a)
+            ok_b = lin is not None and lin[1] == 0 and lin[0] == ({n_var: bN} if n_var is not None else {})
+        else:
+            lin = as_linear(e)
+            ok_b = lin is not None and lin[1] == 0 and (lin[0] == {} if n_var is None else
+                                                        (bN == GROUP and lin[0] == {n_var: 1}))
+    if not ok_b:
+        _fail(f"scales_b must be indexed [bx * block_N // {GROUP}, k]")
+    SA, SB = ra.buffer, rb.buffer
+    if SA.dtype != "float32" or SB.dtype != "float32" or tuple(SA.shape) != (M, nkb) or tuple(SB.shape) != (nnb, nkb):
+        _fail(f"scale tensors must be float32 of shapes {(M, nkb)} and {(nnb, nkb)}")
+
+    # ---- clears: both accumulators before the loop, the partial one again after each promotion
+    def cleared(buf, loop):
+        return any(isinstance(o, T.ClearOp) and o.buffer is buf and o.value == 0.0 and o.loop is loop for o in tr.ops)
+
+    if not (cleared(C_l, None) and cleared(Acc, None) and cleared(C_l, g.loop)):
+        _fail("expected T.clear of both accumulators before the K loop and T.clear(C_local) after each promotion")
+    order = [o for o in tr.ops if o is g or o is st or (isinstance(o, T.ClearOp) and o.buffer is C_l and o.loop is g.loop)]
+    if order[0] is not g or order[1] is not st:
+        _fail("inside the K loop the order must be T.gemm, promotion, T.clear(C_local)")
+
+    # ---- epilogue: Acc -> [C_shared ->] C[by*bM, bx*bN]
+    cur, C_g, c_org = Acc, None, None
+    for o in tr.ops[tr.ops.index(st) + 1:]:
+        if isinstance(o, T.CopyOp) and o.loop is None:
+            if _buf(o.src) is not cur:
+                _fail("the epilogue must copy the promoted accumulator")
+            dst = _buf(o.dst)
+            if dst.is_global:
+                C_g, c_org = dst, _tile_origin(o.dst, {}, "T.copy ->C")
+                break
+            cur = dst
+        elif isinstance(o, T.ElemStore) and o.loop is None:
+            _fail("element-wise epilogues after the promotion are not part of this family")
+    if C_g is None or tuple(C_g.shape) != (M, N) or C_g.dtype not in ("bfloat16", "float32", "float16"):
+        _fail("the promoted accumulator must be stored to a bfloat16/float16/float32 C[M, N]")
+    for (v0, sc0, off), want_v, blk in zip(c_org, (m_var, n_var), (bM, bN)):
+        if off != 0 or (want_v is None and v0 is not None) or (want_v is not None and (v0 is not want_v or sc0 != blk)):
+            _fail("output tile origin does not match the operand tiles' block indices")
+    ids = [A_g.param_index, B_g.param_index, C_g.param_index, SA.param_index, SB.param_index]
+    if len(set(ids)) != 5 or len(tr.params) != 5:
+        _fail("the kernel parameters must be exactly A, B, C, scales_a, scales_b")
+    return BlockScaledProgram(M=M, N=N, K=K, in_dtype=A_s.dtype, out_dtype=C_g.dtype, a_param=ids[0], b_param=ids[1],
+                              c_param=ids[2], sa_param=ids[3], sb_param=ids[4], block_M=bM, block_N=bN, block_K=bK,
+                              num_stages=kloop.num_stages, rasterization=tr.swizzle)
+
+
+def recognize(func: "T.PrimFunc"):
+    """GEMM family first; a program that is not one may still be the block-scaled form."""
+    try:
+        return recognize_gemm(func)
+    except NotAGemmProgram as first:
+        try:
+            return recognize_blockscaled(func)
+        except NotAGemmProgram as second:
+            # five parameters (A, B, C, two scale tensors) = the author meant the block-scaled form
+            raise (second if len(func.params) == 5 else first) from None
