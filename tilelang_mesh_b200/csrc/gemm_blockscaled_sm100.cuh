@@ -10,16 +10,21 @@
 //
 // B200 form: the same persistent warp-specialised ring as gemm_sm100.cuh, except that the MMA warp
 // CLEARS the TMEM accumulator at every K block (one K block = 128 fp8 elements = one 128B-swizzled
-// stage = 4 tcgen05.mma of K = 32) and publishes each partial through a two-deep TMEM ring; the
-// eight epilogue warps pull each partial out with tcgen05.ld and fold it into register accumulators
-// with one FFMA per element (scale = scales_a * scales_b, rounded once, as the reference computes
-// Scale_C_shared).  The register accumulators are cast and stored once per tile.
+// stage = 4 tcgen05.mma of K = 32) and publishes each partial through a ring of TMEM buffers that
+// fills all 512 columns (2 buffers of 256 columns, or 4 of 128); the eight promotion warps pull each
+// partial out with tcgen05.ld (32 columns at a time, the next load in flight while the current
+// chunk is folded) and add it into register accumulators with packed fp32 fmas (fma.rn.f32x2:
+// two IEEE fmas per instruction, bit-identical to fmaf).  scale = scales_a * scales_b is rounded
+// once, as the reference computes Scale_C_shared.  The accumulators are cast and stored once per
+// tile.  The promotion warpgroups raise their register budget with setmaxnreg (128 accumulators +
+// 64 staging registers per thread for BN = 256); the control warpgroup lowers its own.
 //
-// Per SM and K block the tensor pipe needs 2*BN cycles (BN = tile width) and the promotion needs
-// 128*BN FFMAs = BN cycles of the fp32 pipes, so the promotion runs concurrently with the next
-// block's MMAs as long as the epilogue warps are scheduled every other cycle.  The epilogue
-// warpgroups raise their register budget with setmaxnreg (128 accumulators + 64 staging registers
-// per thread for BN = 256); the control warpgroup lowers its own.
+// What bounds it (profiles/r1_notes.md, "block-scaled"): not TMEM bandwidth (tcgen05.ld sustains
+// ~900 B/clk/SM with 8 warps, tools/ubench/tmem_read_width.cu; a K block's partial is 128 KiB =
+// ~145 clk) and not the tensor pipe (512 clk per K block at BN = 256, 75 % busy), but the promotion
+// warps themselves: 2 per scheduler, each K block costs them 64 FFMA2 + 4 loads + waits on a chain
+// that has only two TMEM buffers of slack.  Measured 2.4-2.5 PFLOP/s at 8192^3 = 0.75 x the plain
+// fp8 kernel of this library on the same box.
 #pragma once
 #include "gemm_sm100.cuh"
 
@@ -57,6 +62,16 @@ __device__ __forceinline__ void setmaxnreg_inc() {
 template <int kRegs>
 __device__ __forceinline__ void setmaxnreg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+
+// Two independent IEEE fp32 fmas in one instruction (fma.rn.f32x2, sm_100): {d0, d1} += {x0, x1} * {s, s}.
+// Same results as two fmaf; half the issue slots of the promotion loop.
+__device__ __forceinline__ void fma2(float& d0, float& d1, uint32_t x0, uint32_t x1, uint64_t s2) {
+  uint64_t d, x;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(d0), "f"(d1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(x) : "r"(x0), "r"(x1));
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(x), "l"(s2));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
 }
 
 // Store this thread's kCols consecutive accumulators (tile row = TMEM lane) of one tile.
@@ -119,7 +134,8 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
   constexpr int kBRows = kBN / kCta;                       // rows of B one CTA stages per K block
   constexpr uint32_t kBBytesPerStage = kBRows * kStageRowBytes;
   constexpr uint32_t kStageBytes = kABytesPerStage + kBBytesPerStage;
-  constexpr uint32_t kTmemCols = 2 * kBN;                  // two partial-sum buffers
+  constexpr int kNumBuf = 512 / kBN;                       // partial-sum buffers: the ring fills TMEM (2 or 4)
+  constexpr uint32_t kTmemCols = 512;
   constexpr int kCols = kBN / 2;                           // accumulator columns per epilogue thread
   const int stages = p.stages;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -129,9 +145,9 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
   const uint32_t smem_bar = smem_epi + kBsEpiWarps * kEpiBufBytes;
   const uint32_t bar_full = smem_bar;
   const uint32_t bar_empty = bar_full + 8 * stages;
-  const uint32_t bar_tfull = bar_empty + 8 * stages;   // [2]
-  const uint32_t bar_tempty = bar_tfull + 16;          // [2]
-  const uint32_t smem_tptr = bar_tempty + 16;
+  const uint32_t bar_tfull = bar_empty + 8 * stages;   // [kNumBuf]
+  const uint32_t bar_tempty = bar_tfull + 32;          // [kNumBuf]
+  const uint32_t smem_tptr = bar_tempty + 32;
 
   if (warp == 0) {
     if (elect_one()) {
@@ -145,7 +161,7 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
         mbar_init(bar_full + 8 * s, 1);
         mbar_init(bar_empty + 8 * s, 1);
       }
-      for (int a = 0; a < 2; ++a) {
+      for (int a = 0; a < kNumBuf; ++a) {
         mbar_init(bar_tfull + 8 * a, 1);
         mbar_init(bar_tempty + 8 * a, kBsEpiWarps * kCta);
       }
@@ -233,7 +249,7 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
           }
           __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1u; }
-          if (++as == 2) { as = 0; aph ^= 1u; }
+          if (++as == kNumBuf) { as = 0; aph ^= 1u; }
         }
       }
     }
@@ -245,7 +261,14 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
     const int chalf = ew >> 2;   // column half of the tile
     const uint32_t my_slab = smem_epi + ew * kEpiBufBytes;
     const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, 0) : bar_tempty;
-    const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + chalf * kCols;
+    // Loop-invariant addresses are pinned in registers (an opaque mov): left alone, ptxas re-derives the shared-
+    // memory window base (S2UR SR_CgaCtaId + a ULEA chain) in every K block, ~40 % of the loop's instructions.
+    auto pin = [](uint32_t v) { uint32_t r; asm volatile("mov.b32 %0, %1;" : "=r"(r) : "r"(v)); return r; };
+    const uint32_t lane_taddr = pin(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + chalf * kCols);
+    const uint32_t tfull0 = pin(bar_tfull);
+    const uint32_t tempty0 = pin(tempty_leader);
+    constexpr int kChunks = kCols / 32;
+    static_assert(kChunks % 2 == 0, "the two staging buffers alternate across K blocks");
     int as = 0;
     uint32_t aph = 0;
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
@@ -262,33 +285,63 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
       float acc[kCols];
 #pragma unroll
       for (int i = 0; i < kCols; ++i) acc[i] = 0.f;
-      float s_next = __ldg(sa_ptr) * __ldg(sb_ptr);
+      // The two factors of the next K block's scale are fetched a whole K block ahead and multiplied only when
+      // needed: a multiply placed right behind the loads stalled every iteration for the full global-load latency
+      // (20 % of the promotion warps' samples, profiles/r1_notes.md).
+      float sa_next = __ldg(sa_ptr), sb_next = __ldg(sb_ptr);
+      // One continuous pipeline over (K block, 32-column chunk): while chunk c is folded into the accumulators the
+      // load of the next chunk - possibly the first chunk of the NEXT K block's buffer - is already in flight.
+      uint32_t r[2][32];
+      bool next_started = false;
+      mbar_wait(tfull0 + 8 * as, aph, 3);
+      tc_fence_after();
+      tmem_ld_32x32(lane_taddr + as * kBN, r[0]);
       for (int kb = 0; kb < nkb; ++kb) {
-        const float scale = s_next;
-        if (kb + 1 < nkb) s_next = __ldg(sa_ptr + (kb + 1) * p.sa_sk) * __ldg(sb_ptr + (kb + 1) * p.sb_sk);
-        mbar_wait(bar_tfull + 8 * as, aph, 3);
-        tc_fence_after();
+        const float scale = sa_next * sb_next;
+        uint64_t scale2;  // {scale, scale} for the packed fma
+        asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "f"(scale));
+        const bool more = kb + 1 < nkb;
+        if (more) {
+          sa_ptr += p.sa_sk;
+          sb_ptr += p.sb_sk;
+          sa_next = __ldg(sa_ptr);
+          sb_next = __ldg(sb_ptr);
+        }
         const uint32_t taddr = lane_taddr + as * kBN;
-        uint32_t r[2][32];
-        tmem_ld_32x32(taddr, r[0]);
 #pragma unroll
-        for (int c = 0; c < kCols / 32; ++c) {
+        for (int c = 0; c < kChunks; ++c) {
           tmem_ld_wait();
-          if (c + 1 < kCols / 32) {
+          if (c + 1 < kChunks) {
             tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
           } else {
-            // the whole partial is in registers: hand the TMEM buffer back before the last FFMAs
+            // the whole partial is in registers: hand the TMEM buffer back, then start on the next K block's
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-              if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * as);
-              else mbar_arrive(bar_tempty + 8 * as);
+              if constexpr (kCta == 2) mbar_arrive_cluster(tempty0 + 8 * as);
+              else mbar_arrive(tempty0 + 8 * as);
+            }
+            if (++as == kNumBuf) { as = 0; aph ^= 1u; }
+            // Start on the next K block's partial right away if it is already complete; otherwise fold the last
+            // chunk first and wait afterwards (waiting first idled the FFMAs: measured 2366 -> 2084 TFLOP/s).
+            next_started = false;
+            if (more) {
+              next_started = __shfl_sync(0xffffffffu, mbar_test_wait(tfull0 + 8 * as, aph) ? 1 : 0, 0) != 0;
+              if (next_started) {
+                tc_fence_after();
+                tmem_ld_32x32(lane_taddr + as * kBN, r[0]);
+              }
             }
           }
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc[c * 32 + i] = fmaf(__uint_as_float(r[c & 1][i]), scale, acc[c * 32 + i]);
+          for (int i = 0; i < 32; i += 2)
+            fma2(acc[c * 32 + i], acc[c * 32 + i + 1], r[c & 1][i], r[c & 1][i + 1], scale2);
         }
-        if (++as == 2) { as = 0; aph ^= 1u; }
+        if (more && !next_started) {
+          mbar_wait(tfull0 + 8 * as, aph, 3);
+          tc_fence_after();
+          tmem_ld_32x32(lane_taddr + as * kBN, r[0]);
+        }
       }
       if (row0 < p.m) {
         switch (p.out_kind) {

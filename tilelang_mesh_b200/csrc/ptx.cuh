@@ -81,6 +81,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 
+// Non-blocking probe of a phase parity (try_wait may suspend the warp for a while before answering).
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
 #ifndef TLB200_WATCHDOG_NS
 #define TLB200_WATCHDOG_NS 4000000000ull  // 4 s: a pipeline that waits this long is deadlocked
 #endif

@@ -935,7 +935,7 @@ int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* d, const void* a, con
   if (cg == 0) cg = 1;
   const int block_m = kBlockM * cg;
   const int stage_bytes = kABytesPerStage + (bn / cg) * kStageRowBytes;
-  const int fixed = 1024 + kBsEpiWarps * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16;
+  const int fixed = 1024 + kBsEpiWarps * kEpiBufBytes + (2 * kMaxStages + 8) * 8 + 16;
   int stages = d->cfg_stages > 0 ? d->cfg_stages : (kSmemLimit - fixed) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2 || fixed + stages * stage_bytes > kSmemLimit)
