@@ -75,7 +75,8 @@ typedef struct tlb200_gemm_desc {
   int64_t lda, ldb, ldc;
   float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
   uint32_t epilogue;  /* TLB200_EPI_* */
-  int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles */
+  int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles, 4 = two such pairs per cluster
+                            on neighbouring column tiles, every A box fetched once and TMA-multicast to both */
   int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] or of 64 in (256,512] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
@@ -93,7 +94,7 @@ typedef struct tlb200_gemm_plan {
   uint32_t instr_desc;
   int32_t umma_n, epi_warps; /* N of one tcgen05.mma (block_n / accumulators per tile); epilogue warps */
   int32_t split_k;           /* K slices per tile (1 = no split-K) */
-  int32_t reserved0;
+  int32_t multicast; /* 2 when A boxes are multicast across two pairs (cluster of 4 CTAs), else 1 */
   int64_t workspace_bytes;   /* device scratch tlb200_gemm_ex needs for this plan (0 when split_k == 1) */
 } tlb200_gemm_plan;
 

@@ -124,6 +124,26 @@ def test_padding_right_of_c_untouched_when_row_bytes_not_16_aligned(dt, n, pad):
         G.gemm(a, b, big[:, :n], epilogue=2)
 
 
+@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (300, 200, 136), (512, 2048, 1024), (1000, 3000, 520), (2048, 2048, 2048)])
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float8_e4m3fn, torch.float16])
+def test_a_multicast_clusters_bit_exact(m, n, k, dt):
+    # cfg_cta_group = 4: clusters of two pairs on neighbouring column tiles, A boxes TMA-multicast to both
+    a, b = operands(m, n, k, dt, kind="int")
+    want = a.float() @ b.float().t()
+    for bn in (64, 128, 256):
+        if n <= bn:
+            continue
+        assert G.plan(m, n, k, dt, torch.float32, cta_group=4, block_n=bn)["multicast"] == 2
+        c = G.gemm(a, b, out_dtype=torch.float32, cta_group=4, block_n=bn)
+        assert torch.equal(c, want), f"block_n={bn}"
+    if k >= 1024:  # with K slices through the workspace, and an odd number of column tiles
+        c = G.gemm(a, b[:n - 70], out_dtype=torch.float32, cta_group=4, block_n=128, split_k=2)
+        assert torch.equal(c, want[:, :n - 70])
+    if m % 16 == 0 and dt != torch.float8_e4m3fn:  # an M-contiguous A cannot be split into multicast halves
+        with pytest.raises(RuntimeError, match="cfg_cta_group=4"):
+            G.gemm(a.t().contiguous(), b, out_dtype=torch.float32, trans_a=True, cta_group=4, block_n=64)
+
+
 def test_strided_operands():
     m, n, k = 160, 192, 128
     abig = rand((m, k + 64), torch.bfloat16, "int")

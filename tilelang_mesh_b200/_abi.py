@@ -65,7 +65,7 @@ class GemmPlan(ctypes.Structure):
         ("umma_n", ctypes.c_int32),
         ("epi_warps", ctypes.c_int32),
         ("split_k", ctypes.c_int32),
-        ("reserved0", ctypes.c_int32),
+        ("multicast", ctypes.c_int32),
         ("workspace_bytes", ctypes.c_int64),
     ]
 

@@ -89,6 +89,7 @@ struct alignas(64) GemmKernelParams {
   int epi_tma;
   int relu;
   int l2_policy;
+  int l2_prefetch;  // K blocks of distance at which the producer prefetches operand boxes into L2 (0 = off)
   float alpha;
 };
 
@@ -299,13 +300,24 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
 // region the compiler cannot prove uniformity and wraps every such instruction in an
 // ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" loop, which made the first version of this kernel
 // issue-bound (~870 cycles per K-block instead of 512; profiles/r1_notes.md).
-template <int kCta, int kKind, int kNSub>
+//
+// kMc = 2 (with kCta = 2): clusters of FOUR CTAs = two pairs working on two neighbouring column tiles of the same
+// row tile.  Both pairs need the same A rows, so each CTA fetches only HALF of its A box and TMA multicasts it to
+// the CTA of the other pair that holds the same rows (A traffic per CTA halves: what cuBLAS's 2x2-cluster kernels
+// do for small tiles, where L2->SM bandwidth, not the tensor pipe, is the bound).  A stage may be refilled only
+// when BOTH pairs have consumed it: every pair leader's tcgen05.commit arrives on empty[s] of all four CTAs.
+template <int kCta, int kKind, int kNSub, int kMc = 1>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
+  static_assert(kMc == 1 || (kCta == 2 && kNSub == 1), "A multicast is implemented for pairs with one accumulator per tile");
+  constexpr int kCluster = kCta * kMc;
   extern __shared__ uint8_t smem_raw[];
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(lane_id());
-  const uint32_t cta_rank = (kCta == 2) ? cluster_ctarank() : 0u;
+  const uint32_t cluster_rank = (kCluster > 1) ? cluster_ctarank() : 0u;
+  const uint32_t cta_rank = cluster_rank & (kCta - 1);      // rank inside the pair
+  const uint32_t mc_idx = cluster_rank / kCta;              // which of the cluster's column tiles this pair owns
+  const uint32_t leader_rank = cluster_rank - cta_rank;     // cluster rank of this pair's leader
   const bool leader = cta_rank == 0;
 
   // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
@@ -342,7 +354,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     if (elect_one()) {
       for (int s = 0; s < stages; ++s) {
         mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
-        mbar_init(bar_empty + 8 * s, 1);  // one tcgen05.commit
+        mbar_init(bar_empty + 8 * s, kMc);  // one tcgen05.commit per pair that reads the stage
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
@@ -355,28 +367,29 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   }
   __syncwarp();
   tc_fence_before();
-  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
 
-  const int tiles_mn = p.tiles_m * p.tiles_n;
+  const int tiles_n_c = (p.tiles_n + kMc - 1) / kMc;  // column tiles per cluster step (kMc neighbours at a time)
+  const int tiles_mn = p.tiles_m * tiles_n_c;
   const int num_tiles = tiles_mn * p.split_k;  // work items: (K slice, tile)
-  const int cluster_id = blockIdx.x / kCta;
-  const int num_clusters = gridDim.x / kCta;
+  const int cluster_id = blockIdx.x / kCluster;
+  const int num_clusters = gridDim.x / kCluster;
   const int nkb = p.num_k_blocks;
 
   // Work item -> (row tile, column tile); for a grouped GEMM also the group, the first row of the tile
   // and the end of the group's rows (the tile's row limit).
   auto tile_coord = [&](int w, int& tm, int& tn, int& grp, int& row_base, int& row_limit) {
     const int t = w % tiles_mn;
-    const int group = p.raster * p.tiles_n;
+    const int group = p.raster * tiles_n_c;
     const int g = t / group;
     const int first = g * p.raster;
     const int rows = min(p.raster, p.tiles_m - first);
     const int within = t - g * group;
     tm = first + within % rows;
-    tn = within / rows;
+    tn = (within / rows) * kMc + (int)mc_idx;  // may equal tiles_n for the last odd tile: that pair computes zeros
     if (p.n_groups == 0) {
       grp = 0;
       row_base = tm * kCta * kBlockM;
@@ -418,6 +431,16 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       int kb0, kb1;
       k_range(t, kb0, kb1);
       for (int kb = kb0; kb < kb1; ++kb) {
+        // The smem ring holds `stages` K blocks; with operands coming from DRAM (short problems, cold L2) a block
+        // takes longer than that to arrive, so the boxes of a block further ahead are first pulled into L2.
+        if (p.l2_prefetch > 0 && elected && kb + p.l2_prefetch < kb1) {
+          const int kp0 = (kb + p.l2_prefetch) * kspan;
+          if (!p.a_mn_major) tma_prefetch_2d(&p.tm_a, kp0, row_a + (kMc == 2 ? (int)mc_idx * (kBlockM / 2) : 0));
+          if (!p.b_mn_major) {
+#pragma unroll
+            for (int h = 0; h < n_sub; ++h) tma_prefetch_2d(&p.tm_b, kp0, row_b + h * p.umma_n);
+          }
+        }
         mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
         if (elected) {
           const uint32_t full = bar_full + 8 * s;
@@ -430,7 +453,12 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           for (int j = 0; j < p.a_boxes; ++j) {
             const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
             const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
-            if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
+            if constexpr (kMc == 2) {
+              // K-major A only (host guarantees it): this CTA fetches rows [64*mc_idx, +64) of its 128-row box
+              // and multicasts them to itself and to the CTA of the other pair with the same pair rank.
+              tma_load_2d_pair_mc(dst_a + mc_idx * (kABytesPerStage / 2), &p.tm_a, full, c0, c1 + (int)mc_idx * (kBlockM / 2),
+                                  static_cast<uint16_t>(0x5u << cta_rank), pol_a);
+            } else if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
             else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
           }
           // accumulator h of the tile covers tile columns [h*umma_n, (h+1)*umma_n)
@@ -487,12 +515,12 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             tc_fence_after();
             if (elected) {
               issue_kblock(s, d_tmem, 0u, kb == kb0);
-              umma_commit<kCta>(bar_empty + 8 * s);  // smem stage reusable once these MMAs retire
+              umma_commit<kCta>(bar_empty + 8 * s, kMc == 2 ? 0xF : 0x3);  // smem stage reusable once these MMAs retire
             }
             __syncwarp();
             if (++s == stages) { s = 0; ph ^= 1u; }
           }
-          if (elected) umma_commit<kCta>(bar_tfull + 8 * as);  // accumulator complete -> epilogue
+          if (elected) umma_commit<kCta>(bar_tfull + 8 * as, static_cast<uint16_t>(0x3u << leader_rank));  // accumulator complete -> epilogue
           __syncwarp();
           if (++as == acc_stages) { as = 0; aph ^= 1u; }
         }
@@ -540,7 +568,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const int chalf = ew >> 2;       // with 8 epilogue warps: which half of the tile's columns
     const int nslabs = kEpiSlabs / p.epi_warps;  // 2 or 1 staging slabs per warp
     const uint32_t my_stage = smem_epi + ew * nslabs * kEpiBufBytes;
-    const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, 0) : bar_tempty;
+    const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, leader_rank) : bar_tempty;
     // Column range of this warp inside ONE accumulator (all warps drain accumulator 0, then 1).
     const int acc_width = (kNSub == 2) ? p.umma_n : p.block_n;
     const int ccols = acc_width / (p.epi_warps >> 2);
@@ -586,7 +614,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // ---- teardown: nobody may still be using TMEM / peer smem when it is released
   __syncwarp();  // re-converge the single-lane regions before the .aligned barriers
   tc_fence_before();
-  if constexpr (kCta == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   if (warp == 2) tmem_dealloc<kCta>(tmem_base, tmem_cols);
 }

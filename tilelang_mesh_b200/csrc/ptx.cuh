@@ -136,6 +136,12 @@ __device__ __forceinline__ void cluster_sync_all() {
 __device__ __forceinline__ void tma_prefetch_desc(const void* desc) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(desc)) : "memory");
 }
+// Bring one box of the tensor into L2 only (no shared-memory destination, nothing to wait for).
+__device__ __forceinline__ void tma_prefetch_2d(const void* desc, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(desc)),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
 // 2-D tiled load global -> shared, completion signalled on `bar` (this CTA's).
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint32_t bar, int c0,
                                             int c1, uint64_t policy) {
@@ -154,6 +160,17 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* desc,
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
       ".L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
       "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+// Pair variant that also MULTICASTS the box: it lands at the same smem offset in every CTA of `cta_mask`
+// (bit i = cluster rank i) and each destination's bytes are credited to the barrier at the same offset in
+// that destination's pair leader.  Used to share one A box between the two pairs of a 4-CTA cluster.
+__device__ __forceinline__ void tma_load_2d_pair_mc(uint32_t dst, const void* desc, uint32_t bar, int c0, int c1,
+                                                    uint16_t cta_mask, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".multicast::cluster.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5, %6;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(desc)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "h"(cta_mask), "l"(policy)
       : "memory");
 }
 __device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t src, int c0, int c1) {
@@ -254,18 +271,19 @@ __device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t desc_a, uint64
 // Make `bar` observe completion of every tcgen05.mma this thread issued so far.
 // (implies tcgen05.fence::before_thread_sync).  For a pair the arrive is multicast to the
 // same barrier offset in both CTAs.
+// `cta_mask`: cluster ranks whose barrier (same offset) receives the arrive; default = both CTAs of a pair
+// that sits at cluster ranks 0 and 1.
 template <int kCta>
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
+__device__ __forceinline__ void umma_commit(uint32_t bar, uint16_t cta_mask = 0x3) {
   if constexpr (kCta == 1) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                      bar)
                  : "memory");
   } else {
-    const uint16_t mask = 0x3;
     asm volatile(
         "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
         " [%0], %1;" ::"r"(bar),
-        "h"(mask)
+        "h"(cta_mask)
         : "memory");
   }
 }

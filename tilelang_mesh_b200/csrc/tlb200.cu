@@ -133,6 +133,7 @@ struct Resolved {
   int span;               // elements per 128 B of an operand row
   bool a_mn, b_mn;
   int n_sub, umma_n, acc_stages, epi_warps;
+  int mc;                 // 2 = clusters of two pairs sharing every A box by TMA multicast, else 1
   int b_rows_per_cta;
   int num_k_blocks;
   bool epi_tma;
@@ -145,8 +146,16 @@ struct Resolved {
   long long lda_c, ldb_c, a_copy_bytes, b_copy_bytes, split_bytes;
 };
 
+// Resident 4-CTA clusters (one CTA per SM) on a GPU with `sms` SMs: measured by tlb200_init with
+// cudaOccupancyMaxActiveClusters (33 on a 148-SM B200: GPC sizes are not multiples of 4); estimate otherwise.
+int g_mc_clusters_sms = 0, g_mc_clusters = 0;
+// Cycle-model efficiencies of the A-multicast plans (tools/sweep.py); 0 = never chosen automatically.
+constexpr double kEffMc256 = 1.05, kEffMc128 = 0.78, kEffMc64 = 0.41;
+constexpr bool kAutoMc = true;  // multicast plans are chosen automatically
+int mc_clusters_of(int sms) { return (g_mc_clusters > 0 && sms == g_mc_clusters_sms) ? g_mc_clusters : sms * 33 / 148; }
+
 int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false,
-            const void* a_ptr = nullptr, const void* b_ptr = nullptr) {
+            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = true) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -195,29 +204,41 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
 
   tlb200_gemm_plan& p = r->plan;
   memset(&p, 0, sizeof(p));
-  if (d->cfg_cta_group < 0 || d->cfg_cta_group > 2) return fail("tlb200: cfg_cta_group must be 0, 1 or 2 (got %d)", d->cfg_cta_group);
+  if (d->cfg_cta_group < 0 || d->cfg_cta_group == 3 || d->cfg_cta_group > 4)
+    return fail("tlb200: cfg_cta_group must be 0, 1, 2 or 4 (got %d)", d->cfg_cta_group);
   if (d->reserved[1] < 0 || d->reserved[1] > 64) return fail("tlb200: cfg_split_k must be in [0,64] (got %d)", d->reserved[1]);
   if (d->reserved[1] > 1 && d->ab_dtype == TLB200_INT8) return fail("tlb200: split-K is not offered for int8 (partial sums are kept in fp32)");
   // A tile is n_sub accumulators of umma_n (<= 256) columns each.  The epilogue drains TMEM 32
   // columns at a time, so umma_n is a whole multiple of 32; an N-major B is staged in whole 128 B
   // spans per CTA.  Tiles wider than 256 columns (two accumulators sharing one A stage: 25 % less
   // L2->SM traffic) fill the 512 TMEM columns, so their accumulator is single-buffered.
-  int cg = d->cfg_cta_group, bn = d->cfg_block_n, auto_split = 1;
+  // cfg_cta_group = 4: pairs (cta_group::2 MMAs) in clusters of two pairs that share A by multicast
+  const int cfg_cg = d->cfg_cta_group == 4 ? 2 : d->cfg_cta_group;
+  int cg = cfg_cg, bn = d->cfg_block_n, auto_split = 1, mc = d->cfg_cta_group == 4 ? 2 : 1;
   const int sms_all = sm_count > 0 ? sm_count : 148;
+  const int mc_clusters = mc_clusters_of(sms_all);
+  const bool mc_possible = allow_mc && !r->a_mn && d->m > kBlockM && mc_clusters >= 1;
+  if (mc == 2 && !mc_possible)
+    return fail("tlb200: cfg_cta_group=4 (A multicast across two pairs) needs a K-contiguous A, m > %d and an ordinary "
+                "(not grouped) contraction", kBlockM);
   if (cg == 0 || bn == 0) {
     // Automatic plan: minimise a small cycle model calibrated on B200 (tools/sweep.py,
     // profiles/r1_notes.md) over {cta_group} x {block_n} x {split_k}.
     //   K-block cycles per CTA = 2*block_n / eff(cta_group, block_n)   (512 for a 256-wide tile)
     //   eff: how well the operand feed keeps the tensor pipe busy for that tile shape (measured at
     //   4096^3); wide tiles get a bonus for their lower power per flop but expose one epilogue per tile.
-    struct Cand { int cg, bn; double eff; };
-    const Cand cands[] = {{2, 512, 1.07}, {2, 256, 1.0}, {1, 256, 0.85}, {2, 128, 0.70}, {1, 128, 0.73},
-                          {1, 64, 0.40}, {2, 64, 0.37}, {1, 32, 0.20}};
+    struct Cand { int cg, bn, mc; double eff; };
+    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.85}, {2, 128, 1, 0.70}, {1, 128, 1, 0.73},
+                          {1, 64, 1, 0.40}, {2, 64, 1, 0.37}, {1, 32, 1, 0.20},
+                          {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64}};
     const int nkb = (d->k + r->span - 1) / r->span;
     double best = 1e300;
-    int best_cg = 0, best_bn = 0, best_split = 1;
+    int best_cg = 0, best_bn = 0, best_split = 1, best_mc = 1;
     for (const Cand& c : cands) {
-      if (d->cfg_cta_group && c.cg != d->cfg_cta_group) continue;
+      if (c.mc == 2 && d->cfg_cta_group != 4 && (!kAutoMc || c.bn != 256)) continue;  // measured: only 256-wide tiles gain
+      if (cfg_cg && c.cg != cfg_cg) continue;
+      if (c.mc == 2 && (!mc_possible || d->cfg_cta_group == 2 || d->n <= c.bn)) continue;
+      if (c.mc == 1 && d->cfg_cta_group == 4) continue;
       if (d->cfg_block_n && c.bn != d->cfg_block_n) continue;
       if (c.cg == 2 && (d->m <= kBlockM || sms_all < 2)) continue;
       if (c.bn == 512 && (r->es != 2 || d->n < 512)) continue;  // 8-bit operands: double-buffered tiles measure faster
@@ -225,8 +246,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
       const int step = r->b_mn ? r->span * c.cg : 32;
       if ((c.bn > 256 ? c.bn / 2 : c.bn) % step) continue;
       if (d->cfg_epilogue == 2 && (c.bn > 256 ? c.bn / 2 : c.bn) % (128 / r->ob)) continue;  // TMA-store slabs are 128 B wide
-      const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) * ((d->n + c.bn - 1) / c.bn);
-      const long long clusters = sms_all / c.cg;
+      const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) *
+                              (((d->n + c.bn - 1) / c.bn + c.mc - 1) / c.mc);  // work items: c.mc column tiles each
+      const long long clusters = c.mc == 2 ? mc_clusters : sms_all / c.cg;
       for (int split = 1; split <= 32; split *= 2) {
         if (split > 1 && (!allow_split || d->ab_dtype == TLB200_INT8 || d->reserved[1] == 1 || nkb / split < 8 || tiles * split > 2 * clusters)) break;
         if (d->reserved[1] > 1 && split > d->reserved[1]) break;
@@ -236,14 +258,15 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
         double tile = kb * 2.0 * c.bn / c.eff + (c.bn > 256 ? 8000.0 : 0.0);
         double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn);
         if (split > 1) total += 5000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
-        if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; }
+        if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; best_mc = c.mc; }
       }
     }
     if (best_cg == 0) {  // nothing matched the constraints: fall back to the smallest legal tile
-      best_cg = d->cfg_cta_group ? d->cfg_cta_group : 1;
+      best_cg = cfg_cg ? cfg_cg : 1;
+      best_mc = d->cfg_cta_group == 4 ? 2 : 1;
       best_bn = d->cfg_block_n ? d->cfg_block_n : (r->b_mn ? r->span * best_cg : 32);
     }
-    cg = best_cg; bn = best_bn; auto_split = best_split;
+    cg = best_cg; bn = best_bn; auto_split = best_split; mc = best_mc;
   }
   if (sms_all < 2) cg = 1;
   const int n_step = r->b_mn ? r->span * cg : 32;
@@ -252,6 +275,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (bn < n_step || bn > 512 || bn % r->n_sub || r->umma_n % n_step)
     return fail("tlb200: cfg_block_n=%d invalid for cta_group=%d%s (need a multiple of %d in [%d,256], or of %d in (256,512])",
                 bn, cg, r->b_mn ? ", N-major B" : "", n_step, n_step, 2 * n_step);
+  if (mc == 2 && (r->n_sub != 1 || cg != 2))
+    return fail("tlb200: cfg_cta_group=4 needs block_n <= 256");
+  r->mc = mc;
   r->acc_stages = (2 * bn <= 512) ? 2 : 1;
   int ew = d->reserved[0];  // cfg_epi_warps
   if (ew == 0) {  // 8 warps drain a 512-wide tile unless its halves do not split into whole 128-byte slabs
@@ -276,9 +302,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.tiles_m = (d->m + p.block_m - 1) / p.block_m;
   p.tiles_n = (d->n + bn - 1) / bn;
   r->num_k_blocks = (d->k + r->span - 1) / r->span;
-  const long long tiles = static_cast<long long>(p.tiles_m) * p.tiles_n;
+  const long long tiles = static_cast<long long>(p.tiles_m) * ((p.tiles_n + mc - 1) / mc);  // work items per K slice
   const int sms = sm_count > 0 ? sm_count : 148;
-  long long clusters = sms / cg;
+  long long clusters = mc == 2 ? mc_clusters : sms / cg;
   // Split-K (examples/gemm_splitk in the reference): when the output has too few tiles to occupy the
   // machine and K is deep, K is cut into slices computed by different clusters into an fp32
   // workspace and summed by a second kernel in slice order (deterministic).
@@ -306,7 +332,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   const long long work_items = tiles * r->split_k;
   if (clusters > work_items) clusters = work_items;
   if (clusters < 1) clusters = 1;
-  p.grid = static_cast<int>(clusters) * cg;
+  p.grid = static_cast<int>(clusters) * cg * mc;
+  p.multicast = mc;
   p.threads = 128 + 32 * r->epi_warps;
   p.smem_bytes = kSmemFixed + stages * per_stage;
   p.raster = d->cfg_raster > 0 ? d->cfg_raster : ((bn > 256 || r->es == 1) ? 16 : 16 / cg);
@@ -483,12 +510,21 @@ GemmKernelFn pick_kind(int kind, int n_sub) {
   }
 }
 GemmKernelFn pick_kernel(int cg, int kind, int n_sub) { return cg == 2 ? pick_kind<2>(kind, n_sub) : pick_kind<1>(kind, n_sub); }
-std::array<const void*, 16> all_kernels() {
-  std::array<const void*, 16> k;
+GemmKernelFn pick_kernel_mc(int kind) {  // pairs, one accumulator per tile, A multicast across two pairs
+  switch (kind) {
+    case kKindF8: return gemm_tcgen05_kernel<2, kKindF8, 1, 2>;
+    case kKindTF32: return gemm_tcgen05_kernel<2, kKindTF32, 1, 2>;
+    case kKindI8: return gemm_tcgen05_kernel<2, kKindI8, 1, 2>;
+    default: return gemm_tcgen05_kernel<2, kKindF16, 1, 2>;
+  }
+}
+std::array<const void*, 20> all_kernels() {
+  std::array<const void*, 20> k;
   int i = 0;
   for (int cg = 1; cg <= 2; ++cg)
     for (int kind = 0; kind < 4; ++kind)
       for (int ns = 1; ns <= 2; ++ns) k[i++] = reinterpret_cast<const void*>(pick_kernel(cg, kind, ns));
+  for (int kind = 0; kind < 4; ++kind) k[i++] = reinterpret_cast<const void*>(pick_kernel_mc(kind));
   return k;
 }
 
@@ -645,6 +681,24 @@ int tlb200_init(int device) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
     }
+    {  // how many 4-CTA clusters (two pairs sharing A by multicast) fit this GPU at one CTA per SM
+      cudaLaunchConfig_t qc;
+      memset(&qc, 0, sizeof(qc));
+      qc.gridDim = dim3(prop.multiProcessorCount / 4 * 4, 1, 1);
+      qc.blockDim = dim3(256, 1, 1);
+      qc.dynamicSmemBytes = kSmemLimit;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = 4; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa; qc.numAttrs = 1;
+      int nclusters = 0;
+      if (cudaOccupancyMaxActiveClusters(&nclusters, pick_kernel_mc(kKindF16), &qc) == cudaSuccess && nclusters > 0) {
+        g_mc_clusters = nclusters;
+        g_mc_clusters_sms = prop.multiProcessorCount;
+      } else {
+        cudaGetLastError();  // clear: the estimate in mc_clusters_of() is used instead
+      }
+    }
     HostPipe& hp = g_pipe[device];
     if (!hp.in) {
       bool ok = cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking) == cudaSuccess &&
@@ -669,14 +723,15 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
-  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b)) return rc;
+  const bool allow_mc = n_groups == 0;  // grouped row tiles are not paired up across column tiles
+  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b, allow_mc)) return rc;
   if (r.split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
   if (r.ws_bytes > 0) {
     if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
     if (ws_bytes < r.ws_bytes && r.split_k > 1 && d->reserved[1] <= 1) {
       tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
       d1.reserved[1] = 1;
-      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, true, a, b)) return rc;
+      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, true, a, b, allow_mc)) return rc;
     }
     if (ws_bytes < r.ws_bytes)
       return fail("tlb200_gemm_ex: this call needs a %lld-byte workspace (%lld for re-pitched operands, %lld for split-K x%d), got %lld",
@@ -724,8 +779,9 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   const long long lda = r.lda_c, ldb = r.ldb_c;
   // A
   if (!r.a_mn) {
-    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, kBlockM, "A[M,K]")) return rc;
-    kp.a_boxes = 1; kp.a_box_bytes = kABytesPerStage;
+    // with A multicast every CTA fetches half of its 128-row box (the other half arrives from the other pair)
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, kBlockM / r.mc, "A[M,K]")) return rc;
+    kp.a_boxes = 1; kp.a_box_bytes = kABytesPerStage / r.mc;
   } else {
     if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->k, d->m, lda, r.span, bk, "A[K,M]")) return rc;
     kp.a_boxes = kBlockM / r.span; kp.a_box_bytes = bk * kStageRowBytes;
@@ -809,7 +865,8 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.epi_tma = split ? ws_tma : r.epi_tma;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
-  kp.l2_policy = d->reserved[2];
+  kp.l2_policy = d->reserved[2] & 0xff;
+  kp.l2_prefetch = (d->reserved[2] >> 8) & 0xff;  // experimental knob: cfg_l2_policy bits 8..15 = prefetch distance in K blocks
 
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -819,12 +876,12 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = pl.cta_group;
+  attr[0].val.clusterDim.x = pl.cta_group * r.mc;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  e = cudaLaunchKernelEx(&cfg, pick_kernel(pl.cta_group, mma_kind_of(d->ab_dtype), r.n_sub), kp);
+  e = cudaLaunchKernelEx(&cfg, r.mc == 2 ? pick_kernel_mc(mma_kind_of(d->ab_dtype)) : pick_kernel(pl.cta_group, mma_kind_of(d->ab_dtype), r.n_sub), kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);

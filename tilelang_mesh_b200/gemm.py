@@ -29,6 +29,16 @@ _TORCH2TLB = {
 _AB_DTYPES = (torch.float16, torch.bfloat16, torch.float8_e4m3fn, torch.float8_e5m2, torch.float32, torch.int8)
 
 _inited_devices = set()
+_desc_cache = {}  # problem signature -> (descriptor, byref(descriptor), workspace bytes)
+_lib = None
+
+
+def _load_lib():
+    global _lib
+    _lib = _abi.load()
+    return _lib
+
+
 _workspaces = {}  # (device index, stream handle) -> torch.uint8 scratch for split-K partial sums
 
 
@@ -118,20 +128,38 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
         raise ValueError(f"gemm: unsupported output dtype {c.dtype}")
     ldc = _row_pitch(c, "C")
     dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
-    _ensure_init(dev)
-    desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, lda, ldb,
-                     ldc, alpha, relu, **cfg)
-    lib = _abi.load()
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream(dev).cuda_stream
+    if dev not in _inited_devices:
+        _ensure_init(dev)
+    # Descriptor + workspace size are cached per problem signature: filling ~25 ctypes fields and a plan query cost
+    # more host time than a small contraction takes on the GPU.
+    key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, tuple(sorted(cfg.items())) if cfg else ())
+    hit = _desc_cache.get(key)
+    lib = _lib or _load_lib()
+    if hit is None:
+        desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, lda, ldb,
+                         ldc, alpha, relu, **cfg)
         need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc))
+        if need < 0:
+            _abi.check(-1, "tlb200_gemm_workspace_bytes")
+        if len(_desc_cache) > 4096:
+            _desc_cache.clear()
+        hit = _desc_cache[key] = (desc, ctypes.byref(desc), need)
+    desc, desc_ref, need = hit
+    cur = torch.cuda.current_device()
+    if cur != dev:  # the C ABI launches on the current device: switch only when the tensors live elsewhere
+        torch.cuda.set_device(dev)
+    try:
+        stream = torch._C._cuda_getCurrentRawStream(dev)
         if need > 0:  # split-K partial sums and/or re-pitched copies of operands TMA cannot address
             ws = _workspace(dev, stream, need)
-            rc = lib.tlb200_gemm_ex(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(),
-                                    ws.numel(), stream)
+            rc = lib.tlb200_gemm_ex(desc_ref, a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         else:
-            rc = lib.tlb200_gemm(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(), stream)
-    _abi.check(rc, "tlb200_gemm")
+            rc = lib.tlb200_gemm(desc_ref, a.data_ptr(), b.data_ptr(), c.data_ptr(), stream)
+    finally:
+        if cur != dev:
+            torch.cuda.set_device(cur)
+    if rc != 0:
+        _abi.check(rc, "tlb200_gemm")
     return c
 
 
