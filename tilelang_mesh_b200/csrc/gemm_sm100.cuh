@@ -89,7 +89,6 @@ struct alignas(64) GemmKernelParams {
   int epi_tma;
   int relu;
   int l2_policy;
-  int l2_prefetch;  // K blocks of distance at which the producer prefetches operand boxes into L2 (0 = off)
   float alpha;
 };
 
@@ -431,16 +430,6 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       int kb0, kb1;
       k_range(t, kb0, kb1);
       for (int kb = kb0; kb < kb1; ++kb) {
-        // The smem ring holds `stages` K blocks; with operands coming from DRAM (short problems, cold L2) a block
-        // takes longer than that to arrive, so the boxes of a block further ahead are first pulled into L2.
-        if (p.l2_prefetch > 0 && elected && kb + p.l2_prefetch < kb1) {
-          const int kp0 = (kb + p.l2_prefetch) * kspan;
-          if (!p.a_mn_major) tma_prefetch_2d(&p.tm_a, kp0, row_a + (kMc == 2 ? (int)mc_idx * (kBlockM / 2) : 0));
-          if (!p.b_mn_major) {
-#pragma unroll
-            for (int h = 0; h < n_sub; ++h) tma_prefetch_2d(&p.tm_b, kp0, row_b + h * p.umma_n);
-          }
-        }
         mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
         if (elected) {
           const uint32_t full = bar_full + 8 * s;

@@ -136,12 +136,6 @@ __device__ __forceinline__ void cluster_sync_all() {
 __device__ __forceinline__ void tma_prefetch_desc(const void* desc) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(desc)) : "memory");
 }
-// Bring one box of the tensor into L2 only (no shared-memory destination, nothing to wait for).
-__device__ __forceinline__ void tma_prefetch_2d(const void* desc, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(desc)),
-               "r"(c0), "r"(c1)
-               : "memory");
-}
 // 2-D tiled load global -> shared, completion signalled on `bar` (this CTA's).
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* desc, uint32_t bar, int c0,
                                             int c1, uint64_t policy) {

@@ -865,8 +865,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.epi_tma = split ? ws_tma : r.epi_tma;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
-  kp.l2_policy = d->reserved[2] & 0xff;
-  kp.l2_prefetch = (d->reserved[2] >> 8) & 0xff;  // experimental knob: cfg_l2_policy bits 8..15 = prefetch distance in K blocks
+  kp.l2_policy = d->reserved[2];
 
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

@@ -16,9 +16,14 @@ def timed(fn, n=11):
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 x = torch.zeros(1, device="cuda")
 print("empty-ish launch (x.add_): %.1f us" % timed(lambda: x.add_(1)))
-for (m, n), cfg in [((512, 2048), dict(cta_group=1, block_n=64, split_k=1)), ((512, 2048), dict(cta_group=2, block_n=128, split_k=1)),
-                    ((2048, 2048), dict(cta_group=2, block_n=256, split_k=1))]:
-    for k in (64, 512, 1024, 2048, 4096, 8192):
+cases = [((512, 2048), dict(cta_group=1, block_n=64, split_k=1)), ((512, 2048), dict(cta_group=2, block_n=128, split_k=1)),
+         ((2048, 2048), dict(cta_group=2, block_n=256, split_k=1))]
+if len(sys.argv) > 1 and sys.argv[1] == "mc":
+    cases = [((512, 2048), dict(cta_group=4, block_n=64, split_k=1)), ((512, 2048), dict(cta_group=2, block_n=64, split_k=1)),
+             ((512, 2048), dict(cta_group=4, block_n=128, split_k=1)), ((512, 2048), dict(cta_group=1, block_n=128, split_k=1)),
+             ((512, 2048), dict(cta_group=1, block_n=32, split_k=1))]
+for (m, n), cfg in cases:
+    for k in (64, 2048, 4096, 8192):
         a = torch.randn(m, k, device="cuda").bfloat16(); b = torch.randn(n, k, device="cuda").bfloat16()
         c = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
         t = timed(lambda: G.gemm(a, b, c, **cfg)); tc = timed(lambda: torch.matmul(a, b.t(), out=c))
