@@ -2,7 +2,7 @@
 //
 // One kernel covers the whole TileLang GEMM program  (T.copy A,B tiles -> T.gemm -> T.copy C):
 //
-//   warp 0  producer : TMA bulk-tensor loads of the A / B K-blocks into 128B-swizzled smem,
+//   warps 0,2,3 producers (K blocks round-robin): TMA bulk-tensor loads of the A / B K-blocks into 128B-swizzled smem,
 //                      multi-stage full/empty mbarrier ring          (replaces T.copy g->s:
 //                      src/op/copy.cc:1399-1688, tl::tma_load copy_sm90.h:17-268,
 //                      and the cp.async path the reference is forced onto, copy.h:16-78)
@@ -10,8 +10,7 @@
 //                      double-buffered TMEM accumulator; tcgen05.commit frees smem stages
 //                      and publishes finished accumulators     (replaces tl::tcgen5mma_gemm_ss
 //                      gemm_sm100.h:342-436 and tcgen05_macro_generator.py:140-349)
-//   warp 2  TMEM     : tcgen05.alloc / dealloc                  (replaces tcgen_05.h:13-27)
-//   warp 3  idle
+//   warp 2  also     : tcgen05.alloc / dealloc                  (replaces tcgen_05.h:13-27)
 //   warps 4-7 epilogue: tcgen05.ld -> alpha/relu -> cast -> swizzled smem -> TMA store (or
 //                      predicated 16 B global stores)           (replaces copy.cc:1191-1377
 //                      tmem->fragment, copy.cc:920-958 fragment->shared->global)
@@ -407,8 +406,17 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     kb1 = min(nkb, kb0 + p.kb_per_split);
   };
 
-  if (warp == 0) {
-    // ===================================================== TMA producer (one elected lane issues)
+  if (warp != 1 && warp < kEpiWarp0) {
+    // ===================================================== TMA producers (one elected lane of each issues)
+    // Three producer warps (0, 2, 3) take the K blocks round-robin, each filling whole stages.  One warp's issue
+    // path (try_wait on `empty`, arrive.expect_tx, two TMA issues) costs ~280 ns per K block, which starved every
+    // tile narrower than 256 columns (282 ns per block whatever the tile, stage count or cluster shape;
+    // profiles/r1_notes.md); three interleaved streams bring the issue cost under the MMA time of a 64-wide tile.
+    // Parity waits only tell adjacent phases apart: a producer that skips P K blocks between its visits must not
+    // be able to see a stage's `empty` barrier two phases behind, which holds for P <= stages.
+    const int kProducers = stages < 3 ? stages : 3;
+    const int pidx = warp == 0 ? 0 : warp - 1;  // warps 0, 2, 3 -> 0, 1, 2 (a warp with pidx >= kProducers idles)
+    int turn = 0;                               // whose K block the next one is
     const bool elected = elect_one();
     // Operands are re-read by other tiles of the raster group: keep them in L2 (evict_last measured +1.5 % bf16,
     // +3 % fp8 sustained over evict_normal; profiles/r1_notes.md).  l2_policy 1 restores evict_normal.
@@ -430,8 +438,10 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       int kb0, kb1;
       k_range(t, kb0, kb1);
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
-        if (elected) {
+        const bool mine = turn == pidx;
+        if (++turn == kProducers) turn = 0;
+        if (mine) mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
+        if (mine && elected) {
           const uint32_t full = bar_full + 8 * s;
           if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
           const int k0 = kb * kspan;

@@ -228,8 +228,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     //   eff: how well the operand feed keeps the tensor pipe busy for that tile shape (measured at
     //   4096^3); wide tiles get a bonus for their lower power per flop but expose one epilogue per tile.
     struct Cand { int cg, bn, mc; double eff; };
-    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.85}, {2, 128, 1, 0.70}, {1, 128, 1, 0.73},
-                          {1, 64, 1, 0.40}, {2, 64, 1, 0.37}, {1, 32, 1, 0.20},
+    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.89}, {2, 128, 1, 0.90}, {1, 128, 1, 0.75},
+                          {1, 64, 1, 0.45}, {2, 64, 1, 0.58}, {1, 32, 1, 0.31},
                           {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64}};
     const int nkb = (d->k + r->span - 1) / r->span;
     double best = 1e300;
@@ -256,8 +256,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
         const long long waves = (items + clusters - 1) / clusters;
         const double kb = static_cast<double>((nkb + split - 1) / split);
         double tile = kb * 2.0 * c.bn / c.eff + (c.bn > 256 ? 8000.0 : 0.0);
-        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn);
-        if (split > 1) total += 5000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
+        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? 3000.0 : 0.0);  // pairs start ~1.5 us later
+        if (split > 1) total += 3000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
         if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; best_mc = c.mc; }
       }
     }

@@ -46,7 +46,8 @@ def run(name, fn):
           sm_mhz_med_2nd_half=clk[len(clk)//2] if clk else None, power_w_med=round(pw[len(pw)//2],1) if pw else None)), flush=True)
     time.sleep(1.5)
 
-variants = [("auto", {}), ("normal", dict(l2_policy=1)), ("C_evict_first", dict(l2_policy=2)), ("auto_again", {})]
+variants = [("auto", {}), ("pair256", dict(cta_group=2, block_n=256)), ("pair512", dict(cta_group=2, block_n=512)),
+            ("mc256", dict(cta_group=4, block_n=256)), ("auto_again", {})]
 extra = [v for v in sys.argv[3:]]
 if dt == "bf16":
     run("cublas", lambda: torch.matmul(a, b.t(), out=c))
