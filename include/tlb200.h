@@ -48,6 +48,11 @@ typedef enum tlb200_dtype {
 /* Epilogue flags (fused into the TMEM->global drain). */
 #define TLB200_EPI_NONE 0u
 #define TLB200_EPI_RELU 1u /* examples/quickstart.py:42-43: C = max(C, 0) */
+#define TLB200_EPI_ACCUMULATE 2u /* C = C + alpha * op(A) op(B): what the reference's split-K program does with
+                                  * T.atomic_add on a caller-zeroed C (examples/gemm_splitk/
+                                  * example_tilelang_gemm_splitk.py:35-40); here one deterministic read-modify-write per
+                                  * element (predicated-store epilogue, or the split-K reduction).  Not with RELU,
+                                  * int32 output or tlb200_gemm_bcast. */
 
 /*
  * One dense contraction  C[M,N] = alpha * op(A) * op(B)  with fp32 accumulate

@@ -144,6 +144,25 @@ def test_a_multicast_clusters_bit_exact(m, n, k, dt):
             G.gemm(a.t().contiguous(), b, out_dtype=torch.float32, trans_a=True, cta_group=4, block_n=64)
 
 
+@pytest.mark.parametrize("out", [torch.float32, torch.bfloat16, torch.float16, torch.float8_e4m3fn])
+@pytest.mark.parametrize("cfg", [{}, dict(cta_group=1, block_n=64), dict(cta_group=2, block_n=256), dict(cta_group=4, block_n=128),
+                                 dict(split_k=4), dict(cta_group=2, block_n=512)])
+def test_accumulate_into_c(out, cfg):
+    # TLB200_EPI_ACCUMULATE: C = C + alpha * A B^T (examples/gemm_splitk's atomic-add form, done without atomics)
+    m, n, k = 384, 520, 2048
+    a, b = operands(m, n, k, torch.bfloat16, kind="int")
+    c0 = torch.randint(-8, 9, (m, n), device="cuda").float()
+    c = c0.to(out).clone()
+    alpha = 2.0 ** -7
+    G.gemm(a, b, c, alpha=alpha, accumulate=True, **cfg)
+    want = ((a.float() @ b.float().t()) * alpha + c0.to(out).float()).to(out)  # exact in fp32, one rounding
+    assert torch.equal(c.float(), want.float())
+    with pytest.raises(RuntimeError, match="ACCUMULATE"):
+        G.gemm(a, b, c, relu=True, accumulate=True)
+    with pytest.raises(ValueError, match="accumulate"):
+        G.gemm(a, b, accumulate=True)
+
+
 def test_strided_operands():
     m, n, k = 160, 192, 128
     abig = rand((m, k + 64), torch.bfloat16, "int")

@@ -18,7 +18,7 @@ ABI_VERSION = 1
 
 # tlb200_dtype
 FLOAT16, BFLOAT16, FLOAT8_E4M3, FLOAT8_E5M2, FLOAT32, INT8, INT32 = 0, 1, 2, 3, 4, 5, 6
-EPI_NONE, EPI_RELU = 0, 1
+EPI_NONE, EPI_RELU, EPI_ACCUMULATE = 0, 1, 2
 STATIC_SCRATCH_BYTES = 32 << 20  # TLB200_STATIC_SCRATCH_BYTES
 
 

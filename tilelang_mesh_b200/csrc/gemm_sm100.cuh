@@ -87,6 +87,7 @@ struct alignas(64) GemmKernelParams {
   int acc_int;  // accumulators hold int32 (int8 operands)
   int epi_tma;
   int relu;
+  int accumulate;  // C = C_in + alpha * acc (predicated-store epilogue only)
   int l2_policy;
   float alpha;
 };
@@ -161,6 +162,17 @@ __device__ __forceinline__ void store_scalar(void* c, long long idx, float v) {
   } else {
     constexpr __nv_fp8_interpretation_t kI = (kOut == kOutE4M3) ? __NV_E4M3 : __NV_E5M2;
     reinterpret_cast<uint8_t*>(c)[idx] = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, kI);
+  }
+}
+
+template <int kOut>
+__device__ __forceinline__ float load_out(const void* c, long long idx) {
+  if constexpr (kOut == kOutBF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(c)[idx]);
+  else if constexpr (kOut == kOutF16) return __half2float(reinterpret_cast<const __half*>(c)[idx]);
+  else if constexpr (kOut == kOutF32 || kOut == kOutI32) return reinterpret_cast<const float*>(c)[idx];
+  else {
+    constexpr __nv_fp8_interpretation_t kI = (kOut == kOutE4M3) ? __NV_E4M3 : __NV_E5M2;
+    return __half2float(__half(__nv_cvt_fp8_to_halfraw(reinterpret_cast<const uint8_t*>(c)[idx], kI)));
   }
 }
 
@@ -273,6 +285,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       if (row_ok) {
         const int gcol = col0 + cs;
         const long long base = static_cast<long long>(grow + row_off) * p.ldc + gcol;
+        if (p.accumulate) {  // C += ...: every element is owned by exactly one thread of one CTA, no atomics needed
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (gcol + i < p.n) v[i] += load_out<kOut>(p.c, base + i);
+        }
         for (int g = -1; g < p.n_peer; ++g) {  // g == -1: the local C; others: peer GPUs' copies
           void* cdst = g < 0 ? p.c : p.c_peer[g];
           if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0 && (reinterpret_cast<uintptr_t>(cdst) % 16) == 0) {

@@ -338,6 +338,13 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.smem_bytes = kSmemFixed + stages * per_stage;
   p.raster = d->cfg_raster > 0 ? d->cfg_raster : ((bn > 256 || r->es == 1) ? 16 : 16 / cg);
   int epi = d->cfg_epilogue;
+  const bool accumulate = (d->epilogue & TLB200_EPI_ACCUMULATE) != 0;
+  if (accumulate) {
+    if (d->epilogue & TLB200_EPI_RELU) return fail("tlb200: TLB200_EPI_ACCUMULATE cannot be combined with TLB200_EPI_RELU");
+    if (d->c_dtype == TLB200_INT32) return fail("tlb200: TLB200_EPI_ACCUMULATE is not offered for int32 output");
+    if (epi == 2) return fail("tlb200: TLB200_EPI_ACCUMULATE uses the predicated-store epilogue (cfg_epilogue 0 or 1)");
+    epi = 1;
+  }
   // A TMA store clips at the tensor's last column only in whole 16-byte units (measured: tools/pad_probe.py), so a
   // row whose byte length is not a multiple of 16 must take the predicated stores or the cells right of column n
   // in a padded C would be overwritten.
@@ -403,7 +410,7 @@ __global__ void fill_zero_kernel(void* c, long long ldc, int m, int n) {
 // Split-K second pass: C[m,n] = cast(relu?(alpha * sum_s ws[s*m_pad + m, n])), slices summed in order.
 template <int kOut>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_ld, int m_pad, int split_k, void* c,
-                                     long long ldc, int m, int n, float alpha, int relu) {
+                                     long long ldc, int m, int n, float alpha, int relu, int accumulate) {
   const int n4 = (n + 3) / 4;
   const long long total = static_cast<long long>(m) * n4;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -418,24 +425,27 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       if (relu) o[j] = fmaxf(o[j], 0.f);
-      if (col + j < n) store_scalar<kOut>(c, row * ldc + col + j, o[j]);
+      if (col + j < n) {
+        if (accumulate) o[j] += load_out<kOut>(c, row * ldc + col + j);
+        store_scalar<kOut>(c, row * ldc + col + j, o[j]);
+      }
     }
   }
 }
 
 int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_k, void* c, long long ldc, int m, int n,
-                         float alpha, bool relu, int out_kind, cudaStream_t stream) {
+                         float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream) {
   const long long total = static_cast<long long>(m) * ((n + 3) / 4);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  const int g = static_cast<int>(blocks), rl = relu ? 1 : 0;
+  const int g = static_cast<int>(blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
   switch (out_kind) {
-    case kOutF16: splitk_reduce_kernel<kOutF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
-    case kOutBF16: splitk_reduce_kernel<kOutBF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
-    case kOutF32: splitk_reduce_kernel<kOutF32><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
-    case kOutE4M3: splitk_reduce_kernel<kOutE4M3><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
-    default: splitk_reduce_kernel<kOutE5M2><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl); break;
+    case kOutF16: splitk_reduce_kernel<kOutF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutBF16: splitk_reduce_kernel<kOutBF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF32: splitk_reduce_kernel<kOutF32><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutE4M3: splitk_reduce_kernel<kOutE4M3><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    default: splitk_reduce_kernel<kOutE5M2><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
@@ -864,6 +874,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.acc_int = d->ab_dtype == TLB200_INT8;
   kp.epi_tma = split ? ws_tma : r.epi_tma;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
+  kp.accumulate = (!split && (d->epilogue & TLB200_EPI_ACCUMULATE)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
   kp.l2_policy = d->reserved[2];
 
@@ -887,7 +898,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   g_launches++;
   if (split) {
     if (int rc = launch_splitk_reduce(static_cast<const float*>(ws), r.ws_ld, r.m_pad, r.split_k, c, d->ldc, d->m, d->n, d->alpha,
-                                      (d->epilogue & TLB200_EPI_RELU) != 0, out_kind, stream))
+                                      (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream))
       return rc;
     g_launches++;
   }
@@ -930,6 +941,7 @@ int tlb200_gemm_bcast(const tlb200_gemm_desc* d, const void* a, const void* b, v
       return fail("tlb200_gemm_bcast: destination %d is aligned differently from destination 0", g);
   }
   if (d && d->reserved[1] > 1) return fail("tlb200_gemm_bcast: split-K cannot be combined with multiple destinations");
+  if (d && (d->epilogue & TLB200_EPI_ACCUMULATE)) return fail("tlb200_gemm_bcast: TLB200_EPI_ACCUMULATE is not offered with multiple destinations");
   return gemm_impl(d, a, b, c_list[0], nullptr, 0, stream_v, c_list + 1, n_c - 1);
 }
 

@@ -71,7 +71,8 @@ def _row_pitch(t: torch.Tensor, name: str) -> int:
 
 
 def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha=1.0, relu=False,
-              cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0, split_k=0, l2_policy=0) -> _abi.GemmDesc:
+              cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0, split_k=0, l2_policy=0,
+              accumulate=False) -> _abi.GemmDesc:
     d = _abi.GemmDesc()
     d.abi_version = _abi.ABI_VERSION
     d.m, d.n, d.k = int(m), int(n), int(k)
@@ -79,7 +80,7 @@ def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha
     d.trans_a, d.trans_b = int(bool(trans_a)), int(bool(trans_b))
     d.lda, d.ldb, d.ldc = int(lda), int(ldb), int(ldc)
     d.alpha = float(alpha)
-    d.epilogue = _abi.EPI_RELU if relu else _abi.EPI_NONE
+    d.epilogue = (_abi.EPI_RELU if relu else _abi.EPI_NONE) | (_abi.EPI_ACCUMULATE if accumulate else 0)
     d.cfg_cta_group, d.cfg_block_n, d.cfg_stages = int(cta_group), int(block_n), int(stages)
     d.cfg_raster, d.cfg_epilogue = int(raster), int(epilogue)
     d.reserved[0] = int(epi_warps)
@@ -95,7 +96,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
 
     ``trans_a`` / ``trans_b`` have T.gemm's meaning (tilelang/language/gemm.py:105-116):
     A is [K, M] if trans_a else [M, K]; B is [N, K] if trans_b else [K, N].
+    ``accumulate=True`` (in ``cfg``) adds the product to the contents of ``c`` instead of overwriting them
+    (the reference's T.atomic_add split-K form, examples/gemm_splitk).
     """
+    if cfg.get("accumulate") and c is None:
+        raise ValueError("gemm: accumulate=True needs the C tensor to accumulate into")
     if not (isinstance(a, torch.Tensor) and isinstance(b, torch.Tensor)):
         raise ValueError("gemm: A and B must be torch tensors")
     if not a.is_cuda or not b.is_cuda:
