@@ -225,6 +225,9 @@ def test_scaled_epilogue_and_partial_k_loop_rejected():
      "matmul_non_persistent(1024, 1024, 1024, 128, 256, 32, 128, 3)"),
     ("examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py", "def ceildiv",
      'tl_gemm(1024, 1024, 8192, 64, "float8_e4m3", "bfloat16", "float32")'),
+    ("examples/gemm_splitk/example_tilelang_gemm_splitk.py", "def main()", "matmul(1024, 1024, 1024, 128, 128, 32, 4)"),
+    ("examples/gemm_splitk/example_tilelang_gemm_splitk_vectorize_atomicadd.py", "def main()",
+     "matmul(1024, 1024, 1024, 128, 128, 32, 4)"),
     ("benchmark/matmul/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
     ("benchmark/matmul_fp8/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
 ])
@@ -336,3 +339,30 @@ def test_blockscaled_2xacc_program_family():
         tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, 128, in_dtype="float16"))
     with pytest.raises(NotAGemmProgram, match="scales_b must be indexed"):
         tilelang.compile(P.blockscaled_2xacc(512, 384, 1024, 128, group=64))
+
+
+def test_splitk_atomic_add_programs():
+    for tile_form in (False, True):
+        k = tilelang.compile(P.splitk_atomic(512, 384, 2048, split_k=4, tile_form=tile_form))
+        p = k.program
+        assert (p.M, p.N, p.K, p.accumulate, p.split_k, p.out_dtype) == (512, 384, 2048, True, 4, "float32")
+    with pytest.raises(NotAGemmProgram, match="tile K exactly"):
+        tilelang.compile(P.splitk_atomic(512, 384, 2000, split_k=3))  # 2000 // 3 slices drop the tail of K
+
+    M = N = 256
+
+    @T.prim_func
+    def sliced_but_overwriting(A: T.Tensor((M, 512), "float16"), B: T.Tensor((512, N), "float16"), C: T.Tensor((M, N), "float32")):
+        with T.Kernel(2, 2, 2, threads=128) as (bx, by, bz):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((32, 128), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for ko in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, bz * 256 + ko * 32], a_s)
+                T.copy(B[bz * 256 + ko * 32, bx * 128], b_s)
+                T.gemm(a_s, b_s, acc)
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="must add its partial tiles"):
+        tilelang.compile(sliced_but_overwriting)

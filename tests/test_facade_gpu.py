@@ -157,6 +157,21 @@ def test_blockscaled_2xacc_program_through_the_facade():
         assert kern.get_profiler().do_bench(warmup=5, rep=10) > 0
 
 
+def test_splitk_atomic_add_program_accumulates_into_c():
+    # examples/gemm_splitk: c = zeros; kernel(a, b, c); c == a @ b.  A second call adds the product once more.
+    M, N, K = 1024, 768, 4096
+    for tile_form in (False, True):
+        kern = tilelang.compile(P.splitk_atomic(M, N, K, split_k=4, tile_form=tile_form))
+        a = torch.randint(-3, 4, (M, K), device="cuda").half()
+        b = torch.randint(-3, 4, (K, N), device="cuda").half()
+        c = torch.zeros(M, N, device="cuda", dtype=torch.float32)
+        assert kern(a, b, c) is None
+        want = a.float() @ b.float()
+        assert torch.equal(c, want)
+        kern(a, b, c)
+        assert torch.equal(c, 2 * want)
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

@@ -154,3 +154,30 @@ def blockscaled_2xacc(M, N, K, bN=128, out_dtype="bfloat16", in_dtype="float8_e4
             T.copy(c_s, C[by * bM, bx * bN])
 
     return prog
+
+
+def splitk_atomic(M, N, K, bM=128, bN=128, bK=32, split_k=4, dtype="float16", out_dtype="float32", tile_form=False):
+    """K cut over a third grid dimension, partial tiles added into C with T.atomic_add
+    (the form of examples/gemm_splitk/example_tilelang_gemm_splitk.py:18-40 and its _vectorize_atomicadd variant)."""
+    k_slice = K // split_k
+
+    @T.prim_func
+    def prog(A: T.Tensor((M, K), dtype), B: T.Tensor((K, N), dtype), C: T.Tensor((M, N), out_dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), split_k, threads=128) as (bx, by, bz):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bK, bN), dtype)
+            c_s = T.alloc_shared((bM, bN), out_dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            T.clear(acc)
+            for ko in T.Pipelined(T.ceildiv(k_slice, bK), num_stages=0):
+                T.copy(A[by * bM, bz * k_slice + ko * bK], a_s)
+                T.copy(B[bz * k_slice + ko * bK, bx * bN], b_s)
+                T.gemm(a_s, b_s, acc)
+            T.copy(acc, c_s)
+            if tile_form:
+                T.atomic_add(C[by * bM, bx * bN], c_s)
+            else:
+                for i, j in T.Parallel(bM, bN):
+                    T.atomic_add(C[by * bM + i, bx * bN + j], c_s[i, j])
+
+    return prog

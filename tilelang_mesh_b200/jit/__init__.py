@@ -116,7 +116,8 @@ class JITKernel:
             hints = {k: v for k, v in self.tile_hints.items() if k in ("cta_group", "block_n", "stages", "raster")}
             G.gemm_blockscaled(a, b, full[p.sa_param], full[p.sb_param], c, **hints)
         else:
-            G.gemm(a, b, c, trans_a=p.trans_A, trans_b=p.trans_B, alpha=p.alpha, relu=p.relu, **self.tile_hints)
+            extra = dict(self.tile_hints, accumulate=True) if p.accumulate else self.tile_hints
+            G.gemm(a, b, c, trans_a=p.trans_A, trans_b=p.trans_B, alpha=p.alpha, relu=p.relu, **extra)
         return c if self._out_idx else None
 
     # ---------------------------------------------------------------- introspection

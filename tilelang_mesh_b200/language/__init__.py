@@ -21,7 +21,7 @@ from .expr import BinOp, Call, Const, Expr, Var, as_affine, evaluate, is_const, 
 __all__ = [
     "prim_func", "Tensor", "StridedTensor", "Buffer", "Kernel", "alloc_shared", "alloc_fragment", "alloc_local",
     "alloc_tmem", "alloc_barrier", "Pipelined", "Persistent", "Parallel", "serial", "grid", "unroll", "copy", "gemm", "gemm_v1",
-    "gemm_v2", "clear", "fill", "use_swizzle", "annotate_layout", "mbarrier_wait_parity", "max", "min", "ceildiv",
+    "gemm_v2", "clear", "fill", "use_swizzle", "annotate_layout", "mbarrier_wait_parity", "atomic_add", "max", "min", "ceildiv",
     "GemmWarpPolicy", "dynamic", "symbolic", "float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2", "int32",
 ]
 
@@ -189,6 +189,14 @@ class ElemStore:
     value: Any
     parallel_vars: Tuple
     loop: Optional[Var] = None
+
+
+@dataclass
+class AtomicAddOp:
+    dst: Any          # BufferRegion of a global tensor (one element inside T.Parallel, or a tile origin)
+    value: Any        # ElemLoad (element form) or a tile buffer (tile form)
+    parallel_vars: Tuple
+    loop: Optional[Var]
 
 
 @dataclass
@@ -467,6 +475,15 @@ def clear(buffer):
 def fill(buffer, value):
     tr = _current_trace()
     tr.ops.append(ClearOp(buffer, float(value), tr.current_loop))
+
+
+def atomic_add(dst, value, memory_order=None, return_prev: bool = False, use_tma: bool = False):
+    """tilelang/language/atomic.py:115-119.  Recognised only as the output step of a split-K GEMM program
+    (examples/gemm_splitk/example_tilelang_gemm_splitk.py:39-40): partial tiles added into a global C."""
+    if return_prev:
+        raise NotImplementedError("T.atomic_add(return_prev=True) is outside the GEMM program family")
+    tr = _current_trace()
+    tr.ops.append(AtomicAddOp(dst, value, tuple(tr.parallel_vars), tr.current_loop))
 
 
 def use_swizzle(panel_size: int = 10, order: str = "row", enable: bool = True):

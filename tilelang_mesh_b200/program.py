@@ -45,6 +45,8 @@ class GemmProgram:
     threads: Optional[int]
     relu: bool = False
     alpha: float = 1.0
+    accumulate: bool = False       # C += A B (split-K program that adds its partial tiles into C with T.atomic_add)
+    split_k: int = 1               # K slices of the program's grid (a hint: the backend picks its own split)
     accumulator: str = "fragment"  # "fragment" (register accumulators in the reference) or "tmem"
     rasterization: Optional[dict] = None
     notes: List[str] = field(default_factory=list)
@@ -77,7 +79,10 @@ def _tile_origin(region, want_vars: Dict[str, Var], what: str):
     for s in region.starts:
         aff = as_affine(s)
         if aff is None:
-            _fail(f"{what}: index {s!r} is not of the form var*block + const")
+            lin = as_linear(s)  # split-K programs index K with two variables: bz*(K/split) + ko*block_K
+            if lin is None or lin[1] != 0 or len(lin[0]) != 2:
+                _fail(f"{what}: index {s!r} is not of the form var*block + const")
+            aff = (lin[0], None, 0)
         out.append(aff)
     return out
 
@@ -165,6 +170,7 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     A_g, a_org = staging(A_s, "A")
     B_g, b_org = staging(B_s, "B")
     bvars = list(tr.block_vars)
+    split = []  # [(slice block index, K elements per slice)] when the program cuts K over a grid dimension
 
     def classify(org, dims_are, nm):
         """dims_are: tuple naming each dim of the global operand, e.g. ('M','K').  Returns block var of the M/N dim."""
@@ -173,9 +179,19 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
             if off != 0:
                 _fail(f"{nm}: tile origin has a constant offset {off}")
             if role == "K":
-                if v is not g.loop or sc != bK:
+                if isinstance(v, dict):  # {k loop: block_K, slice index: K / split_k}
+                    others = [x for x in v if x is not g.loop]
+                    if v.get(g.loop) != bK or len(others) != 1 or not any(others[0] is bv for bv in bvars):
+                        _fail(f"{nm}: split-K index must be slice*(K/split_k) + k*block_K")
+                    cand = (others[0], v[others[0]])
+                    if split and not (split[0][0] is cand[0] and split[0][1] == cand[1]):
+                        _fail("A and B are sliced differently along K")
+                    split[:] = [cand]
+                elif v is not g.loop or sc != bK:
                     _fail(f"{nm}: K index must be k*block_K (got {v!r}*{sc})")
             else:
+                if isinstance(v, dict):
+                    _fail(f"{nm}: {role} index mixes two indices")
                 if v is None and sc == 0:
                     blk = None  # single tile along this dimension
                 elif any(v is bv for bv in bvars) and sc == tile_ext:
@@ -207,8 +223,16 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
             ext_v = int(evaluate(ext, {}))
         except Exception:  # noqa: BLE001
             _fail("K loop extent is not a compile-time constant")
-    if ext_v != -(-K // bK):
-        _fail(f"K loop runs {ext_v} iterations, expected ceildiv({K},{bK}) = {-(-K // bK)}")
+    split_k = 1
+    k_per_cta = K
+    if split:
+        zvar, k_per_cta = split[0]
+        from .language.expr import evaluate as _ev
+        split_k = int(_ev(zvar.extent, {}))
+        if zvar is m_var or zvar is n_var or k_per_cta * split_k != K or k_per_cta % bK:
+            _fail(f"split-K slices must tile K exactly: {split_k} slices of {k_per_cta} for K = {K}, block_K = {bK}")
+    if ext_v != -(-k_per_cta // bK):
+        _fail(f"K loop runs {ext_v} iterations, expected ceildiv({k_per_cta},{bK}) = {-(-k_per_cta // bK)}")
 
     # ---- grid must cover the output
     def grid_extent(v):
@@ -249,7 +273,36 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     alpha = 1.0
     cur = C_acc
     C_g, c_org = None, None
+    accumulate = False
     for o in post:
+        if isinstance(o, T.AtomicAddOp):
+            # partial tile added into C: element-wise `T.atomic_add(C[by*bM + i, bx*bN + j], C_shared[i, j])`
+            # (examples/gemm_splitk/example_tilelang_gemm_splitk.py:39-40) or the tile form atomic_add(C[...], C_shared)
+            if o.loop is not None or not isinstance(o.dst, T.BufferRegion) or not o.dst.buffer.is_global:
+                _fail("T.atomic_add must add the finished tile into a global tensor after the K loop")
+            if relu or alpha != 1.0:
+                _fail("element-wise epilogue before T.atomic_add")
+            if o.parallel_vars:
+                pv = tuple(o.parallel_vars)
+                if tuple(v.extent for v in pv) != (bM, bN) or not _is_load(o.value, cur, pv):
+                    _fail("T.atomic_add must add `tile[i, j]` of the accumulator for the whole tile")
+                starts = []
+                for d, st in enumerate(o.dst.starts):
+                    lin = as_linear(st)
+                    if lin is None or lin[0].pop(pv[d], 0) != 1 or any(v in lin[0] for v in pv) or len(lin[0]) > 1:
+                        _fail(f"T.atomic_add destination index {st!r} must be tile_origin + parallel index")
+                    base = lin[1]
+                    for v, c in lin[0].items():
+                        base = v * c + lin[1]
+                    starts.append(base)
+                region = T.BufferRegion(o.dst.buffer, starts, (bM, bN))
+            else:
+                if _buf(o.value) is not cur:
+                    _fail("T.atomic_add must add the buffer that holds the accumulator")
+                region = o.dst
+            C_g, c_org = region.buffer, _tile_origin(region, {}, f"T.atomic_add ->{region.buffer.name}")
+            accumulate = True
+            break
         if isinstance(o, T.CopyOp):
             if o.loop is not None:
                 _fail("T.copy inside the K loop after T.gemm")
@@ -263,7 +316,8 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
                 _fail(f"epilogue staging buffer {dst.name} has shape {dst.shape}, expected {(bM, bN)}")
             cur = dst
         elif isinstance(o, T.ElemStore):
-            if o.buffer is not cur or len(o.index) != 2 or tuple(o.index) != tuple(o.parallel_vars):
+            if o.buffer is not cur or len(o.index) != 2 or len(o.parallel_vars) != 2 or \
+                    any(a is not b for a, b in zip(o.index, o.parallel_vars)):
                 _fail("element-wise epilogue must be `C[i, j] = f(C[i, j])` over the whole accumulator tile")
             if tuple(v.extent for v in o.parallel_vars) != (bM, bN):
                 _fail("element-wise epilogue does not cover the accumulator tile")
@@ -288,6 +342,8 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
             _fail("T.clear/T.fill after T.gemm")
     if C_g is None:
         _fail("the accumulator is never copied to a global tensor")
+    if split and not accumulate:
+        _fail("a program that cuts K over a grid dimension must add its partial tiles into C (T.atomic_add)")
     if tuple(C_g.shape) != (M, N):
         _fail(f"output tensor {C_g.name} has shape {C_g.shape}, expected {(M, N)}")
     for (v, sc, off), want_v, ext_ in zip(c_org, (m_var, n_var), (bM, bN)):
@@ -328,6 +384,7 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
                        trans_A=g.transpose_A, trans_B=g.transpose_B, a_param=A_g.param_index, b_param=B_g.param_index,
                        c_param=C_g.param_index, block_M=bM, block_N=bN, block_K=bK, num_stages=kloop.num_stages,
                        threads=tr.threads if isinstance(tr.threads, int) else None, relu=relu, alpha=alpha,
+                       accumulate=accumulate, split_k=split_k,
                        accumulator="tmem" if C_acc.scope == "shared.tmem" else "fragment", rasterization=tr.swizzle,
                        notes=notes)
 
