@@ -13,6 +13,6 @@ import tilelang_mesh_b200 as _impl  # noqa: E402
 
 for _sub in ("language", "jit", "profiler", "autotuner", "layout", "testing", "transform", "utils", "utils.tensor",
              "utils.target", "transform.pass_config", "carver", "carver.arch", "carver.arch.driver", "carver.template",
-             "carver.roller", "carver.roller.rasterization"):
+             "carver.roller", "carver.roller.rasterization", "tvm"):
     sys.modules[__name__ + "." + _sub] = importlib.import_module("tilelang_mesh_b200." + _sub)
 sys.modules[__name__] = _impl

@@ -228,6 +228,14 @@ def test_scaled_epilogue_and_partial_k_loop_rejected():
     ("examples/gemm_splitk/example_tilelang_gemm_splitk.py", "def main()", "matmul(1024, 1024, 1024, 128, 128, 32, 4)"),
     ("examples/gemm_splitk/example_tilelang_gemm_splitk_vectorize_atomicadd.py", "def main()",
      "matmul(1024, 1024, 1024, 128, 128, 32, 4)"),
+    ("examples/warp_specialize/example_warp_specialize_gemm_copy_0_gemm_1.py", "\ndef main(",
+     "matmul_warp_specialize_copy_0_gemm_1(1024, 1024, 1024, 128, 128, 64)"),
+    ("examples/warp_specialize/example_warp_specialize_gemm_copy_1_gemm_0.py", "\ndef main(",
+     "matmul_warp_specialize_copy_1_gemm_0(1024, 1024, 1024, 128, 128, 64)"),
+    ("examples/warp_specialize/example_warp_specialize_gemm_softpipe_stage2.py", "\ndef main(",
+     "matmul(1024, 1024, 1024, 128, 128, 64)"),
+    ("examples/dynamic_shape/example_dynamic.py", "\ndef matmul_dynamic(",
+     'matmul_dynamic_mnk(128, 128, 32, False, False, "float16", "float16", "float32", 3, 128)'),
     ("benchmark/matmul/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
     ("benchmark/matmul_fp8/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
 ])
@@ -366,3 +374,13 @@ def test_splitk_atomic_add_programs():
 
     with pytest.raises(NotAGemmProgram, match="must add its partial tiles"):
         tilelang.compile(sliced_but_overwriting)
+
+
+def test_dynamic_shape_and_warp_specialized_programs():
+    for te_var in (False, True):
+        k = tilelang.compile(P.dynamic_mnk(use_te_var=te_var, trans_B=True))
+        assert k._dynamic and [v.name for v in k._symbols] == ["m", "k", "n"]
+        assert k.program.trans_B and not k.program.trans_A and k.program.block_K == 32
+        assert all(kp.is_dynamic for kp in k.params)
+    k = tilelang.compile(P.warp_specialized(512, 768, 1024), out_idx=[2])
+    assert (k.program.M, k.program.N, k.program.K) == (512, 768, 1024)

@@ -172,6 +172,34 @@ def test_splitk_atomic_add_program_accumulates_into_c():
         assert torch.equal(c, 2 * want)
 
 
+def test_dynamic_shapes_bound_per_call():
+    # examples/dynamic_shape/example_dynamic.py: one kernel object, any (m, n, k); a plan is resolved per shape
+    for ta, tb in ((False, False), (False, True), (True, True)):
+        kern = tilelang.compile(P.dynamic_mnk(trans_A=ta, trans_B=tb))
+        for m, n, k in ((1024, 1024, 1024), (300, 520, 136), (4096, 256, 2048)):
+            a = torch.randint(-3, 4, (k, m) if ta else (m, k), device="cuda").half()
+            b = torch.randint(-3, 4, (n, k) if tb else (k, n), device="cuda").half()
+            c = torch.zeros(m, n, device="cuda", dtype=torch.float16)
+            kern(a, b, c)
+            want = ((a.t() if ta else a).float() @ (b.t() if tb else b).float()).half()
+            assert torch.equal(c, want)
+        assert len(kern._programs) == 3
+        with pytest.raises(ValueError, match="shape mismatch"):  # k of A and B disagree
+            kern(torch.zeros((64, 128) if ta else (128, 64), device="cuda").half(),
+                 torch.zeros((128, 96) if tb else (96, 128), device="cuda").half(), torch.zeros(128, 128, device="cuda").half())
+    kern = tilelang.compile(P.dynamic_mnk(trans_B=True), out_idx=[2])  # output allocated from the bound symbols
+    a = torch.randn(200, 264, device="cuda").half()
+    b = torch.randn(96, 264, device="cuda").half()
+    torch.testing.assert_close(kern(a, b), a @ b.t(), rtol=1e-2, atol=1e-2)
+
+
+def test_warp_specialized_program():
+    kern = tilelang.compile(P.warp_specialized(1024, 768, 512), out_idx=[2])
+    a = torch.randn(1024, 512, device="cuda").half()
+    b = torch.randn(512, 768, device="cuda").half()
+    torch.testing.assert_close(kern(a, b), a @ b, rtol=1e-2, atol=1e-2)  # example's own check (:67)
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

@@ -181,3 +181,59 @@ def splitk_atomic(M, N, K, bM=128, bN=128, bK=32, split_k=4, dtype="float16", ou
                     T.atomic_add(C[by * bM + i, bx * bN + j], c_s[i, j])
 
     return prog
+
+
+def dynamic_mnk(bM=128, bN=128, bK=32, trans_A=False, trans_B=False, dtype="float16", out_dtype="float16", use_te_var=False):
+    """All three extents are shape symbols (the form of examples/dynamic_shape/example_dynamic.py:19-52)."""
+    if use_te_var:
+        from tilelang import tvm
+        M, N, K = tvm.te.var("m"), tvm.te.var("n"), tvm.te.var("k")
+    else:
+        M, N, K = T.dynamic("m"), T.dynamic("n"), T.dynamic("k")
+    a_shape, b_shape = ((K, M) if trans_A else (M, K)), ((N, K) if trans_B else (K, N))
+    a_tile, b_tile = ((bK, bM) if trans_A else (bM, bK)), ((bN, bK) if trans_B else (bK, bN))
+
+    @T.prim_func
+    def prog(A: T.Tensor(a_shape, dtype), B: T.Tensor(b_shape, dtype), C: T.Tensor((M, N), out_dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=128) as (bx, by):
+            a_s = T.alloc_shared(a_tile, dtype)
+            b_s = T.alloc_shared(b_tile, dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            T.clear(acc)
+            for k in T.Pipelined(T.ceildiv(K, bK), num_stages=3):
+                T.copy(A[(k * bK, by * bM) if trans_A else (by * bM, k * bK)], a_s)
+                T.copy(B[(bx * bN, k * bK) if trans_B else (k * bK, bx * bN)], b_s)
+                T.gemm(a_s, b_s, acc, trans_A, trans_B)
+            T.copy(acc, C[by * bM, bx * bN])
+
+    return prog
+
+
+def warp_specialized(M, N, K, bM=128, bN=128, bK=64, dtype="float16"):
+    """Hand-specialised producer / consumer warp groups with user barriers (the form of
+    examples/warp_specialize/example_warp_specialize_gemm_copy_0_gemm_1.py:19-48)."""
+
+    @T.prim_func
+    def prog(A: T.Tensor[(M, K), dtype], B: T.Tensor[(K, N), dtype], C: T.Tensor[(M, N), dtype]):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=256) as (bx, by):
+            a_s = T.alloc_shared((bM, bK), dtype)
+            b_s = T.alloc_shared((bK, bN), dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            ready = T.alloc_barrier(arrive_count=128)
+            done = T.alloc_barrier(arrive_count=128)
+            with T.ws(1):
+                T.clear(acc)
+            for ko in T.Pipelined(T.ceildiv(K, bK), num_stages=0):
+                with T.ws(0):
+                    T.barrier_wait(done, (ko + 1) % 2)
+                    T.copy(A[by * bM, ko * bK], a_s)
+                    T.copy(B[ko * bK, bx * bN], b_s)
+                    T.barrier_arrive(ready)
+                with T.ws(1):
+                    T.barrier_wait(ready, ko % 2)
+                    T.gemm(a_s, b_s, acc)
+                    T.barrier_arrive(done)
+            with T.ws(1):
+                T.copy(acc, C[by * bM, bx * bN])
+
+    return prog

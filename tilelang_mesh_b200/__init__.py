@@ -8,7 +8,7 @@ tcgen05 / TMA kernels.  `compat/tilelang` makes it importable as `tilelang`.
 __version__ = "0.1.0"
 
 from . import language  # noqa: F401
-from . import layout, testing, transform, utils  # noqa: F401
+from . import layout, testing, transform, tvm, utils  # noqa: F401
 from .autotuner import autotune  # noqa: F401
 from .jit import JITKernel, compile, jit, par_compile  # noqa: F401,A004
 from .profiler import Profiler, do_bench  # noqa: F401

@@ -14,6 +14,7 @@ from typing import Any, Callable, Dict, List, Optional
 import torch
 
 from .. import language as T
+from ..language.expr import Expr, Var
 from ..program import BlockScaledProgram, GemmProgram, recognize
 from ..utils.target import determine_target
 from ..utils.tensor import TensorSupplyType, map_torch_type
@@ -27,7 +28,12 @@ class KernelParam:
     """tilelang/engine/param.py: dtype + static shape of one kernel parameter."""
 
     def __init__(self, name: str, dtype: torch.dtype, shape):
-        self.name, self.dtype, self.shape = name, dtype, tuple(int(s) for s in shape)
+        # dynamic dimensions (T.dynamic / tvm.te.var) stay symbolic and are bound from the tensors of each call
+        self.name, self.dtype, self.shape = name, dtype, tuple(s if isinstance(s, Expr) else int(s) for s in shape)
+
+    @property
+    def is_dynamic(self) -> bool:
+        return any(isinstance(s, Expr) for s in self.shape)
 
     def __repr__(self):
         return f"KernelParam({self.name}: {self.dtype}{list(self.shape)})"
@@ -62,8 +68,23 @@ class JITKernel:
         self.target = determine_target(target)
         self.execution_backend = "ctypes"  # one adapter: ctypes over the C ABI
         self.verbose, self.pass_configs, self.compile_flags = verbose, dict(pass_configs or {}), compile_flags
-        self.program = recognize(func)  # GemmProgram or BlockScaledProgram
         self._params = [KernelParam(n, map_torch_type(a.dtype), a.shape) for n, a in func.params]
+        self._dynamic = any(kp.is_dynamic for kp in self._params)
+        self._programs: Dict[tuple, Any] = {}
+        if self._dynamic:
+            # Validate the program's structure once with every shape symbol at a nominal size; the plan itself is
+            # resolved per call from the actual tensor shapes (examples/dynamic_shape/example_dynamic.py).
+            syms = []
+            for kp in self._params:
+                for d in kp.shape:
+                    if isinstance(d, Expr) and not isinstance(d, Var):
+                        raise NotImplementedError("a dynamic dimension must be a plain shape symbol (T.dynamic / te.var)")
+                    if isinstance(d, Var) and not any(d is x for x in syms):
+                        syms.append(d)
+            self._symbols = syms
+            self.program = recognize(func, {v: 1024 for v in syms})
+        else:
+            self.program = recognize(func)  # GemmProgram or BlockScaledProgram
         self._out_idx = _legalize_out_idx(out_idx, len(self._params))
         if any(i != self.program.c_param for i in self._out_idx):
             raise ValueError(f"out_idx {self._out_idx} names an input tensor; the program's only output is parameter "
@@ -99,6 +120,7 @@ class JITKernel:
         it = iter(args)
         for i in range(len(self._params)):
             full.append(None if i in self._out_idx else next(it))
+        env: Dict[Var, int] = {}
         for i, t in enumerate(full):
             if t is None:
                 continue
@@ -107,11 +129,26 @@ class JITKernel:
                 raise ValueError(f"argument {i} ({kp.name}) must be a torch.Tensor")
             if t.dtype != kp.dtype:
                 raise ValueError(f"argument {i} ({kp.name}) dtype mismatch: expected {kp.dtype}, got {t.dtype}")
-            if tuple(t.shape) != kp.shape:
+            ok = t.dim() == len(kp.shape)
+            for want, got in zip(kp.shape, t.shape) if ok else ():
+                if isinstance(want, Var):  # bind the symbol on first sight, then insist on the same value
+                    ok = ok and env.setdefault(want, int(got)) == int(got)
+                else:
+                    ok = ok and want == got
+            if not ok:
                 raise ValueError(f"argument {i} ({kp.name}) shape mismatch: expected {list(kp.shape)}, got {list(t.shape)}")
+        if self._dynamic:
+            missing = [v.name for v in self._symbols if not any(v is k for k in env)]
+            if missing:
+                raise ValueError(f"shape symbols {missing} appear only in output tensors: pass those tensors explicitly")
+            key = tuple(env[v] for v in self._symbols)
+            p = self._programs.get(key)
+            if p is None:
+                p = self._programs[key] = recognize(self.prim_func, env)
         a, b, c = full[p.a_param], full[p.b_param], full[p.c_param]
         if c is None:
-            c = torch.empty(self._params[p.c_param].shape, dtype=self._params[p.c_param].dtype, device=a.device)
+            shape = tuple(env[d] if isinstance(d, Var) else d for d in self._params[p.c_param].shape)
+            c = torch.empty(shape, dtype=self._params[p.c_param].dtype, device=a.device)
         if isinstance(p, BlockScaledProgram):
             hints = {k: v for k, v in self.tile_hints.items() if k in ("cta_group", "block_n", "stages", "raster")}
             G.gemm_blockscaled(a, b, full[p.sa_param], full[p.sb_param], c, **hints)

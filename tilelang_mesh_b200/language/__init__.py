@@ -21,7 +21,8 @@ from .expr import BinOp, Call, Const, Expr, Var, as_affine, evaluate, is_const, 
 __all__ = [
     "prim_func", "Tensor", "StridedTensor", "Buffer", "Kernel", "alloc_shared", "alloc_fragment", "alloc_local",
     "alloc_tmem", "alloc_barrier", "Pipelined", "Persistent", "Parallel", "serial", "grid", "unroll", "copy", "gemm", "gemm_v1",
-    "gemm_v2", "clear", "fill", "use_swizzle", "annotate_layout", "mbarrier_wait_parity", "atomic_add", "max", "min", "ceildiv",
+    "gemm_v2", "clear", "fill", "use_swizzle", "annotate_layout", "mbarrier_wait_parity", "atomic_add", "ws", "barrier_wait",
+    "barrier_arrive", "mbarrier_arrive", "create_list_of_mbarrier", "max", "min", "ceildiv",
     "GemmWarpPolicy", "dynamic", "symbolic", "float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2", "int32",
 ]
 
@@ -63,8 +64,20 @@ class TensorAnnot:
         self.strides = tuple(strides) if strides is not None else None
 
 
-def Tensor(shape, dtype="float32", *args, **kwargs):  # noqa: N802 - reference spelling
-    return TensorAnnot(shape, dtype)
+class _TensorFactory:
+    """`T.Tensor((M, K), dtype)` and the subscript spelling `T.Tensor[(M, K), dtype]` some examples use
+    (examples/warp_specialize/example_warp_specialize_gemm_softpipe_stage2.py:15-17)."""
+
+    def __call__(self, shape, dtype="float32", *args, **kwargs):
+        return TensorAnnot(shape, dtype)
+
+    def __getitem__(self, item):
+        if not isinstance(item, tuple) or len(item) < 1:
+            raise TypeError("T.Tensor[shape, dtype]")
+        return TensorAnnot(item[0], item[1] if len(item) > 1 else "float32")
+
+
+Tensor = _TensorFactory()
 
 
 def StridedTensor(shape, strides, dtype="float32", *args, **kwargs):  # noqa: N802
@@ -293,8 +306,10 @@ def prim_func(fn=None, **_ignored):
 
 
 def dynamic(name: str, dtype: str = "int32"):
-    raise NotImplementedError("dynamic shapes: the B200 backend resolves tile plans per concrete (M, N, K); "
-                              "re-create the kernel per shape (the jit cache is keyed by the factory arguments)")
+    """tilelang/language/__init__.py `T.dynamic` (and `tvm.te.var`, examples/dynamic_shape/example_dynamic.py:19-21):
+    a shape symbol.  The B200 backend resolves a plan per concrete (M, N, K): the symbol is bound from the tensors
+    of each call (jit/__init__.py) and the recognised program is cached per shape."""
+    return Var(str(name), "dyn", None)
 
 
 symbolic = dynamic
@@ -498,6 +513,39 @@ def annotate_layout(layout_map):
 
 def mbarrier_wait_parity(mbarrier, parity):
     """tilelang/language/builtin.py:188.  The kernel's own pipeline owns MMA completion."""
+    return None
+
+
+class ws:  # noqa: N801 - reference spelling `with T.ws(0):`
+    """tilelang/language/warpgroup.py: statements for one warp group of a hand-specialised kernel
+    (examples/warp_specialize/example_warp_specialize_gemm_copy_0_gemm_1.py:32-48).  The B200 kernel has its own
+    fixed producer / MMA / epilogue roles, so the annotation only groups statements here."""
+
+    def __init__(self, *warp_group_ids):
+        self.ids = warp_group_ids
+
+    def __enter__(self):
+        _current_trace()
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def barrier_wait(barrier_id, parity=None):
+    """tilelang/language/builtin.py (alias of mbarrier_wait_parity): the kernel owns its pipeline barriers."""
+    return None
+
+
+def barrier_arrive(barrier_id):
+    return None
+
+
+def mbarrier_arrive(mbarrier):
+    return None
+
+
+def create_list_of_mbarrier(*args):
     return None
 
 

@@ -116,7 +116,19 @@ def _elementwise_staging(o, nm):
     return T.CopyOp(T.BufferRegion(src.buffer, starts, tile.shape), tile, o.loop)
 
 
-def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
+def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgram:
+    """`env` binds dynamic shape symbols (T.dynamic / tvm.te.var) to the sizes of the tensors of one call."""
+    from .language.expr import evaluate
+    env = env or {}
+
+    def cv(x):  # concrete value of a shape entry / extent under `env`
+        if isinstance(x, Expr):
+            try:
+                return int(evaluate(x, env))
+            except KeyError:
+                _fail(f"shape symbol in {x!r} is not bound (dynamic shapes are resolved per call from the tensors)")
+        return x
+
     tr = func.trace()
     if not tr.in_kernel:
         _fail("no T.Kernel frame")
@@ -204,31 +216,21 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
     b_dims = ("N", "K") if g.transpose_B else ("K", "N")
     m_var = classify(a_org, a_dims, "A")
     n_var = classify(b_org, b_dims, "B")
-    M = A_g.shape[1] if g.transpose_A else A_g.shape[0]
-    K = A_g.shape[0] if g.transpose_A else A_g.shape[1]
-    N = B_g.shape[0] if g.transpose_B else B_g.shape[1]
-    K_b = B_g.shape[1] if g.transpose_B else B_g.shape[0]
-    for v in (M, N, K, K_b):
-        if not isinstance(v, int):
-            _fail("dynamic shapes")
+    M = cv(A_g.shape[1] if g.transpose_A else A_g.shape[0])
+    K = cv(A_g.shape[0] if g.transpose_A else A_g.shape[1])
+    N = cv(B_g.shape[0] if g.transpose_B else B_g.shape[1])
+    K_b = cv(B_g.shape[1] if g.transpose_B else B_g.shape[0])
     if K != K_b:
         _fail(f"K of A ({K}) != K of B ({K_b})")
 
     # ---- K loop must cover ceildiv(K, bK)
     ext = kloop.extent
-    ext_v = ext if isinstance(ext, int) else None
-    if ext_v is None:
-        try:
-            from .language.expr import evaluate
-            ext_v = int(evaluate(ext, {}))
-        except Exception:  # noqa: BLE001
-            _fail("K loop extent is not a compile-time constant")
+    ext_v = cv(ext)
     split_k = 1
     k_per_cta = K
     if split:
         zvar, k_per_cta = split[0]
-        from .language.expr import evaluate as _ev
-        split_k = int(_ev(zvar.extent, {}))
+        split_k = cv(zvar.extent)
         if zvar is m_var or zvar is n_var or k_per_cta * split_k != K or k_per_cta % bK:
             _fail(f"split-K slices must tile K exactly: {split_k} slices of {k_per_cta} for K = {K}, block_K = {bK}")
     if ext_v != -(-k_per_cta // bK):
@@ -236,11 +238,7 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
 
     # ---- grid must cover the output
     def grid_extent(v):
-        e = v.extent
-        if isinstance(e, int):
-            return e
-        from .language.expr import evaluate
-        return int(evaluate(e, {}))
+        return cv(v.extent)
 
     if m_var is not None and grid_extent(m_var) != -(-M // bM):
         _fail(f"grid dimension of {m_var!r} is {grid_extent(m_var)}, expected ceildiv(M, block_M) = {-(-M // bM)}")
@@ -344,7 +342,7 @@ def recognize_gemm(func: "T.PrimFunc") -> GemmProgram:
         _fail("the accumulator is never copied to a global tensor")
     if split and not accumulate:
         _fail("a program that cuts K over a grid dimension must add its partial tiles into C (T.atomic_add)")
-    if tuple(C_g.shape) != (M, N):
+    if tuple(cv(x) for x in C_g.shape) != (M, N):
         _fail(f"output tensor {C_g.name} has shape {C_g.shape}, expected {(M, N)}")
     for (v, sc, off), want_v, ext_ in zip(c_org, (m_var, n_var), (bM, bN)):
         if off != 0 or (want_v is None and v is not None) or (want_v is not None and (v is not want_v or sc != ext_)):
@@ -592,10 +590,10 @@ def recognize_blockscaled(func: "T.PrimFunc") -> BlockScaledProgram:
                               num_stages=kloop.num_stages, rasterization=tr.swizzle)
 
 
-def recognize(func: "T.PrimFunc"):
+def recognize(func: "T.PrimFunc", env: Optional[dict] = None):
     """GEMM family first; a program that is not one may still be the block-scaled form."""
     try:
-        return recognize_gemm(func)
+        return recognize_gemm(func, env)
     except NotAGemmProgram as first:
         try:
             return recognize_blockscaled(func)
