@@ -236,6 +236,14 @@ def test_scaled_epilogue_and_partial_k_loop_rejected():
      "matmul(1024, 1024, 1024, 128, 128, 64)"),
     ("examples/dynamic_shape/example_dynamic.py", "\ndef matmul_dynamic(",
      'matmul_dynamic_mnk(128, 128, 32, False, False, "float16", "float16", "float32", 3, 128)'),
+    ("testing/python/tilelibrary/test_tilelang_tilelibrary_gemm.py", "\nif __name__", 'tilelang.compile(matmul_rs(512, 1024, 768, '
+     '128, 256, 32, False, True, "float16", "float16", "float32", 2, 128), out_idx=[2])'),
+    ("testing/python/tilelibrary/test_tilelang_tilelibrary_gemm.py", "\nif __name__", 'tilelang.compile(matmul_rr(512, 1024, 768, '
+     '128, 256, 32, True, False, "bfloat16", "bfloat16", "float32", 2, 128), out_idx=[2])'),
+    ("testing/python/kernel/test_tilelang_kernel_gemm.py", "\nif __name__", 'tilelang.compile(matmul(512, 1024, 768, 128, 128, 32, '
+     'False, True, "float32", "float32", "float32", 2, 128), out_idx=[2])'),
+    ("testing/python/kernel/test_tilelang_kernel_fp8_gemm.py", "\nif __name__", 'tilelang.compile(matmul_nt(1024, 1024, 1024, 128, '
+     '128, 64, "float8_e4m3", "bfloat16", "float32"), out_idx=[-1])'),
     ("benchmark/matmul/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
     ("benchmark/matmul_fp8/benchmark_matmul.py", 'if __name__ == "__main__":', "matmul(8192, 8192, 8192, False)"),
 ])
@@ -384,3 +392,30 @@ def test_dynamic_shape_and_warp_specialized_programs():
         assert all(kp.is_dynamic for kp in k.params)
     k = tilelang.compile(P.warp_specialized(512, 768, 1024), out_idx=[2])
     assert (k.program.M, k.program.N, k.program.K) == (512, 768, 1024)
+
+
+@pytest.mark.parametrize("a_frag,b_frag", [(True, False), (False, True), (True, True)], ids=["rs", "sr", "rr"])
+def test_fragment_operand_forms(a_frag, b_frag):
+    k = tilelang.compile(P.fragment_operands(512, 384, 256, a_frag, b_frag), out_idx=[2])
+    assert (k.program.M, k.program.N, k.program.K) == (512, 384, 256)
+    assert sum("fragment copy" in n for n in k.program.notes) == int(a_frag) + int(b_frag)
+
+
+def test_fragment_operand_must_be_a_plain_copy_of_a_shared_tile():
+    @T.prim_func
+    def stale(A: T.Tensor((256, 256), "float16"), B: T.Tensor((256, 256), "float16"), C: T.Tensor((256, 256), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((128, 32), "float16")
+            a_f = T.alloc_fragment((128, 32), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            T.copy(a_s, a_f)  # outside the K loop: every iteration would multiply the same stale tile
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                T.copy(B[bx * 128, k * 32], b_s)
+                T.gemm(a_f, b_s, acc, transpose_B=True)
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="not a plain copy of a shared tile"):
+        tilelang.compile(stale)

@@ -200,6 +200,21 @@ def test_warp_specialized_program():
     torch.testing.assert_close(kern(a, b), a @ b, rtol=1e-2, atol=1e-2)  # example's own check (:67)
 
 
+@pytest.mark.parametrize("a_frag,b_frag", [(True, False), (False, True), (True, True)], ids=["rs", "sr", "rr"])
+@pytest.mark.parametrize("ta,tb", [(False, True), (True, False)], ids=["nt", "tn"])
+def test_fragment_operand_forms_on_gpu(a_frag, b_frag, ta, tb):
+    # the reference's run_gemm_rs / _sr / _rr cases (test_tilelang_tilelibrary_gemm.py), checked the way they are:
+    # profiler.assert_allclose against torch.matmul of the (transposed) inputs, rtol = atol = 1e-2
+    kern = tilelang.compile(P.fragment_operands(512, 1024, 768, a_frag, b_frag, 128, 256, 32, ta, tb), out_idx=[2])
+
+    def ref_program(A, B):
+        A = A.T if ta else A
+        B = B.T if tb else B
+        return torch.matmul(A.float(), B.float()).half()
+
+    kern.get_profiler(tilelang.TensorSupplyType.Normal).assert_allclose(ref_program, atol=1e-2, rtol=1e-2)
+
+
 def test_kernel_source_and_multi_stream():
     kern = tilelang.compile(P.nt_fragment(512, 512, 512, dtype="bfloat16"), out_idx=[2])
     assert "tcgen05.mma" in kern.get_kernel_source(kernel_only=False)

@@ -237,3 +237,31 @@ def warp_specialized(M, N, K, bM=128, bN=128, bK=64, dtype="float16"):
                 T.copy(acc, C[by * bM, bx * bN])
 
     return prog
+
+
+def fragment_operands(M, N, K, a_frag=True, b_frag=False, bM=128, bN=128, bK=32, trans_A=False, trans_B=True, dtype="float16"):
+    """Operands handed to T.gemm as register fragments copied from their shared tiles: the gemm_rs / gemm_sr / gemm_rr
+    forms (testing/python/tilelibrary/test_tilelang_tilelibrary_gemm.py:137-186 and the sr / rr siblings)."""
+    a_shape, b_shape = ((K, M) if trans_A else (M, K)), ((N, K) if trans_B else (K, N))
+    a_tile, b_tile = ((bK, bM) if trans_A else (bM, bK)), ((bN, bK) if trans_B else (bK, bN))
+
+    @T.prim_func
+    def prog(A: T.Tensor(a_shape, dtype), B: T.Tensor(b_shape, dtype), C: T.Tensor((M, N), dtype)):
+        with T.Kernel(T.ceildiv(N, bN), T.ceildiv(M, bM), threads=128) as (bx, by):
+            a_s = T.alloc_shared(a_tile, dtype)
+            b_s = T.alloc_shared(b_tile, dtype)
+            a_f = T.alloc_fragment(a_tile, dtype)
+            b_f = T.alloc_fragment(b_tile, dtype)
+            acc = T.alloc_fragment((bM, bN), "float")
+            T.clear(acc)
+            for k in T.Pipelined(T.ceildiv(K, bK), num_stages=2):
+                T.copy(A[(k * bK, by * bM) if trans_A else (by * bM, k * bK)], a_s)
+                T.copy(B[(bx * bN, k * bK) if trans_B else (k * bK, bx * bN)], b_s)
+                if a_frag:
+                    T.copy(a_s, a_f)
+                if b_frag:
+                    T.copy(b_s, b_f)
+                T.gemm_v2(a_f if a_frag else a_s, b_f if b_frag else b_s, acc, trans_A, trans_B)
+            T.copy(acc, C[by * bM, bx * bN])
+
+    return prog

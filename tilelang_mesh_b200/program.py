@@ -140,6 +140,23 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
         _fail("T.gemm is not inside a T.Pipelined / T.serial K loop")
     kloop = next(li for li in tr.loops if li.var is g.loop)
     A_s, B_s, C_acc = _buf(g.A), _buf(g.B), _buf(g.C)
+    notes = []
+
+    def through_fragment(b, nm):
+        # gemm_rs / gemm_sr / gemm_rr forms of the reference's tile-library tests (matmul_rs: T.copy(A_shared, A_frag);
+        # T.gemm(A_frag, ...), testing/python/tilelibrary/test_tilelang_tilelibrary_gemm.py:137-186): the register copy
+        # of an operand tile is the same tile, so follow it back to the shared buffer that was filled from global.
+        if b.scope != "local.fragment":
+            return b
+        cs = [o for o in tr.ops if isinstance(o, T.CopyOp) and _buf(o.dst) is b]
+        if len(cs) != 1 or cs[0].loop is not g.loop or isinstance(cs[0].src, T.BufferRegion) or \
+                _buf(cs[0].src).is_global or tuple(_buf(cs[0].src).shape) != tuple(b.shape) or _buf(cs[0].src).dtype != b.dtype:
+            _fail(f"T.gemm operand {nm} is a fragment that is not a plain copy of a shared tile filled in the same K loop")
+        notes.append(f"operand {nm} read from a fragment copy of its shared tile (gemm_{'r' if nm == 'A' else 's'}* form): "
+                     "tcgen05.mma reads the shared tile directly")
+        return _buf(cs[0].src)
+
+    A_s, B_s = through_fragment(A_s, "A"), through_fragment(B_s, "B")
     for nm, b in (("A", A_s), ("B", B_s)):
         if b.is_global or not b.scope.startswith("shared") or b.scope in ("shared.tmem", "shared.barrier"):
             _fail(f"T.gemm operand {nm} must be a shared-memory tile (gemm_ss); got scope {b.scope!r} "
@@ -373,7 +390,6 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
         if C_g.dtype not in ("float16", "bfloat16", "float32", "float8_e4m3", "float8_e5m2"):
             _fail(f"output dtype {C_g.dtype}")
 
-    notes = []
     if C_acc.dtype == "float16":
         notes.append("accum_dtype float16 widened to float32 (single rounding to the output dtype)")
     if g.wg_wait not in (0, -1):

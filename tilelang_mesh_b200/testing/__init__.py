@@ -41,6 +41,18 @@ def requires_cuda_compute_version_eq(major, minor=0):
     return requires_cuda_compute_version(major, minor, "eq")
 
 
+def requires_cuda_compute_version_gt(major, minor=0):
+    return requires_cuda_compute_version(major, minor, "gt")
+
+
+def requires_cuda_compute_version_lt(major, minor=0):
+    return requires_cuda_compute_version(major, minor, "lt")
+
+
+def requires_cuda_compute_version_le(major, minor=0):
+    return requires_cuda_compute_version(major, minor, "le")
+
+
 def main():
     frame = sys._getframe(1)
     sys.exit(pytest.main([frame.f_globals["__file__"]] + sys.argv[1:]))
