@@ -31,7 +31,7 @@ M_PER_GPU, N_DIM, K_DIM = 8192, 8192, 8192
 NOMINAL = {"bf16": 2250.0, "fp8": 4500.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel bench.py times, from the
 # `ncu --set full` captures profiles/prof_bf16_r1d.txt and profiles/prof_fp8_r1d.txt (8192^3, default plan).
-NCU_DRAM_TRAFFIC = {"bf16": 876_832_768 + 120_963_584, "fp8": 228_951_808 + 116_029_184}
+NCU_DRAM_TRAFFIC = {"bf16": 853_894_912 + 119_959_296, "fp8": 229_277_440 + 115_448_832}
 METRIC = {"bf16": "GEMM TFLOP/s (bf16, 8192^3 per GPU, fp32 accumulate)",
           "fp8": "GEMM TFLOP/s (fp8 e4m3, 8192^3 per GPU, per-tensor scales, fp32 accumulate)"}
 
@@ -264,7 +264,7 @@ def run_ours(args):
                            ((a.numel() * a.element_size() + b.numel() * b.element_size()) >> 20)},
                 "roofline": {"bound": "tensor", "achieved": round(per_gpu, 2), "peak": round(peak, 1), "unit": "TFLOP/s",
                              "frac": round(per_gpu / peak, 4), "traffic": NCU_DRAM_TRAFFIC[args.dtype],
-                             "traffic_source": "ncu capture profiles/prof_%s_r1d.txt (bytes per launch)" % ("fp8" if fp8 else "bf16"),
+                             "traffic_source": "ncu capture profiles/prof_%s_r1e.txt (bytes per launch)" % ("fp8" if fp8 else "bf16"),
                              "peak_kind": ("sustained" if sustained else "burst") + (" x2 (fp8)" if fp8 else "") + ", " + peaks["source"],
                              "frac_nominal": round(per_gpu / NOMINAL[args.dtype], 4), "nominal_peak": NOMINAL[args.dtype],
                              "algorithmic_flop_per_launch": flop_step,
