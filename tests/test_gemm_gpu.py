@@ -441,3 +441,38 @@ def test_host_buffer_entry_point(m, n, k):
     assert rc == 0, _abi.last_error()
     assert torch.equal(c, (a.float() @ b.float().t()).bfloat16())
     assert lib.tlb200_gemm_host(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), need - 1, None) != 0
+
+
+def test_cuda_graph_capture_and_replay():
+    # tlb200_gemm encodes its tensor maps on the host and makes one launch on the given stream: it can be captured.
+    # A launch-bound chain of small contractions replayed from a graph must give the same bits as eager calls.
+    a, b = operands(256, 256, 256, torch.bfloat16, kind="int")
+    w = [rand((256, 256), torch.bfloat16, "int") for _ in range(4)]
+    x0 = torch.empty(256, 256, device="cuda", dtype=torch.bfloat16)
+    xs = [torch.empty_like(x0) for _ in range(4)]
+
+    def chain():
+        G.gemm(a, b, x0, alpha=2.0 ** -8)
+        src = x0
+        for wi, xi in zip(w, xs):
+            G.gemm(src, wi, xi, alpha=2.0 ** -8)
+            src = xi
+
+    chain()
+    torch.cuda.synchronize()
+    eager = [t.clone() for t in xs]
+    for t in xs:
+        t.zero_()
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        chain()  # warm-up on the capture stream (descriptor cache, device init)
+        with torch.cuda.graph(g, stream=side):
+            chain()
+    torch.cuda.current_stream().wait_stream(side)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for got, want in zip(xs, eager):
+        assert bit_equal(got, want)

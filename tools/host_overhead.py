@@ -26,3 +26,15 @@ import tilelang  # noqa: E402
 import tile_programs as P  # noqa: E402
 kern = tilelang.compile(P.nt_fragment(256, 256, 256, 128, 128, 32, dtype="bfloat16"), out_idx=[2])
 print("JITKernel(a, b)           : host %.1f us/call, incl. drain %.1f us/call" % wall(lambda: kern(a, b)))
+# the same tiny contraction replayed from a CUDA graph of 100 launches: the per-launch cost without the host path
+g = torch.cuda.CUDAGraph()
+side = torch.cuda.Stream()
+side.wait_stream(torch.cuda.current_stream())
+with torch.cuda.stream(side):
+    G.gemm(a, b, c)
+    with torch.cuda.graph(g, stream=side):
+        for _ in range(100):
+            G.gemm(a, b, c)
+torch.cuda.current_stream().wait_stream(side)
+h, d = wall(lambda: g.replay(), n=100)
+print("graph of 100 x G.gemm     : %.2f us per contraction (replay incl. drain)" % (d / 100))
