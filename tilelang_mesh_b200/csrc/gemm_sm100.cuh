@@ -386,6 +386,11 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+  // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may
+  // overlap the tail of the previous kernel in the stream; the next kernel may start its own set-up now.  The warps
+  // that read or write global memory wait for the previous grid first (producers before the first TMA load,
+  // epilogue warps before the first store).
+  griddep_launch_dependents();
 
   const int tiles_n_c = (p.tiles_n + kMc - 1) / kMc;  // column tiles per cluster step (kMc neighbours at a time)
   const int tiles_mn = p.tiles_m * tiles_n_c;
@@ -444,6 +449,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
     int s = 0;
     uint32_t ph = 0;
+    griddep_wait();
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       int tm, tn, grp, row_base, row_limit;
       tile_coord(t, tm, tn, grp, row_base, row_limit);
@@ -591,6 +597,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     int as = 0;
     uint32_t aph = 0;
     int slab_iter = 0;
+    griddep_wait();
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       int tm, tn, grp, row_base, row_limit;
       tile_coord(t, tm, tn, grp, row_base, row_limit);
@@ -624,7 +631,11 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       }
       if constexpr (kNSub == 2) { aph ^= 1u; } else if (++as == acc_stages) { as = 0; aph ^= 1u; }
     }
-    if (p.epi_tma && lane == 0) tma_store_wait_all<0>();
+    // The staging slabs must have been read before the CTA's shared memory goes away; the writes themselves are
+    // complete when the grid is.  Stores into peer GPUs' memory are waited for in full.
+    if (p.epi_tma && lane == 0) {
+      if (p.n_peer > 0) tma_store_wait_all<0>(); else tma_store_wait_read<0>();
+    }
   }
 
   // ---- teardown: nobody may still be using TMEM / peer smem when it is released

@@ -132,6 +132,13 @@ __device__ __forceinline__ void cluster_sync_all() {
                    : "memory");
 }
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// `griddep_wait` blocks until the grids this launch depends on have completed and their memory is visible (a no-op
+// for a launch without the programmatic-serialization attribute); `griddep_launch_dependents` lets the next launch
+// of the stream begin its own set-up while this grid is still running.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* desc) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(desc)) : "memory");

@@ -884,13 +884,17 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   cfg.blockDim = dim3(pl.threads, 1, 1);
   cfg.dynamicSmemBytes = pl.smem_bytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = pl.cta_group * r.mc;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  // programmatic dependent launch: this grid's set-up may overlap the previous kernel's tail (the kernel waits
+  // with griddepcontrol.wait before it touches global memory)
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   e = cudaLaunchKernelEx(&cfg, r.mc == 2 ? pick_kernel_mc(mma_kind_of(d->ab_dtype)) : pick_kernel(pl.cta_group, mma_kind_of(d->ab_dtype), r.n_sub), kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
