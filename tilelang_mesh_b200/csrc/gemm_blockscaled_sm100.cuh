@@ -194,8 +194,11 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
   if (warp < kEpiWarp0) {
     // ===================================================== control warpgroup: give registers away
     setmaxnreg_dec<56>();
-    if (warp == 0) {
-      // ---- TMA producer
+    if (warp != 1) {
+      // ---- TMA producers: warps 0, 2, 3 take the K blocks round-robin (at most `stages` of them; gemm_sm100.cuh)
+      const int kProducers = stages < 3 ? stages : 3;
+      const int pidx = warp == 0 ? 0 : warp - 1;
+      int turn = 0;
       const bool elected = elect_one();
       const uint64_t pol = p.l2_policy == 1 ? policy_evict_normal() : policy_evict_last();
       int s = 0;
@@ -206,8 +209,10 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
         const int row_a = (tm * kCta + (int)cta_rank) * kBlockM;
         const int row_b = tn * kBN + (int)cta_rank * kBRows;
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
-          if (elected) {
+          const bool mine = turn == pidx;
+          if (++turn == kProducers) turn = 0;
+          if (mine) mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
+          if (mine && elected) {
             const uint32_t full = bar_full + 8 * s;
             if (leader) mbar_arrive_expect_tx(full, kStageBytes * kCta);
             const int k0 = kb * kStageRowBytes;  // fp8: one element per byte
@@ -223,8 +228,8 @@ gemm_blockscaled_kernel(const __grid_constant__ BlockScaledParams p) {
           if (++s == stages) { s = 0; ph ^= 1u; }
         }
       }
-    } else if (warp == 1 && leader) {
-      // ---- MMA issuer: every K block starts a fresh partial sum in TMEM buffer `as`
+    } else if (leader) {
+      // ---- MMA issuer (warp 1): every K block starts a fresh partial sum in TMEM buffer `as`
       const bool elected = elect_one();
       const uint64_t hi = static_cast<uint64_t>(p.desc_hi) << 32 | (1u << 16);
       const uint32_t a_lo0 = (smem_a & 0x3FFFFu) >> 4, b_lo0 = (smem_b & 0x3FFFFu) >> 4;
