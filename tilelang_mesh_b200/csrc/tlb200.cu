@@ -733,8 +733,23 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
-  const bool allow_mc = n_groups == 0;  // grouped row tiles are not paired up across column tiles
+  bool allow_mc = n_groups == 0;  // grouped row tiles are not paired up across column tiles
   if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b, allow_mc)) return rc;
+  if (r.mc == 2) {
+    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+    // memory hung the GPU: the multicast plan is used only when the A the kernel will read (the caller's, or its
+    // re-pitched copy in the workspace) is ordinary device memory of the current device.
+    const void* a_src = r.copy_a ? ws : a;
+    cudaPointerAttributes pa;
+    const bool own = a_src && cudaPointerGetAttributes(&pa, a_src) == cudaSuccess && pa.type == cudaMemoryTypeDevice && pa.device == dev;
+    if (!own) {
+      cudaGetLastError();
+      if (d->cfg_cta_group == 4)
+        return fail("tlb200_gemm: cfg_cta_group=4 (A multicast) needs A in the current device's own memory");
+      allow_mc = false;
+      if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b, allow_mc)) return rc;
+    }
+  }
   if (r.split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
   if (r.ws_bytes > 0) {
     if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
