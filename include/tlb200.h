@@ -81,7 +81,9 @@ typedef struct tlb200_gemm_desc {
   float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
   uint32_t epilogue;  /* TLB200_EPI_* */
   int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles, 4 = two such pairs per cluster
-                            on neighbouring column tiles, every A box fetched once and TMA-multicast to both */
+                            on neighbouring column tiles, every A box fetched once and TMA-multicast to both
+                            (only when A lies in the current device's own memory; chosen automatically under
+                            the same condition) */
   int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] or of 64 in (256,512] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
