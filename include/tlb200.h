@@ -102,7 +102,7 @@ typedef struct tlb200_gemm_plan {
   int32_t umma_n, epi_warps; /* N of one tcgen05.mma (block_n / accumulators per tile); epilogue warps */
   int32_t split_k;           /* K slices per tile (1 = no split-K) */
   int32_t multicast; /* 2 when A boxes are multicast across two pairs (cluster of 4 CTAs), else 1 */
-  int64_t workspace_bytes;   /* device scratch tlb200_gemm_ex needs for this plan (0 when split_k == 1) */
+  int64_t workspace_bytes;   /* device scratch tlb200_gemm_ex can use for this plan (split-K, tail split, re-pitched operands) */
 } tlb200_gemm_plan;
 
 /* Replaces the generated `int init()` (wrapper.py:40-44): binds the CUDA
@@ -118,11 +118,18 @@ int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void
                 void* stream);
 
 /* tlb200_gemm with a caller-owned device workspace (scratch memory; 256-byte
- * aligned) of at least tlb200_gemm_workspace_bytes(desc) bytes.  Two things
+ * aligned) of at least tlb200_gemm_workspace_bytes(desc) bytes.  Three things
  * use it:
  *  - split-K (the reference's examples/gemm_splitk idea): when the output has
  *    too few tiles to fill the GPU, K is cut into slices accumulated in fp32 in
  *    the workspace and summed in slice order by a second kernel;
+ *  - the tail split (stream-K's remedy for wave quantisation, cf. the reference's
+ *    examples/gemm_streamk): when the last wave of whole tiles would occupy
+ *    only a fraction of the GPU, just those tiles are cut along K over all
+ *    clusters, their fp32 partial tiles go to the workspace and a small second
+ *    kernel sums them in slice order.  Optional: a workspace that lacks this
+ *    part runs the ordinary schedule.  cfg_split_k = 1 switches it off, -1
+ *    forces it whenever the shape allows it;
  *  - operands TMA cannot address (row pitch or base not a multiple of 16 bytes,
  *    e.g. K = 763 fp16 - the reference's test_pad_* cases, which it serves
  *    with SIMT copies, src/op/copy.cc:823-855) are first re-pitched into it.

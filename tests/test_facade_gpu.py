@@ -286,7 +286,10 @@ def test_matches_reference_lineage_tcgen05_kernel(tmp_path):
     c = kern(a, b)
     # both accumulate in fp32 and round once: they may differ by a bf16 ulp where the K order differs
     diff = (c.float() - c_ref.float()).abs()
-    ulp = c_ref.float().abs().clamp_min(1e-3) * 2.0**-7
+    # (tiles of a split tail wave add their K slices' fp32 sums in a different order: with |terms| ~ 1 and sums of
+    # magnitude ~90 over K = 8192 that moves an fp32 result by up to ~1e-3 absolute, which near zero is many bf16
+    # ulps - hence the absolute floor; elsewhere one bf16 ulp of the larger neighbour across a binade edge)
+    ulp = (c_ref.float().abs() * 2.0**-6).clamp_min(4e-3)
     assert (diff <= ulp).all(), f"max diff {diff.max().item()}"
     frac_equal = (c.view(torch.int16) == c_ref.view(torch.int16)).float().mean().item()
     assert frac_equal > 0.95

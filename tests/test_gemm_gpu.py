@@ -476,3 +476,50 @@ def test_cuda_graph_capture_and_replay():
     torch.cuda.synchronize()
     for got, want in zip(xs, eager):
         assert bit_equal(got, want)
+
+
+@pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.float32), (torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.float16),
+                                    (torch.float16, torch.float8_e4m3fn)])
+@pytest.mark.parametrize("cfg", [dict(cta_group=2, block_n=128), dict(cta_group=1, block_n=256), dict(cta_group=2, block_n=256)])
+def test_tail_split_bit_exact(dt, out, cfg):
+    # cfg_split_k = -1: the tiles of the last, partial wave are cut along K over all clusters and summed by a
+    # second kernel.  Same bits as the ordinary schedule on exactly representable inputs, ragged edges included.
+    m, n, k = 2000, 2504, 2048
+    a, b = operands(m, n, k, dt, kind="int")
+    plan = G.plan(m, n, k, dt, out, split_k=-1, **cfg)
+    assert plan["workspace_bytes"] > 0 and plan["split_k"] == 1, "the shape must leave a partial last wave"
+    want = ((a.float() @ b.float().t()) * 2.0 ** -5).to(out)
+    big = torch.full((m + 2, n + 8), -1.0, device="cuda").to(out)
+    G.gemm(a, b, big[:m, :n], alpha=2.0 ** -5, split_k=-1, **cfg)
+    assert torch.equal(big[:m, :n].float(), want.float())
+    assert (big[m:].float() == -1).all() and (big[:, n:].float() == -1).all()
+    assert bit_equal(G.gemm(a, b, out_dtype=out, alpha=2.0 ** -5, split_k=1, **cfg), want)  # switched off: same result
+
+
+def test_tail_split_epilogues_and_small_workspace():
+    m, n, k = 2048, 2560, 2048
+    a, b = operands(m, n, k, torch.bfloat16, kind="int")
+    cfg = dict(cta_group=2, block_n=128, split_k=-1)
+    ref = a.float() @ b.float().t()
+    assert torch.equal(G.gemm(a, b, out_dtype=torch.float32, relu=True, **cfg), torch.relu(ref))
+    c0 = torch.randint(-8, 9, (m, n), device="cuda").float()
+    c = c0.clone()
+    G.gemm(a, b, c, accumulate=True, **cfg)
+    assert torch.equal(c, ref + c0)
+    # through the C ABI with a workspace that lacks the tail part: the ordinary schedule runs, same result
+    lib = _abi.load()
+    d = G.make_desc(m, n, k, _abi.BFLOAT16, _abi.FLOAT32, 0, 1, k, k, n, **cfg)
+    need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(d))
+    assert need > 0
+    out = torch.empty(m, n, device="cuda")
+    small = torch.empty(1024, dtype=torch.uint8, device="cuda")
+    n0 = lib.tlb200_launch_count()
+    _abi.check(lib.tlb200_gemm_ex(ctypes.byref(d), a.data_ptr(), b.data_ptr(), out.data_ptr(), small.data_ptr(), small.numel(),
+                                  torch.cuda.current_stream().cuda_stream), "tlb200_gemm_ex")
+    assert lib.tlb200_launch_count() - n0 == 1 and torch.equal(out, ref)
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    out.zero_()
+    n0 = lib.tlb200_launch_count()
+    _abi.check(lib.tlb200_gemm_ex(ctypes.byref(d), a.data_ptr(), b.data_ptr(), out.data_ptr(), ws.data_ptr(), need,
+                                  torch.cuda.current_stream().cuda_stream), "tlb200_gemm_ex")
+    assert lib.tlb200_launch_count() - n0 == 2 and torch.equal(out, ref)  # GEMM + tail reduction

@@ -54,6 +54,13 @@ struct alignas(64) GemmKernelParams {
   int n_peer;        // number of additional destinations (0 = single-GPU store)
   // grouped GEMM (examples/grouped_gemm): rows [group_row[g], group_row[g+1]) of A and C use B block g.
   // tiles_m then counts the row tiles of all groups; group_tile[g] is the first row tile of group g.
+  // Tail split: the tiles of the last, partial wave are cut into K slices so that the whole machine works on them
+  // (a stream-K style fix of wave quantisation).  Work items [0, tail_begin) are whole tiles; item tail_begin +
+  // s * tail_tiles + j is K slice s of tile tail_begin + j and stores raw fp32 partial sums as tile (s * tail_tiles + j)
+  // of the workspace matrix [tail_split * tail_tiles * block_m rows, block_n columns]; a reduction kernel finishes them.
+  CUtensorMap tm_ws;
+  void* ws;
+  int tail_begin, tail_tiles, tail_split, tail_kb;  // tail_tiles == 0: off
   int n_groups;      // 0 = ordinary GEMM
   int b_group_rows;  // rows of one group's B in the 2-D view TMA sees (N if K-major, K if N-major)
   int group_row[kMaxGroups + 1];
@@ -190,11 +197,23 @@ __device__ __forceinline__ float epi_value(uint32_t raw, float alpha, bool relu,
   }
 }
 
+// Where and how one tile's accumulator is written: the final C (cast, alpha, relu, optional += C), or - for the K
+// slices of a split tail tile - raw fp32 partial sums into the caller's workspace.
+struct EpiOut {
+  const CUtensorMap* tm;  // TMA-store map (valid iff tma)
+  void* c;
+  long long ldc;
+  int n;                  // columns of the destination matrix (stores are clipped to it)
+  float alpha;
+  int relu, accumulate, tma, n_peer;
+  int evict_first;        // C is write-once: keep it from displacing the operands in L2
+};
+
 // ---------------------------------------------------------------- epilogue for one tile
 // Executed by the 4 epilogue warps.  Warp `q` owns TMEM lanes / tile rows [32q, 32q+32).
 // tmem_acc = TMEM address of the accumulator (lane 0, first column).
 template <int kOut>
-__device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_t tmem_acc, int q,
+__device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const EpiOut& o, uint32_t tmem_acc, int q,
                                               int lane, int row0, int row_limit, int row_off, int col0, int cbeg, int cend,
                                               uint32_t stage_smem, int nslabs, int& slab_iter) {
   constexpr int kOB = OutTraits<kOut>::kBytes;
@@ -203,21 +222,21 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
   constexpr int kValsPerPacket = 16 / kOB;
   const int grow = row0 + q * 32 + lane;  // global row of this thread
   const uint32_t lane_taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
-  const float alpha = p.alpha;
-  const bool relu = p.relu != 0;
+  const float alpha = o.alpha;
+  const bool relu = o.relu != 0;
   const bool acc_int = p.acc_int != 0;
 
   // A TMA store writes the warp's whole 32-row slab: use it only when all 32 rows belong to this tile's
   // row range (always true for an ordinary GEMM, where the tensor map clips at M; a grouped GEMM's last
   // row tile of a group falls back to predicated stores).
   const bool slab_rows_ok = p.n_groups == 0 || row0 + q * 32 + 32 <= row_limit;
-  if (p.epi_tma && slab_rows_ok) {
+  if (o.tma && slab_rows_ok) {
     // Per 128-byte-wide slab: TMEM loads (two x32 loads in flight) and the cast run BEFORE waiting
     // for the TMA store that last read the slab, so that store's smem read is hidden behind them.
     constexpr int kLdsPerSlab = kColsPerSlab / 32;
     constexpr int kPair = kLdsPerSlab >= 2 ? 2 : 1;
     for (int cs = cbeg; cs < cend; cs += kColsPerSlab) {
-      if (col0 + cs >= p.n) break;  // warp-uniform: remaining slabs are fully out of range
+      if (col0 + cs >= o.n) break;  // warp-uniform: remaining slabs are fully out of range
       const uint32_t slab = stage_smem + (nslabs == 2 ? (slab_iter & 1) : 0) * kEpiBufBytes;
       bool slab_free = false;
 #pragma unroll
@@ -260,10 +279,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       if (lane == 0) {
         if (row0 + q * 32 < row_limit) {
           // C is write-once: evict_first keeps the operands in L2
-          if (p.l2_policy != 1) tma_store_2d_hint(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
-          else tma_store_2d(&p.tm_c, slab, col0 + cs, row_off + row0 + q * 32);
+          if (o.evict_first) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
+          else tma_store_2d(o.tm, slab, col0 + cs, row_off + row0 + q * 32);
           // fused all-gather: the same slab goes straight into every peer GPU's C over NVLink
-          for (int g = 0; g < p.n_peer; ++g) tma_store_2d(&p.tm_c_peer[g], slab, col0 + cs, row_off + row0 + q * 32);
+          for (int g = 0; g < o.n_peer; ++g) tma_store_2d(&p.tm_c_peer[g], slab, col0 + cs, row_off + row0 + q * 32);
         }
         tma_store_commit();
       }
@@ -271,9 +290,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
     }
   } else {
     const bool row_ok = grow < row_limit;
-    const bool vec_ok = ((p.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(p.c) % 16) == 0);
+    const bool vec_ok = ((o.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(o.c) % 16) == 0);
     for (int cs = cbeg; cs < cend; cs += 32) {
-      if (col0 + cs >= p.n) break;
+      if (col0 + cs >= o.n) break;
       uint32_t r[32];
       tmem_ld_32x32(lane_taddr + cs, r);
       tmem_ld_wait();
@@ -284,22 +303,22 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, uint32_
       }
       if (row_ok) {
         const int gcol = col0 + cs;
-        const long long base = static_cast<long long>(grow + row_off) * p.ldc + gcol;
-        if (p.accumulate) {  // C += ...: every element is owned by exactly one thread of one CTA, no atomics needed
+        const long long base = static_cast<long long>(grow + row_off) * o.ldc + gcol;
+        if (o.accumulate) {  // C += ...: every element is owned by exactly one thread of one CTA, no atomics needed
 #pragma unroll
           for (int i = 0; i < 32; ++i)
-            if (gcol + i < p.n) v[i] += load_out<kOut>(p.c, base + i);
+            if (gcol + i < o.n) v[i] += load_out<kOut>(o.c, base + i);
         }
-        for (int g = -1; g < p.n_peer; ++g) {  // g == -1: the local C; others: peer GPUs' copies
-          void* cdst = g < 0 ? p.c : p.c_peer[g];
-          if (vec_ok && gcol + 32 <= p.n && (gcol * kOB) % 16 == 0 && (reinterpret_cast<uintptr_t>(cdst) % 16) == 0) {
+        for (int g = -1; g < o.n_peer; ++g) {  // g == -1: the local C; others: peer GPUs' copies
+          void* cdst = g < 0 ? o.c : p.c_peer[g];
+          if (vec_ok && gcol + 32 <= o.n && (gcol * kOB) % 16 == 0 && (reinterpret_cast<uintptr_t>(cdst) % 16) == 0) {
             uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(cdst) + base * kOB);
 #pragma unroll
             for (int pk = 0; pk < kPacketsPerLd; ++pk) dst[pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
           } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              if (gcol + i < p.n) store_scalar<kOut>(cdst, base + i, v[i]);
+              if (gcol + i < o.n) store_scalar<kOut>(cdst, base + i, v[i]);
           }
         }
       }
@@ -394,7 +413,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
 
   const int tiles_n_c = (p.tiles_n + kMc - 1) / kMc;  // column tiles per cluster step (kMc neighbours at a time)
   const int tiles_mn = p.tiles_m * tiles_n_c;
-  const int num_tiles = tiles_mn * p.split_k;  // work items: (K slice, tile)
+  const bool tail_mode = p.tail_tiles > 0;
+  const int num_tiles = tail_mode ? p.tail_begin + p.tail_tiles * p.tail_split : tiles_mn * p.split_k;  // work items
   const int cluster_id = blockIdx.x / kCluster;
   const int num_clusters = gridDim.x / kCluster;
   const int nkb = p.num_k_blocks;
@@ -402,7 +422,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // Work item -> (row tile, column tile); for a grouped GEMM also the group, the first row of the tile
   // and the end of the group's rows (the tile's row limit).
   auto tile_coord = [&](int w, int& tm, int& tn, int& grp, int& row_base, int& row_limit) {
-    const int t = w % tiles_mn;
+    const int t = !tail_mode ? w % tiles_mn : (w < p.tail_begin ? w : p.tail_begin + (w - p.tail_begin) % p.tail_tiles);
     const int group = p.raster * tiles_n_c;
     const int g = t / group;
     const int first = g * p.raster;
@@ -424,8 +444,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   };
   // K-block range [kb0, kb1) of work item w
   auto k_range = [&](int w, int& kb0, int& kb1) {
-    kb0 = (w / tiles_mn) * p.kb_per_split;
-    kb1 = min(nkb, kb0 + p.kb_per_split);
+    if (tail_mode) {
+      kb0 = w < p.tail_begin ? 0 : ((w - p.tail_begin) / p.tail_tiles) * p.tail_kb;
+      kb1 = w < p.tail_begin ? nkb : min(nkb, kb0 + p.tail_kb);
+    } else {
+      kb0 = (w / tiles_mn) * p.kb_per_split;
+      kb1 = min(nkb, kb0 + p.kb_per_split);
+    }
   };
 
   if (warp != 1 && warp < kEpiWarp0) {
@@ -601,9 +626,19 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       int tm, tn, grp, row_base, row_limit;
       tile_coord(t, tm, tn, grp, row_base, row_limit);
-      const int row0 = row_base + (int)cta_rank * kBlockM;
-      const int col0 = tn * p.block_n;
-      const int row_off = (t / tiles_mn) * p.split_row_pitch;
+      const bool tail_item = tail_mode && t >= p.tail_begin;
+      const bool rows_in_range = row_base + (int)cta_rank * kBlockM < row_limit;
+      // a tail slice writes tile (t - tail_begin) of the workspace matrix, whole (the reduction clips to M x N)
+      const int row0 = (tail_item ? (t - p.tail_begin) * kCta * kBlockM : row_base) + (int)cta_rank * kBlockM;
+      const int col0 = tail_item ? 0 : tn * p.block_n;
+      const int row_off = (tail_mode ? 0 : t / tiles_mn) * p.split_row_pitch;
+      if (tail_item) row_limit = 0x7fffffff;
+      // partial sums of a tail slice go to the workspace raw; everything else is the final C
+      const EpiOut o{tail_item ? &p.tm_ws : &p.tm_c, tail_item ? p.ws : p.c, tail_item ? (long long)p.block_n : p.ldc,
+                     tail_item ? p.block_n : p.n, tail_item ? 1.0f : p.alpha, tail_item ? 0 : p.relu,
+                     tail_item ? 0 : p.accumulate, tail_item ? 1 : p.epi_tma, tail_item ? 0 : p.n_peer,
+                     (!tail_item && p.l2_policy != 1) ? 1 : 0};
+      const int out_kind = tail_item ? static_cast<int>(kOutF32) : p.out_kind;
 #pragma unroll
       for (int h = 0; h < kNSub; ++h) {
         const int bi = (kNSub == 2) ? h : as;  // barrier / accumulator slot
@@ -611,14 +646,14 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         tc_fence_after();
         const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
         const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
-        if (row0 < row_limit) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
-          switch (p.out_kind) {
-            case kOutBF16: epilogue_tile<kOutBF16>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF16: epilogue_tile<kOutF16>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF32: epilogue_tile<kOutF32>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutE4M3: epilogue_tile<kOutE4M3>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutI32: epilogue_tile<kOutI32>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            default: epilogue_tile<kOutE5M2>(p, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+        if (rows_in_range) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
+          switch (out_kind) {
+            case kOutBF16: epilogue_tile<kOutBF16>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF16: epilogue_tile<kOutF16>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutF32: epilogue_tile<kOutF32>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutE4M3: epilogue_tile<kOutE4M3>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            case kOutI32: epilogue_tile<kOutI32>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+            default: epilogue_tile<kOutE5M2>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
           }
         }
         // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.

@@ -144,6 +144,10 @@ struct Resolved {
   // workspace with a 128-byte-multiple pitch (the reference falls back to SIMT copies: src/op/copy.cc:823-855)
   bool copy_a, copy_b, tr_a, tr_b;
   long long lda_c, ldb_c, a_copy_bytes, b_copy_bytes, split_bytes;
+  // tail split (optional: used only when the caller's workspace also holds tail_bytes beyond ws_bytes): the
+  // tiles of the last, partial wave are cut into K slices; see GemmKernelParams::tail_*
+  int tail_begin, tail_tiles, tail_split, tail_kb;
+  long long tail_bytes;
 };
 
 // Resident 4-CTA clusters (one CTA per SM) on a GPU with `sms` SMs: measured by tlb200_init with
@@ -155,7 +159,7 @@ constexpr bool kAutoMc = true;  // multicast plans are chosen automatically
 int mc_clusters_of(int sms) { return (g_mc_clusters > 0 && sms == g_mc_clusters_sms) ? g_mc_clusters : sms * 33 / 148; }
 
 int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false,
-            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = true) {
+            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = true, bool allow_tail = true) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -206,7 +210,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   memset(&p, 0, sizeof(p));
   if (d->cfg_cta_group < 0 || d->cfg_cta_group == 3 || d->cfg_cta_group > 4)
     return fail("tlb200: cfg_cta_group must be 0, 1, 2 or 4 (got %d)", d->cfg_cta_group);
-  if (d->reserved[1] < 0 || d->reserved[1] > 64) return fail("tlb200: cfg_split_k must be in [0,64] (got %d)", d->reserved[1]);
+  if (d->reserved[1] < -1 || d->reserved[1] > 64)
+    return fail("tlb200: cfg_split_k must be in [0,64], or -1 to force the tail split (got %d)", d->reserved[1]);
   if (d->reserved[1] > 1 && d->ab_dtype == TLB200_INT8) return fail("tlb200: split-K is not offered for int8 (partial sums are kept in fp32)");
   // A tile is n_sub accumulators of umma_n (<= 256) columns each.  The epilogue drains TMEM 32
   // columns at a time, so umma_n is a whole multiple of 32; an N-major B is staged in whole 128 B
@@ -257,6 +262,19 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
         const double kb = static_cast<double>((nkb + split - 1) / split);
         double tile = kb * 2.0 * c.bn / c.eff + (c.bn > 256 ? 8000.0 : 0.0);
         double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? 3000.0 : 0.0);  // pairs start ~1.5 us later
+        if (split == 1 && allow_split && allow_tail && d->reserved[1] != 1 && c.mc == 1 && c.bn <= 256 && d->ab_dtype != TLB200_INT8 &&
+            items > clusters && items % clusters != 0) {
+          // the tail split (decided below) shortens the last, partial wave to 1/S of a wave plus a small reduction
+          const long long rem = items % clusters;
+          long long s_tail = clusters / rem;
+          if (s_tail > 8) s_tail = 8;
+          if (s_tail > nkb / 8) s_tail = nkb / 8;
+          if (s_tail >= 2) {
+            const double cost = 9000.0 + static_cast<double>(rem) * kBlockM * c.cg * c.bn * (s_tail * 4.0 + 4.0) / 2500.0;
+            const double with_tail = total - tile * (1.0 - 1.0 / static_cast<double>(s_tail)) + cost;
+            if (with_tail < total) total = with_tail;
+          }
+        }
         if (split > 1) total += 3000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
         if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; best_mc = c.mc; }
       }
@@ -308,7 +326,10 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   // Split-K (examples/gemm_splitk in the reference): when the output has too few tiles to occupy the
   // machine and K is deep, K is cut into slices computed by different clusters into an fp32
   // workspace and summed by a second kernel in slice order (deterministic).
-  int split = d->reserved[1];  // cfg_split_k: 0 auto, 1 off, n = n slices (fewer if K is short)
+  int split = d->reserved[1];  // cfg_split_k: 0 auto, 1 off, n = n slices (fewer if K is short), -1 = tail split only
+  const bool force_tail = split == -1;
+  if (force_tail) split = 1;
+  const bool tail_off = d->reserved[1] == 1;
   if (split == 0) {
     split = auto_split;
     if (split == 1 && allow_split && d->ab_dtype != TLB200_INT8 && (d->cfg_cta_group != 0 && d->cfg_block_n != 0) && tiles * 2 <= clusters && r->num_k_blocks >= 16) {
@@ -328,8 +349,31 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   r->split_bytes = r->split_k > 1 ? static_cast<long long>(r->split_k) * r->m_pad * r->ws_ld * 4 : 0;
   r->ws_bytes = r->a_copy_bytes + r->b_copy_bytes + r->split_bytes;
   p.split_k = r->split_k;
-  p.workspace_bytes = r->ws_bytes;
-  const long long work_items = tiles * r->split_k;
+  // Tail split: with more than one wave of whole tiles, the last wave may hold only a few tiles.  Cutting just those
+  // along K over all clusters shortens it from one wave to 1/S of one, at the price of a small reduction kernel.
+  r->tail_begin = r->tail_tiles = r->tail_split = r->tail_kb = 0;
+  r->tail_bytes = 0;
+  if (allow_split && allow_tail && !tail_off && r->split_k == 1 && r->n_sub == 1 && mc == 1 && d->ab_dtype != TLB200_INT8 &&
+      tiles > clusters && tiles % clusters != 0 && d->k > 0) {
+    const long long rem = tiles % clusters;
+    long long s_tail = clusters / rem;
+    if (s_tail > 8) s_tail = 8;
+    if (s_tail > r->num_k_blocks / 8) s_tail = r->num_k_blocks / 8;
+    if (s_tail >= 2) {
+      const double wave = static_cast<double>(r->num_k_blocks) * 2.0 * bn;           // tensor cycles of one wave
+      const double saved = wave * (1.0 - 1.0 / static_cast<double>(s_tail));
+      const double cost = 9000.0 + static_cast<double>(rem) * p.block_m * bn * (s_tail * 4.0 + 2.0 + r->ob) / 2500.0;
+      if (force_tail || saved > 1.25 * cost) {
+        r->tail_kb = static_cast<int>((r->num_k_blocks + s_tail - 1) / s_tail);
+        r->tail_split = (r->num_k_blocks + r->tail_kb - 1) / r->tail_kb;
+        r->tail_tiles = static_cast<int>(rem);
+        r->tail_begin = static_cast<int>(tiles - rem);
+        r->tail_bytes = (static_cast<long long>(r->tail_split) * rem * p.block_m * bn * 4 + 255) / 256 * 256;
+      }
+    }
+  }
+  p.workspace_bytes = r->ws_bytes + r->tail_bytes;
+  const long long work_items = r->tail_tiles ? r->tail_begin + static_cast<long long>(r->tail_tiles) * r->tail_split : tiles * r->split_k;
   if (clusters > work_items) clusters = work_items;
   if (clusters < 1) clusters = 1;
   p.grid = static_cast<int>(clusters) * cg * mc;
@@ -449,6 +493,68 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+// Tail split second pass: tile j of the tail (work item order of the GEMM kernel) is the sum over its K slices s of
+// workspace tiles (s * tail_tiles + j), each [block_m x block_n] fp32, summed in slice order (deterministic).
+template <int kOut>
+__global__ void tail_reduce_kernel(const float* __restrict__ ws, int tail_begin, int tail_tiles, int tail_split, int block_m,
+                                   int block_n, int tiles_m, int tiles_n, int raster, void* c, long long ldc, int m, int n,
+                                   float alpha, int relu, int accumulate) {
+  const int n4 = block_n / 4;
+  const long long per_tile = static_cast<long long>(block_m) * n4;
+  const long long total = per_tile * tail_tiles;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int j = static_cast<int>(i / per_tile);
+    const int rem = static_cast<int>(i - j * per_tile);
+    const int r = rem / n4, c4 = (rem - r * n4) * 4;
+    // tile index -> (row tile, column tile): the kernel's grouped raster (gemm_sm100.cuh, tile_coord)
+    const int t = tail_begin + j;
+    const int group = raster * tiles_n;
+    const int g = t / group;
+    const int first = g * raster;
+    const int rows = min(raster, tiles_m - first);
+    const int within = t - g * group;
+    const int tm = first + within % rows, tn = within / rows;
+    const long long row = static_cast<long long>(tm) * block_m + r;
+    const int col = tn * block_n + c4;
+    if (row >= m || col >= n) continue;
+    float4 acc = *reinterpret_cast<const float4*>(ws + (static_cast<long long>(j) * block_m + r) * block_n + c4);
+    for (int sl = 1; sl < tail_split; ++sl) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + ((static_cast<long long>(sl) * tail_tiles + j) * block_m + r) * block_n + c4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    float o[4] = {acc.x * alpha, acc.y * alpha, acc.z * alpha, acc.w * alpha};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (relu) o[q] = fmaxf(o[q], 0.f);
+      if (col + q < n) {
+        if (accumulate) o[q] += load_out<kOut>(c, row * ldc + col + q);
+        store_scalar<kOut>(c, row * ldc + col + q, o[q]);
+      }
+    }
+  }
+}
+
+int launch_tail_reduce(const float* ws, const Resolved& r, const tlb200_gemm_plan& pl, void* c, long long ldc, int m, int n,
+                       float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream) {
+  const long long total = static_cast<long long>(r.tail_tiles) * pl.block_m * (pl.block_n / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  const int g = static_cast<int>(blocks < 1 ? 1 : blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
+#define TLB_TAIL(K) tail_reduce_kernel<K><<<g, 256, 0, stream>>>(ws, r.tail_begin, r.tail_tiles, r.tail_split, pl.block_m, pl.block_n, \
+                                                                 pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac)
+  switch (out_kind) {
+    case kOutF16: TLB_TAIL(kOutF16); break;
+    case kOutBF16: TLB_TAIL(kOutBF16); break;
+    case kOutF32: TLB_TAIL(kOutF32); break;
+    case kOutE4M3: TLB_TAIL(kOutE4M3); break;
+    default: TLB_TAIL(kOutE5M2); break;
+  }
+#undef TLB_TAIL
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail("tlb200: tail-split reduce launch: %s", cudaGetErrorString(e));
   return 0;
 }
 
@@ -763,6 +869,10 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
                   r.ws_bytes, r.a_copy_bytes + r.b_copy_bytes, r.split_bytes, r.split_k, (long long)ws_bytes);
   }
   const bool split = r.split_k > 1;
+  // The tail split is optional: it is used when the workspace also holds its partial tiles (256-aligned), and never
+  // for grouped contractions or multiple destinations.
+  const bool tail = r.tail_tiles > 0 && ws && n_groups == 0 && n_peer == 0 && reinterpret_cast<uintptr_t>(ws) % 256 == 0 &&
+                    ws_bytes >= r.ws_bytes + r.tail_bytes;
   if (d->m == 0 || d->n == 0) return 0;
   if (!c || (d->k > 0 && (!a || !b))) return fail("tlb200_gemm: null tensor pointer (a=%p b=%p c=%p)", a, b, c);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
@@ -830,6 +940,13 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     if (int rc = encode_2d(&kp.tm_c, d->c_dtype, c, d->m, d->n, d->ldc, 128 / r.ob, 32, "C[M,N]")) return rc;
     for (int g = 0; g < n_peer; ++g)
       if (int rc = encode_2d(&kp.tm_c_peer[g], d->c_dtype, peers[g], d->m, d->n, d->ldc, 128 / r.ob, 32, "peer C[M,N]")) return rc;
+  }
+  if (tail) {  // region after the re-pitched operands (there is no uniform split-K region in this mode)
+    float* tws = reinterpret_cast<float*>(static_cast<char*>(ws) + r.split_bytes);
+    if (int rc = encode_2d(&kp.tm_ws, TLB200_FLOAT32, tws, static_cast<long long>(r.tail_split) * r.tail_tiles * pl.block_m, pl.block_n,
+                           pl.block_n, 32, 32, "tail workspace")) return rc;
+    kp.ws = tws;
+    kp.tail_begin = r.tail_begin; kp.tail_tiles = r.tail_tiles; kp.tail_split = r.tail_split; kp.tail_kb = r.tail_kb;
   }
   kp.n_peer = n_peer;
   for (int g = 0; g < n_peer; ++g) kp.c_peer[g] = peers[g];
@@ -915,6 +1032,12 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     return fail("tlb200_gemm: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), pl.grid,
                 pl.cta_group, pl.smem_bytes);
   g_launches++;
+  if (tail) {
+    if (int rc = launch_tail_reduce(static_cast<const float*>(kp.ws), r, pl, c, d->ldc, d->m, d->n, d->alpha,
+                                    (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream))
+      return rc;
+    g_launches++;
+  }
   if (split) {
     if (int rc = launch_splitk_reduce(static_cast<const float*>(ws), r.ws_ld, r.m_pad, r.split_k, c, d->ldc, d->m, d->n, d->alpha,
                                       (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream))
@@ -1121,7 +1244,7 @@ int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* d) {
   const int sms = (dev >= 0 && dev < kMaxDevices && g_sm_count[dev] > 0) ? g_sm_count[dev] : 148;
   Resolved r;
   if (resolve(d, sms, nullptr, &r, true)) return -1;
-  return r.ws_bytes;
+  return r.ws_bytes + r.tail_bytes;  // the tail part is optional: a smaller workspace simply runs without the tail split
 }
 
 static long long extent_bytes(long long rows, long long cols, long long ld, int eb) {
