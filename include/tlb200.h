@@ -240,6 +240,8 @@ int tlb200_gemm_static_scratch(const tlb200_gemm_desc* desc, const void* a, cons
  * then A in row panels, to the device; runs tlb200_gemm per panel on `stream`
  * while the next panel is copied in and the previous panel's C is copied out
  * (two internal copy streams created by tlb200_init), then synchronises.
+ * Operands whose host row pitch TMA cannot address (not a multiple of 16
+ * bytes) are re-pitched by the copy itself.
  * `workspace` is a caller-owned device buffer of at least
  * tlb200_gemm_host_workspace_bytes(desc) bytes (the library never allocates).
  * This is the host-buffer form of the reference's adapter call path

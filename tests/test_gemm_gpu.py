@@ -523,3 +523,21 @@ def test_tail_split_epilogues_and_small_workspace():
     _abi.check(lib.tlb200_gemm_ex(ctypes.byref(d), a.data_ptr(), b.data_ptr(), out.data_ptr(), ws.data_ptr(), need,
                                   torch.cuda.current_stream().cuda_stream), "tlb200_gemm_ex")
     assert lib.tlb200_launch_count() - n0 == 2 and torch.equal(out, ref)  # GEMM + tail reduction
+
+
+def test_host_buffer_entry_point_repitches_unaligned_operands():
+    # K = 763 fp16: a host pitch of 1526 bytes is not TMA-addressable; the copy to the device re-pitches the rows
+    # (the reference's test_pad_* shapes, through the host-buffer form of the call)
+    m, n, k = 1100, 520, 763
+    a = torch.randint(-3, 4, (m, k)).half().pin_memory()
+    b = torch.randint(-3, 4, (k, n + 3)).half().pin_memory()[:, :n]  # B given as [K, N] with an odd pitch too
+    c = torch.empty(m, n, dtype=torch.float32).pin_memory()
+    lib = _abi.load()
+    G._ensure_init(0)
+    d = G.make_desc(m, n, k, _abi.FLOAT16, _abi.FLOAT32, 0, 0, k, n + 3, n)
+    need = lib.tlb200_gemm_host_workspace_bytes(ctypes.byref(d))
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    rc = lib.tlb200_gemm_host(ctypes.byref(d), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), need,
+                              torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, _abi.last_error()
+    assert torch.equal(c, a.float() @ b.float())

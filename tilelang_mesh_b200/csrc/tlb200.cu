@@ -1252,13 +1252,20 @@ static long long extent_bytes(long long rows, long long cols, long long ld, int 
   return ((rows - 1) * ld + cols) * eb;
 }
 static long long round256(long long x) { return (x + 255) & ~255ll; }
+// Row pitch (elements) of an operand's device copy in the host-buffer path: the host pitch when TMA can address it,
+// else the row length rounded up to 128 bytes (the copy to the device is then a pitched 2-D copy).
+static long long host_path_pitch(long long ld, long long cols, int es) {
+  return (ld * es) % 16 == 0 ? ld : (cols * es + 127) / 128 * 128 / es;
+}
 
 int64_t tlb200_gemm_host_workspace_bytes(const tlb200_gemm_desc* d) {
   if (!d) return -1;
   const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
   if (!es || !ob) return -1;
-  const long long a = extent_bytes(d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, d->lda, es);
-  const long long b = extent_bytes(d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, d->ldb, es);
+  const long long a_rows = d->trans_a ? d->k : d->m, a_cols = d->trans_a ? d->m : d->k;
+  const long long b_rows = d->trans_b ? d->n : d->k, b_cols = d->trans_b ? d->k : d->n;
+  const long long a = extent_bytes(a_rows, a_cols, host_path_pitch(d->lda, a_cols, es), es);
+  const long long b = extent_bytes(b_rows, b_cols, host_path_pitch(d->ldb, b_cols, es), es);
   const long long c = extent_bytes(d->m, d->n, d->ldc, ob);
   return round256(a) + round256(b) + round256(c);
 }
@@ -1275,20 +1282,30 @@ int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, 
   if (d->m == 0 || d->n == 0) return 0;
   if (!hc || (d->k > 0 && (!ha || !hb))) return fail("tlb200_gemm_host: null host pointer");
   const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
-  const long long ab = extent_bytes(d->trans_a ? d->k : d->m, d->trans_a ? d->m : d->k, d->lda, es);
-  const long long bb = extent_bytes(d->trans_b ? d->n : d->k, d->trans_b ? d->k : d->n, d->ldb, es);
+  const long long a_rows = d->trans_a ? d->k : d->m, a_cols = d->trans_a ? d->m : d->k;
+  const long long b_rows = d->trans_b ? d->n : d->k, b_cols = d->trans_b ? d->k : d->n;
+  const long long lda_d = host_path_pitch(d->lda, a_cols, es), ldb_d = host_path_pitch(d->ldb, b_cols, es);
+  const long long ab = extent_bytes(a_rows, a_cols, lda_d, es);
+  const long long bb = extent_bytes(b_rows, b_cols, ldb_d, es);
   char* da = static_cast<char*>(ws);
   char* db = da + round256(ab);
   char* dc = db + round256(bb);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   HostPipe& hp = g_pipe[dev];
   cudaError_t e;
-#define TLB_CK(call, what) if ((e = (call)) != cudaSuccess) return fail("tlb200_gemm_host: %s: %s", what, cudaGetErrorString(e))
+#define TLB_CK(call, what) do { if ((e = (call)) != cudaSuccess) return fail("tlb200_gemm_host: %s: %s", what, cudaGetErrorString(e)); } while (0)
   // Everything is ordered after the caller's stream; B (needed by every panel) goes first.
   TLB_CK(cudaEventRecord(hp.fork, stream), "fork");
   TLB_CK(cudaStreamWaitEvent(hp.in, hp.fork, 0), "fork");
   TLB_CK(cudaStreamWaitEvent(hp.out, hp.fork, 0), "fork");
-  if (bb) TLB_CK(cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, hp.in), "H2D B");
+  // an operand whose host pitch TMA cannot address is re-pitched by the copy itself
+  if (bb) {
+    if (ldb_d == d->ldb) {
+      TLB_CK(cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, hp.in), "H2D B");
+    } else {
+      TLB_CK(cudaMemcpy2DAsync(db, ldb_d * es, hb, d->ldb * es, b_cols * es, b_rows, cudaMemcpyHostToDevice, hp.in), "H2D B");
+    }
+  }
   // Row panels of A / C (contiguous when A is [M,K]): panel p+1 is copied in while panel p is
   // multiplied and panel p-1 is copied out, so PCIe runs in both directions under the GEMM.
   int panels = 1;
@@ -1302,16 +1319,26 @@ int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, 
   for (int r0 = 0; r0 < d->m; r0 += rows_per, ++p) {
     const int rows = (d->m - r0 < rows_per) ? d->m - r0 : rows_per;
     tlb200_gemm_desc pd = *d;
-    long long a_off = 0, a_bytes = ab;
+    pd.lda = lda_d;
+    pd.ldb = ldb_d;
+    long long a_off = 0, a_off_h = 0, a_bytes = ab, a_rows_p = a_rows;
     if (panels > 1) {
       pd.m = rows;
-      a_off = static_cast<long long>(r0) * d->lda * es;
-      a_bytes = extent_bytes(rows, d->k, d->lda, es);
+      a_off = static_cast<long long>(r0) * lda_d * es;
+      a_off_h = static_cast<long long>(r0) * d->lda * es;
+      a_bytes = extent_bytes(rows, d->k, lda_d, es);
+      a_rows_p = rows;
     }
     const long long c_off = static_cast<long long>(r0) * d->ldc * ob;
     const long long c_bytes = extent_bytes(rows, d->n, d->ldc, ob);
-    if (d->k > 0 && a_bytes)
-      TLB_CK(cudaMemcpyAsync(da + a_off, static_cast<const char*>(ha) + a_off, a_bytes, cudaMemcpyHostToDevice, hp.in), "H2D A");
+    if (d->k > 0 && a_bytes) {
+      if (lda_d == d->lda) {
+        TLB_CK(cudaMemcpyAsync(da + a_off, static_cast<const char*>(ha) + a_off_h, a_bytes, cudaMemcpyHostToDevice, hp.in), "H2D A");
+      } else {
+        TLB_CK(cudaMemcpy2DAsync(da + a_off, lda_d * es, static_cast<const char*>(ha) + a_off_h, d->lda * es, a_cols * es, a_rows_p,
+                                 cudaMemcpyHostToDevice, hp.in), "H2D A");
+      }
+    }
     TLB_CK(cudaEventRecord(hp.loaded[p], hp.in), "record");
     TLB_CK(cudaStreamWaitEvent(stream, hp.loaded[p], 0), "wait");
     if (int rc = tlb200_gemm(&pd, da + a_off, db, dc + c_off, stream_v)) return rc;
