@@ -451,10 +451,29 @@ __global__ void fill_zero_kernel(void* c, long long ldc, int m, int n) {
   }
 }
 
+// Launch a plain kernel as a programmatic dependent of the previous launch in `stream`: its blocks may become
+// resident while that kernel still runs and proceed at their griddepcontrol.wait the moment it completes, which
+// takes the launch latency of the reduction kernels off the critical path.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_dependent(void (*kernel)(KArgs...), int grid, int block, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(block, 1, 1);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // Split-K second pass: C[m,n] = cast(relu?(alpha * sum_s ws[s*m_pad + m, n])), slices summed in order.
 template <int kOut>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_ld, int m_pad, int split_k, void* c,
                                      long long ldc, int m, int n, float alpha, int relu, int accumulate) {
+  griddep_wait();  // the partial sums come from the previous kernel
   const int n4 = (n + 3) / 4;
   const long long total = static_cast<long long>(m) * n4;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -485,11 +504,11 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
   if (blocks < 1) blocks = 1;
   const int g = static_cast<int>(blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
   switch (out_kind) {
-    case kOutF16: splitk_reduce_kernel<kOutF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutBF16: splitk_reduce_kernel<kOutBF16><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutF32: splitk_reduce_kernel<kOutF32><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutE4M3: splitk_reduce_kernel<kOutE4M3><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    default: splitk_reduce_kernel<kOutE5M2><<<g, 256, 0, stream>>>(ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF16: launch_dependent(splitk_reduce_kernel<kOutF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutBF16: launch_dependent(splitk_reduce_kernel<kOutBF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF32: launch_dependent(splitk_reduce_kernel<kOutF32>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutE4M3: launch_dependent(splitk_reduce_kernel<kOutE4M3>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    default: launch_dependent(splitk_reduce_kernel<kOutE5M2>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
@@ -502,6 +521,7 @@ template <int kOut>
 __global__ void tail_reduce_kernel(const float* __restrict__ ws, int tail_begin, int tail_tiles, int tail_split, int block_m,
                                    int block_n, int tiles_m, int tiles_n, int raster, void* c, long long ldc, int m, int n,
                                    float alpha, int relu, int accumulate) {
+  griddep_wait();  // the partial tiles come from the previous kernel
   const int n4 = block_n / 4;
   const long long per_tile = static_cast<long long>(block_m) * n4;
   const long long total = per_tile * tail_tiles;
@@ -543,8 +563,8 @@ int launch_tail_reduce(const float* ws, const Resolved& r, const tlb200_gemm_pla
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const int g = static_cast<int>(blocks < 1 ? 1 : blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
-#define TLB_TAIL(K) tail_reduce_kernel<K><<<g, 256, 0, stream>>>(ws, r.tail_begin, r.tail_tiles, r.tail_split, pl.block_m, pl.block_n, \
-                                                                 pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac)
+#define TLB_TAIL(K) launch_dependent(tail_reduce_kernel<K>, g, 256, stream, ws, r.tail_begin, r.tail_tiles, r.tail_split, pl.block_m, \
+                                    pl.block_n, pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac)
   switch (out_kind) {
     case kOutF16: TLB_TAIL(kOutF16); break;
     case kOutBF16: TLB_TAIL(kOutBF16); break;
