@@ -89,7 +89,8 @@ typedef struct tlb200_gemm_desc {
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
   int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */
   int32_t reserved[3];   /* [0] = cfg_epi_warps: 0 auto, 4 or 8 epilogue warps;
-                          * [1] = cfg_split_k: 0 auto, 1 off, n = at most n K slices (needs a workspace);
+                          * [1] = cfg_split_k: 0 auto, 1 off (no split-K, no tail split), n = at most n K slices,
+                          *       -1 = no split-K but force the tail split (both need a workspace);
                           * [2] = cfg_l2_policy: 0 default (operands evict_last, C evict_first), 1 = no hints */
 } tlb200_gemm_desc;
 
