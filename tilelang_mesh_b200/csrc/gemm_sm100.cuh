@@ -370,7 +370,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t bar_tfull = bar_empty + 8 * stages;     // [2]
   const uint32_t bar_tempty = bar_tfull + 16;            // [2]
   const uint32_t smem_tptr = bar_tempty + 16;            // u32 TMEM base address
-  const uint32_t stage_tx_bytes = (kABytesPerStage + b_stage_bytes) * kCta;
+  // bytes that land in one stage: the A boxes actually issued (a short problem, M < 128, fetches only its own rows;
+  // with A multicast each CTA issues half a box and receives the other half) plus the B rows, per CTA of the pair
+  const uint32_t stage_tx_bytes = (static_cast<uint32_t>(p.a_boxes * p.a_box_bytes) * kMc + b_stage_bytes) * kCta;
   const uint32_t acc_cols = static_cast<uint32_t>(p.block_n) * acc_stages;
   const uint32_t tmem_cols = acc_cols <= 32u ? 32u : acc_cols <= 64u ? 64u : acc_cols <= 128u ? 128u
                              : acc_cols <= 256u ? 256u : 512u;

@@ -935,8 +935,13 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   // A
   if (!r.a_mn) {
     // with A multicast every CTA fetches half of its 128-row box (the other half arrives from the other pair)
-    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, kBlockM / r.mc, "A[M,K]")) return rc;
-    kp.a_boxes = 1; kp.a_box_bytes = kABytesPerStage / r.mc;
+    // A problem shorter than one tile (decode-time shapes) fetches only the rows it has, rounded up to the 8-row
+    // swizzle atom: the other rows of the stage feed accumulator rows that are never stored, and filling them
+    // with zeros would still cost the SM's TMA write bandwidth (the bound for such shapes).
+    int a_box_rows = kBlockM / r.mc;
+    if (pl.cta_group == 1 && n_groups == 0 && d->m < kBlockM) a_box_rows = (d->m + 7) / 8 * 8;
+    if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, a_box_rows, "A[M,K]")) return rc;
+    kp.a_boxes = 1; kp.a_box_bytes = a_box_rows * kStageRowBytes;
   } else {
     if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->k, d->m, lda, r.span, bk, "A[K,M]")) return rc;
     kp.a_boxes = kBlockM / r.span; kp.a_box_bytes = bk * kStageRowBytes;
