@@ -51,7 +51,7 @@ variants = [("auto", {}), ("pair256", dict(cta_group=2, block_n=256)), ("pair512
 if len(sys.argv) > 3 and sys.argv[3] == "knobs":
     base = dict(cta_group=2, block_n=256) if dt == "fp8" else dict(cta_group=2, block_n=512)
     variants = [("auto", {})] + [(f"raster{r}", dict(base, raster=r)) for r in (4, 8, 32)] + \
-               [(f"stages{st}", dict(base, stages=st)) for st in ((4, 5) if dt == "fp8" else (3,))] + [("auto_again", {})]
+               [(f"stages{st}", dict(base, stages=st)) for st in ((4, 5) if dt == "fp8" else (2, 3, 3))] + [("auto_again", {})]
 extra = [v for v in sys.argv[3:]]
 if dt == "bf16":
     run("cublas", lambda: torch.matmul(a, b.t(), out=c))
