@@ -82,8 +82,10 @@ typedef struct tlb200_gemm_desc {
   uint32_t epilogue;  /* TLB200_EPI_* */
   int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles, 4 = two such pairs per cluster
                             on neighbouring column tiles, every A box fetched once and TMA-multicast to both
-                            (only when A lies in the current device's own memory; chosen automatically under
-                            the same condition) */
+                            (only when all of A is proven to lie in the current device's own memory, see
+                            tlb200_is_own_device_memory - an error otherwise; chosen automatically under the
+                            same condition; never by tlb200_gemm_bcast / _grouped; TLB200_NO_MULTICAST=1 in the
+                            environment at tlb200_init switches the plan off altogether) */
   int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] or of 64 in (256,512] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
@@ -252,8 +254,25 @@ int64_t tlb200_gemm_host_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_host(const tlb200_gemm_desc* desc, const void* host_a, const void* host_b,
                      void* host_c, void* workspace, int64_t workspace_bytes, void* stream);
 
-/* Resolve the plan without launching (pure host arithmetic; no GPU needed). */
+/* Resolve the plan without launching (pure host arithmetic; no GPU needed): what the reference reports through
+ * its tile-program constants and `JITKernel.get_kernel_source()` (tilelang/jit/kernel.py:420-440).  Nothing is
+ * known here about where A lives, so `multicast` is 2 only when the descriptor asks for it (cfg_cta_group = 4). */
 int tlb200_gemm_plan_query(const tlb200_gemm_desc* desc, int sm_count, tlb200_gemm_plan* out);
+
+/* The plan a tlb200_gemm / tlb200_gemm_ex call with exactly these pointers would run on the current device (no
+ * launch).  Same role as above; it exists because the A-multicast plan (`multicast` = 2) depends on the pointer:
+ * TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+ * memory hung the GPU, so that plan is taken only when the whole extent of A (or of its re-pitched copy in the
+ * workspace) is proven to be one cudaMalloc allocation of the current device - see tlb200_is_own_device_memory. */
+int tlb200_gemm_plan_query_call(const tlb200_gemm_desc* desc, const void* a, const void* b, const void* c,
+                                const void* workspace, int64_t workspace_bytes, tlb200_gemm_plan* out);
+
+/* No counterpart in the reference (it has no multi-GPU path).  1 when [ptr, ptr + bytes) is proven to be ordinary
+ * memory of the CURRENT device allocated by this process with cudaMalloc / cuMemAlloc and lying inside one
+ * allocation; 0 for everything else - host, managed, stream-ordered-pool, virtual-memory-mapped (cuMemMap:
+ * symmetric memory, expandable segments), imported (IPC) and peer memory, ranges that cross an allocation
+ * boundary, and any query error.  This is the condition under which the library uses TMA multicast loads. */
+int tlb200_is_own_device_memory(const void* ptr, int64_t bytes);
 
 /* Replaces `const char* get_last_error()` (wrapper.py:36-38). Thread-local. */
 const char* tlb200_last_error(void);

@@ -419,3 +419,79 @@ def test_fragment_operand_must_be_a_plain_copy_of_a_shared_tile():
 
     with pytest.raises(NotAGemmProgram, match="not a plain copy of a shared tile"):
         tilelang.compile(stale)
+
+
+def test_writes_that_change_the_meaning_are_rejected():
+    """Programs that look like the family but compute something else must not be folded into a plain GEMM."""
+    M = N = K = 256
+
+    @T.prim_func
+    def scale_inside_k_loop(A: T.Tensor((M, K), "float16"), B: T.Tensor((N, K), "float16"), C: T.Tensor((M, N), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((128, 32), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                T.copy(B[bx * 128, k * 32], b_s)
+                T.gemm(a_s, b_s, acc, transpose_B=True)
+                for i, j in T.Parallel(128, 128):  # once per K block: a geometric rescaling, not alpha = 0.5
+                    acc[i, j] = acc[i, j] * 0.5
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="inside the K loop"):
+        tilelang.compile(scale_inside_k_loop)
+
+    @T.prim_func
+    def operand_tile_scaled_in_place(A: T.Tensor((M, K), "float16"), B: T.Tensor((N, K), "float16"), C: T.Tensor((M, N), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((128, 32), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                T.copy(B[bx * 128, k * 32], b_s)
+                for i, j in T.Parallel(128, 32):  # result is 2*A@B, not A@B
+                    a_s[i, j] = a_s[i, j] * 2
+                T.gemm(a_s, b_s, acc, transpose_B=True)
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="modified element-wise"):
+        tilelang.compile(operand_tile_scaled_in_place)
+
+    @T.prim_func
+    def work_after_the_store(A: T.Tensor((M, K), "float16"), B: T.Tensor((N, K), "float16"), C: T.Tensor((M, N), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((128, 32), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                T.copy(B[bx * 128, k * 32], b_s)
+                T.gemm(a_s, b_s, acc, transpose_B=True)
+            T.copy(acc, C[by * 128, bx * 128])
+            T.clear(acc)
+            T.copy(acc, C[by * 128, bx * 128])  # overwrites the product with zeros
+
+    with pytest.raises(NotAGemmProgram, match="unexpected"):
+        tilelang.compile(work_after_the_store)
+
+    @T.prim_func
+    def fill_inside_k_loop(A: T.Tensor((M, K), "float16"), B: T.Tensor((N, K), "float16"), C: T.Tensor((M, N), "float16")):
+        with T.Kernel(2, 2, threads=128) as (bx, by):
+            a_s = T.alloc_shared((128, 32), "float16")
+            b_s = T.alloc_shared((128, 32), "float16")
+            acc = T.alloc_fragment((128, 128), "float")
+            T.clear(acc)
+            for k in T.Pipelined(8, num_stages=2):
+                T.copy(A[by * 128, k * 32], a_s)
+                T.copy(B[bx * 128, k * 32], b_s)
+                T.fill(b_s, 1.0)
+                T.gemm(a_s, b_s, acc, transpose_B=True)
+            T.copy(acc, C[by * 128, bx * 128])
+
+    with pytest.raises(NotAGemmProgram, match="unexpected ClearOp inside the K loop"):
+        tilelang.compile(fill_inside_k_loop)

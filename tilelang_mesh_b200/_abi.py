@@ -105,6 +105,9 @@ SYMBOLS = {
                                         ctypes.c_void_p]),
     "tlb200_gemm_plan_query": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_int,
                                               ctypes.POINTER(GemmPlan)]),
+    "tlb200_gemm_plan_query_call": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                   ctypes.c_void_p, ctypes.c_int64, ctypes.POINTER(GemmPlan)]),
+    "tlb200_is_own_device_memory": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "tlb200_last_error": (ctypes.c_char_p, []),
     "tlb200_abi_version": (ctypes.c_int, []),
     "tlb200_launch_count": (ctypes.c_int64, []),

@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -37,10 +38,20 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
+// Pointer queries behind own_device_extent() below (bound at init like the encoder).
+typedef CUresult (*PtrAttrFn)(void*, CUpointer_attribute, CUdeviceptr);
+typedef CUresult (*AddrRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+typedef CUresult (*RetainHandleFn)(CUmemGenericAllocationHandle*, void*);
+typedef CUresult (*ReleaseHandleFn)(CUmemGenericAllocationHandle);
+PtrAttrFn g_ptr_attr = nullptr;
+AddrRangeFn g_addr_range = nullptr;
+RetainHandleFn g_retain_handle = nullptr;
+ReleaseHandleFn g_release_handle = nullptr;
+bool g_no_multicast = false;  // TLB200_NO_MULTICAST=1 in the environment: the A-multicast plan is never used
 std::mutex g_init_mu;
 constexpr int kMaxDevices = 64;
-int g_sm_count[kMaxDevices] = {0};
-bool g_dev_ready[kMaxDevices] = {false};
+std::atomic<int> g_sm_count[kMaxDevices];   // zero-initialised (static storage)
+std::atomic<bool> g_dev_ready[kMaxDevices];
 // Host-buffer path: per device one copy-in and one copy-out stream plus an event ring, created at
 // init (streams/events are driver objects, not device memory; the library still allocates none).
 constexpr int kMaxPanels = 16;
@@ -159,7 +170,7 @@ constexpr bool kAutoMc = true;  // multicast plans are chosen automatically
 int mc_clusters_of(int sms) { return (g_mc_clusters > 0 && sms == g_mc_clusters_sms) ? g_mc_clusters : sms * 33 / 148; }
 
 int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false,
-            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = true, bool allow_tail = true) {
+            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = false, bool allow_tail = true) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -225,7 +236,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   const bool mc_possible = allow_mc && !r->a_mn && d->m > kBlockM && mc_clusters >= 1;
   if (mc == 2 && !mc_possible)
     return fail("tlb200: cfg_cta_group=4 (A multicast across two pairs) needs a K-contiguous A, m > %d and an ordinary "
-                "(not grouped) contraction", kBlockM);
+                "(not grouped, single-destination) contraction%s", kBlockM,
+                g_no_multicast ? "; TLB200_NO_MULTICAST is set" : "");
   if (cg == 0 || bn == 0) {
     // Automatic plan: minimise a small cycle model calibrated on B200 (tools/sweep.py,
     // profiles/r1_notes.md) over {cta_group} x {block_n} x {split_k}.
@@ -503,14 +515,15 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
   const int g = static_cast<int>(blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
+  cudaError_t e = cudaSuccess;
   switch (out_kind) {
-    case kOutF16: launch_dependent(splitk_reduce_kernel<kOutF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutBF16: launch_dependent(splitk_reduce_kernel<kOutBF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutF32: launch_dependent(splitk_reduce_kernel<kOutF32>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutE4M3: launch_dependent(splitk_reduce_kernel<kOutE4M3>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    default: launch_dependent(splitk_reduce_kernel<kOutE5M2>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF16: e = launch_dependent(splitk_reduce_kernel<kOutF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutBF16: e = launch_dependent(splitk_reduce_kernel<kOutBF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF32: e = launch_dependent(splitk_reduce_kernel<kOutF32>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutE4M3: e = launch_dependent(splitk_reduce_kernel<kOutE4M3>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    default: e = launch_dependent(splitk_reduce_kernel<kOutE5M2>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
   }
-  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
   return 0;
 }
@@ -565,15 +578,16 @@ int launch_tail_reduce(const float* ws, const Resolved& r, const tlb200_gemm_pla
   const int g = static_cast<int>(blocks < 1 ? 1 : blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
 #define TLB_TAIL(K) launch_dependent(tail_reduce_kernel<K>, g, 256, stream, ws, r.tail_begin, r.tail_tiles, r.tail_split, pl.block_m, \
                                     pl.block_n, pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac)
+  cudaError_t e = cudaSuccess;
   switch (out_kind) {
-    case kOutF16: TLB_TAIL(kOutF16); break;
-    case kOutBF16: TLB_TAIL(kOutBF16); break;
-    case kOutF32: TLB_TAIL(kOutF32); break;
-    case kOutE4M3: TLB_TAIL(kOutE4M3); break;
-    default: TLB_TAIL(kOutE5M2); break;
+    case kOutF16: e = TLB_TAIL(kOutF16); break;
+    case kOutBF16: e = TLB_TAIL(kOutBF16); break;
+    case kOutF32: e = TLB_TAIL(kOutF32); break;
+    case kOutE4M3: e = TLB_TAIL(kOutE4M3); break;
+    default: e = TLB_TAIL(kOutE5M2); break;
   }
 #undef TLB_TAIL
-  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: tail-split reduce launch: %s", cudaGetErrorString(e));
   return 0;
 }
@@ -681,17 +695,94 @@ int out_kind_of(int dt) {
   }
 }
 
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU.  The A-multicast plan is therefore used only when this predicate PROVES that every byte the
+// tensor map of A can address is ordinary memory of device `dev`, allocated by this process with cudaMalloc /
+// cuMemAlloc: first and last byte are device memory of `dev`, not managed, not from a stream-ordered pool, not a
+// virtual-memory mapping (cuMemMap: symmetric memory, multi-GPU fabrics, expandable segments), exportable by this
+// process (an imported IPC mapping is not), and both lie in ONE allocation that contains the whole extent.
+// Anything it cannot prove, and any query error, answers "no": the ordinary plan runs instead.
+bool own_device_extent(const void* ptr, long long bytes, int dev) {
+  if (!ptr || bytes <= 0 || dev < 0) return false;
+  if (!g_ptr_attr || !g_addr_range || !g_retain_handle || !g_release_handle) return false;
+  const CUdeviceptr lo = reinterpret_cast<CUdeviceptr>(ptr);
+  const CUdeviceptr hi = lo + static_cast<CUdeviceptr>(bytes) - 1;
+  if (hi < lo) return false;
+  unsigned long long id[2] = {0, 0};
+  const CUdeviceptr ends[2] = {lo, hi};
+  for (int i = 0; i < 2; ++i) {
+    unsigned int mtype = 0, managed = 1, ipc_ok = 0;
+    int ordinal = -1;
+    CUmemoryPool pool = nullptr;
+    if (g_ptr_attr(&mtype, CU_POINTER_ATTRIBUTE_MEMORY_TYPE, ends[i]) != CUDA_SUCCESS || mtype != CU_MEMORYTYPE_DEVICE) return false;
+    if (g_ptr_attr(&ordinal, CU_POINTER_ATTRIBUTE_DEVICE_ORDINAL, ends[i]) != CUDA_SUCCESS || ordinal != dev) return false;
+    if (g_ptr_attr(&managed, CU_POINTER_ATTRIBUTE_IS_MANAGED, ends[i]) != CUDA_SUCCESS || managed) return false;
+    if (g_ptr_attr(&pool, CU_POINTER_ATTRIBUTE_MEMPOOL_HANDLE, ends[i]) != CUDA_SUCCESS || pool != nullptr) return false;
+    if (g_ptr_attr(&ipc_ok, CU_POINTER_ATTRIBUTE_IS_LEGACY_CUDA_IPC_CAPABLE, ends[i]) != CUDA_SUCCESS || !ipc_ok) return false;
+    if (g_ptr_attr(&id[i], CU_POINTER_ATTRIBUTE_BUFFER_ID, ends[i]) != CUDA_SUCCESS) return false;
+    CUmemGenericAllocationHandle h = 0;
+    if (g_retain_handle(&h, reinterpret_cast<void*>(ends[i])) == CUDA_SUCCESS) {  // a cuMemMap'd range: never trusted
+      g_release_handle(h);
+      return false;
+    }
+  }
+  if (id[0] != id[1]) return false;
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (g_addr_range(&base, &size, lo) != CUDA_SUCCESS) return false;
+  if (base > lo || static_cast<unsigned long long>(hi - base) >= static_cast<unsigned long long>(size)) return false;
+  return true;
+}
+
 int current_device_ready(int* dev_out) {
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return fail("tlb200: cudaGetDevice: %s", cudaGetErrorString(e));
   if (dev < 0 || dev >= kMaxDevices) return fail("tlb200: device ordinal %d out of range", dev);
-  if (!g_dev_ready[dev]) {
+  if (!g_dev_ready[dev].load()) {
     int rc = tlb200_init(dev);
     if (rc) return rc;
   }
   *dev_out = dev;
   return 0;
+}
+
+// The plan one call will run: resolve(), the fall-back to an unsplit schedule when an automatic split-K does not fit
+// the workspace, and - after the LAST resolve, whatever path led to it - the proof that an A-multicast plan reads
+// this GPU's own memory only (own_device_extent).  Without the proof the ordinary plan is resolved instead; an
+// explicit cfg_cta_group = 4 is an error.  Shared by gemm_impl and tlb200_gemm_plan_query_call.
+int plan_call(const tlb200_gemm_desc* d, int dev, const void* a, const void* b, const void* c, const void* ws,
+              int64_t ws_bytes, int n_peer, int n_groups, Resolved* r) {
+  // never with grouped row tiles (not paired across column tiles) nor on the multi-GPU entry point
+  bool allow_mc = n_groups == 0 && n_peer == 0 && !g_no_multicast;
+  const int sms = g_sm_count[dev].load();
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    if (int rc = resolve(d, sms, c, r, ws != nullptr, a, b, allow_mc)) return rc;
+    if (r->split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
+    if (r->ws_bytes > 0) {
+      if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
+      if (ws_bytes < r->ws_bytes && r->split_k > 1 && d->reserved[1] <= 1) {
+        tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
+        d1.reserved[1] = 1;
+        if (int rc = resolve(&d1, sms, c, r, true, a, b, allow_mc)) return rc;
+      }
+      if (ws_bytes < r->ws_bytes)
+        return fail("tlb200_gemm_ex: this call needs a %lld-byte workspace (%lld for re-pitched operands, %lld for split-K x%d), got %lld",
+                    r->ws_bytes, r->a_copy_bytes + r->b_copy_bytes, r->split_bytes, r->split_k, (long long)ws_bytes);
+    }
+    if (r->mc != 2) return 0;
+    // What the multicast loads would read: the caller's A, or its re-pitched copy at the start of the workspace.
+    // The extent is everything the tensor map [m rows x k columns, pitch lda] can address.
+    const void* a_src = r->copy_a ? ws : a;
+    const long long a_ld = r->copy_a ? r->lda_c : d->lda;
+    const long long a_extent = ((static_cast<long long>(d->m) - 1) * a_ld + d->k) * r->es;
+    if (allow_mc && !r->a_mn && own_device_extent(a_src, a_extent, dev)) return 0;
+    if (d->cfg_cta_group == 4)
+      return fail("tlb200_gemm: cfg_cta_group=4 (A multicast) needs all of A in one cudaMalloc allocation of the current "
+                  "device (not managed, pooled, virtual-memory-mapped, imported or peer memory)");
+    allow_mc = false;  // resolve again: no multicast plan can come out of it
+  }
+  return fail("tlb200_gemm: internal error: plan still multicast after it was ruled out");
 }
 
 }  // namespace
@@ -765,11 +856,31 @@ uint64_t tlb200_smem_desc(uint32_t smem_addr, int lbo16, int sbo16, int base_off
 }
 
 int tlb200_gemm_plan_query(const tlb200_gemm_desc* desc, int sm_count, tlb200_gemm_plan* out) {
+  // The plan tlb200_gemm_ex follows when given a workspace.  Without pointers nothing is known about where A lives,
+  // so the A-multicast plan is reported only when the caller asks for it by name (cfg_cta_group = 4).
   Resolved r;
-  int rc = resolve(desc, sm_count, nullptr, &r, true);  // the plan tlb200_gemm_ex follows when given a workspace
+  int rc = resolve(desc, sm_count, nullptr, &r, true, nullptr, nullptr, desc && desc->cfg_cta_group == 4 && !g_no_multicast);
   if (rc) return rc;
   if (out) *out = r.plan;
   return 0;
+}
+
+int tlb200_gemm_plan_query_call(const tlb200_gemm_desc* desc, const void* a, const void* b, const void* c, const void* ws,
+                                int64_t ws_bytes, tlb200_gemm_plan* out) {
+  g_err[0] = 0;
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
+  Resolved r;
+  if (int rc = plan_call(desc, dev, a, b, c, ws, ws_bytes, 0, 0, &r)) return rc;
+  if (out) *out = r.plan;
+  return 0;
+}
+
+int tlb200_is_own_device_memory(const void* ptr, int64_t bytes) {
+  g_err[0] = 0;
+  int dev;
+  if (current_device_ready(&dev)) return 0;
+  return own_device_extent(ptr, bytes, dev) ? 1 : 0;
 }
 
 int tlb200_init(int device) {
@@ -793,7 +904,7 @@ int tlb200_init(int device) {
       rc = fail("tlb200_init: device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
       break;
     }
-    g_sm_count[device] = prop.multiProcessorCount;
+    g_sm_count[device].store(prop.multiProcessorCount);
     if (!g_encode) {
       void* fn = nullptr;
       cudaDriverEntryPointQueryResult q;
@@ -803,6 +914,22 @@ int tlb200_init(int device) {
         break;
       }
       g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+      // Optional: without them own_device_extent() answers "no" and the A-multicast plan is simply never used.
+      auto bind = [](const char* name) -> void* {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint(name, &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+          cudaGetLastError();
+          return nullptr;
+        }
+        return f;
+      };
+      g_ptr_attr = reinterpret_cast<PtrAttrFn>(bind("cuPointerGetAttribute"));
+      g_addr_range = reinterpret_cast<AddrRangeFn>(bind("cuMemGetAddressRange"));
+      g_retain_handle = reinterpret_cast<RetainHandleFn>(bind("cuMemRetainAllocationHandle"));
+      g_release_handle = reinterpret_cast<ReleaseHandleFn>(bind("cuMemRelease"));
+      const char* nm = getenv("TLB200_NO_MULTICAST");
+      g_no_multicast = nm && nm[0] && nm[0] != '0';
     }
     // Same step as the generated init(): raise the dynamic shared memory limit (wrapper.py:15-21).
     e = cudaSuccess;
@@ -846,7 +973,7 @@ int tlb200_init(int device) {
              cudaEventCreateWithFlags(&hp.done[i], cudaEventDisableTiming) == cudaSuccess;
       if (!ok) { rc = fail("tlb200_init: cannot create copy streams/events: %s", cudaGetErrorString(cudaGetLastError())); break; }
     }
-    g_dev_ready[device] = true;
+    g_dev_ready[device].store(true);
   } while (0);
   if (prev >= 0 && prev != device) cudaSetDevice(prev);
   return rc;
@@ -859,35 +986,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
-  bool allow_mc = n_groups == 0;  // grouped row tiles are not paired up across column tiles
-  if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b, allow_mc)) return rc;
-  if (r.mc == 2) {
-    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
-    // memory hung the GPU: the multicast plan is used only when the A the kernel will read (the caller's, or its
-    // re-pitched copy in the workspace) is ordinary device memory of the current device.
-    const void* a_src = r.copy_a ? ws : a;
-    cudaPointerAttributes pa;
-    const bool own = a_src && cudaPointerGetAttributes(&pa, a_src) == cudaSuccess && pa.type == cudaMemoryTypeDevice && pa.device == dev;
-    if (!own) {
-      cudaGetLastError();
-      if (d->cfg_cta_group == 4)
-        return fail("tlb200_gemm: cfg_cta_group=4 (A multicast) needs A in the current device's own memory");
-      allow_mc = false;
-      if (int rc = resolve(d, g_sm_count[dev], c, &r, ws != nullptr, a, b, allow_mc)) return rc;
-    }
-  }
-  if (r.split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
-  if (r.ws_bytes > 0) {
-    if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
-    if (ws_bytes < r.ws_bytes && r.split_k > 1 && d->reserved[1] <= 1) {
-      tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
-      d1.reserved[1] = 1;
-      if (int rc = resolve(&d1, g_sm_count[dev], c, &r, true, a, b, allow_mc)) return rc;
-    }
-    if (ws_bytes < r.ws_bytes)
-      return fail("tlb200_gemm_ex: this call needs a %lld-byte workspace (%lld for re-pitched operands, %lld for split-K x%d), got %lld",
-                  r.ws_bytes, r.a_copy_bytes + r.b_copy_bytes, r.split_bytes, r.split_k, (long long)ws_bytes);
-  }
+  if (int rc = plan_call(d, dev, a, b, c, ws, ws_bytes, n_peer, n_groups, &r)) return rc;
   const bool split = r.split_k > 1;
   // The tail split is optional: it is used when the workspace also holds its partial tiles (256-aligned), and never
   // for grouped contractions or multiple destinations.
@@ -898,18 +997,22 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
   const int out_kind = out_kind_of(d->c_dtype);
   cudaError_t e;
-  if (d->k == 0) {  // empty contraction: C = 0 (T.clear semantics)
+  if (d->k == 0) {  // empty contraction: C = 0 (T.clear semantics), in every destination
+    if (d->epilogue & TLB200_EPI_ACCUMULATE) return 0;  // C += 0
     const int blocks = 148 * 4;
-    switch (out_kind) {
-      case kOutF16: fill_zero_kernel<kOutF16><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
-      case kOutBF16: fill_zero_kernel<kOutBF16><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
-      case kOutF32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
-      case kOutE4M3: fill_zero_kernel<kOutE4M3><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
-      case kOutI32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;  // same bits
-      default: fill_zero_kernel<kOutE5M2><<<blocks, 256, 0, stream>>>(c, d->ldc, d->m, d->n); break;
+    for (int g = -1; g < n_peer; ++g) {
+      void* dst = g < 0 ? c : peers[g];
+      switch (out_kind) {
+        case kOutF16: fill_zero_kernel<kOutF16><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;
+        case kOutBF16: fill_zero_kernel<kOutBF16><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;
+        case kOutF32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;
+        case kOutE4M3: fill_zero_kernel<kOutE4M3><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;
+        case kOutI32: fill_zero_kernel<kOutF32><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;  // same bits
+        default: fill_zero_kernel<kOutE5M2><<<blocks, 256, 0, stream>>>(dst, d->ldc, d->m, d->n); break;
+      }
+      if ((e = cudaGetLastError()) != cudaSuccess) return fail("tlb200_gemm: fill launch: %s", cudaGetErrorString(e));
+      g_launches++;
     }
-    if ((e = cudaGetLastError()) != cudaSuccess) return fail("tlb200_gemm: fill launch: %s", cudaGetErrorString(e));
-    g_launches++;
     return 0;
   }
 
@@ -998,7 +1101,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     kp.group_tile[n_groups] = tile;
     kp.tiles_m = tile;
     if (tile == 0) return 0;
-    long long clusters = g_sm_count[dev] / pl.cta_group;
+    long long clusters = g_sm_count[dev].load() / pl.cta_group;
     const long long items = static_cast<long long>(tile) * pl.tiles_n;
     if (clusters > items) clusters = items;
     grid = static_cast<int>(clusters < 1 ? 1 : clusters) * pl.cta_group;
@@ -1159,7 +1262,7 @@ int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* d, const void* a, con
   int cg = d->cfg_cta_group, bn = d->cfg_block_n;
   if (cg != 0 && cg != 1 && cg != 2) return fail("tlb200_gemm_blockscaled: cfg_cta_group %d (0, 1 or 2)", cg);
   if (bn != 0 && bn != 128 && bn != 256) return fail("tlb200_gemm_blockscaled: cfg_block_n %d (0, 128 or 256)", bn);
-  const int sms = g_sm_count[dev];
+  const int sms = g_sm_count[dev].load();
   if (bn == 0) {
     // 256-wide tiles halve the A traffic; fall back to 128 when that leaves SMs without a tile
     const long long t256 = static_cast<long long>((d->m + 127) / 128) * ((d->n + 255) / 256);
@@ -1254,22 +1357,35 @@ int tlb200_gemm_static_scratch(const tlb200_gemm_desc* d, const void* a, const v
     }
     scratch = g_static_scratch_ptr[dev];
   }
+  // Size check on the plan this very call would run (same pointers, same fall-backs as gemm_impl: an AUTOMATIC
+  // split-K that does not fit simply runs unsplit).  Only scratch the caller asked for by name - a forced
+  // cfg_split_k, or operands that must be re-pitched - can exceed the array, and that is an error here.
   Resolved r;
-  if (int rc = resolve(d, g_sm_count[dev], c, &r, true)) return rc;
-  if (r.ws_bytes > static_cast<long long>(TLB200_STATIC_SCRATCH_BYTES))
-    return fail("tlb200_gemm_static_scratch: this plan (split-K x%d of %dx%d) needs %lld bytes of scratch but the static "
-                "scratch array holds %u; lower cfg_split_k or call tlb200_gemm_ex with a workspace of your own",
-                r.split_k, d->m, d->n, r.ws_bytes, static_cast<unsigned>(TLB200_STATIC_SCRATCH_BYTES));
+  if (plan_call(d, dev, a, b, c, scratch, static_cast<int64_t>(TLB200_STATIC_SCRATCH_BYTES), 0, 0, &r)) {
+    Resolved want;  // what it would have needed, for the message
+    if (resolve(d, g_sm_count[dev].load(), c, &want, true, a, b, false) == 0 &&
+        want.ws_bytes > static_cast<long long>(TLB200_STATIC_SCRATCH_BYTES))
+      return fail("tlb200_gemm_static_scratch: this plan (split-K x%d of %dx%d) needs %lld bytes of scratch but the static "
+                  "scratch array holds %u; lower cfg_split_k or call tlb200_gemm_ex with a workspace of your own",
+                  want.split_k, d->m, d->n, want.ws_bytes, static_cast<unsigned>(TLB200_STATIC_SCRATCH_BYTES));
+    return -1;  // plan_call's own message stands
+  }
   return gemm_impl(d, a, b, c, scratch, static_cast<int64_t>(TLB200_STATIC_SCRATCH_BYTES), stream_v);
 }
 
 int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* d) {
   int dev = -1;
   cudaGetDevice(&dev);
-  const int sms = (dev >= 0 && dev < kMaxDevices && g_sm_count[dev] > 0) ? g_sm_count[dev] : 148;
+  const int sms = (dev >= 0 && dev < kMaxDevices && g_sm_count[dev].load() > 0) ? g_sm_count[dev].load() : 148;
+  // Whether a call takes the A-multicast plan depends on where its A lives: size for the larger of the two plans.
+  // The tail part is optional: a smaller workspace simply runs without the tail split.
   Resolved r;
-  if (resolve(d, sms, nullptr, &r, true)) return -1;
-  return r.ws_bytes + r.tail_bytes;  // the tail part is optional: a smaller workspace simply runs without the tail split
+  if (resolve(d, sms, nullptr, &r, true, nullptr, nullptr, false)) return -1;
+  long long need = r.ws_bytes + r.tail_bytes;
+  if (!g_no_multicast && resolve(d, sms, nullptr, &r, true, nullptr, nullptr, true) == 0 && r.ws_bytes + r.tail_bytes > need)
+    need = r.ws_bytes + r.tail_bytes;
+  g_err[0] = 0;
+  return need;
 }
 
 static long long extent_bytes(long long rows, long long cols, long long ld, int eb) {
@@ -1305,6 +1421,8 @@ int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, 
   if (ws_bytes < need || (!ws && need > 0)) return fail("tlb200_gemm_host: workspace %lld B < required %lld B", (long long)ws_bytes, (long long)need);
   if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_host: workspace must be 256-byte aligned");
   if (d->m == 0 || d->n == 0) return 0;
+  if (d->epilogue & TLB200_EPI_ACCUMULATE)
+    return fail("tlb200_gemm_host: TLB200_EPI_ACCUMULATE is not offered with host buffers (C is write-only on this path)");
   if (!hc || (d->k > 0 && (!ha || !hb))) return fail("tlb200_gemm_host: null host pointer");
   const int es = dtype_bytes(d->ab_dtype), ob = dtype_bytes(d->c_dtype);
   const long long a_rows = d->trans_a ? d->k : d->m, a_cols = d->trans_a ? d->m : d->k;

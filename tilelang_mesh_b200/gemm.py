@@ -265,7 +265,9 @@ def gemm_bcast(a: torch.Tensor, b: torch.Tensor, dst_ptrs, ldc: int, c_dtype: to
 
 def plan(m, n, k, ab_dtype=torch.bfloat16, c_dtype=torch.bfloat16, trans_a=False, trans_b=True,
          sm_count=148, **cfg) -> dict:
-    """Resolve the tile plan for a problem without touching a GPU."""
+    """Resolve the tile plan for a problem without touching a GPU.  Nothing is known about where A lives, so the
+    A-multicast plan (``multicast`` = 2) is reported only for an explicit ``cta_group=4``; ``plan_for`` reports the
+    plan a call with given tensors runs."""
     lda = m if trans_a else k
     ldb = k if trans_b else n
     desc = make_desc(m, n, k, _TORCH2TLB[ab_dtype], _TORCH2TLB[c_dtype], trans_a, trans_b, lda, ldb, n,
@@ -275,3 +277,30 @@ def plan(m, n, k, ab_dtype=torch.bfloat16, c_dtype=torch.bfloat16, trans_a=False
     _abi.check(lib.tlb200_gemm_plan_query(ctypes.byref(desc), sm_count, ctypes.byref(out)),
                "tlb200_gemm_plan_query")
     return out.as_dict()
+
+
+def plan_for(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, trans_a: bool = False, trans_b: bool = True,
+             workspace_bytes: Optional[int] = None, **cfg) -> dict:
+    """The plan ``gemm(a, b, c, ...)`` would run for exactly these tensors on their device (no launch):
+    tlb200_gemm_plan_query_call.  ``workspace_bytes`` defaults to what ``gemm`` itself would provide."""
+    m, ka = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    n = b.shape[0] if trans_b else b.shape[1]
+    desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, _row_pitch(a, "A"),
+                     _row_pitch(b, "B"), _row_pitch(c, "C"), **cfg)
+    lib = _abi.load()
+    dev = c.device.index if c.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    out = _abi.GemmPlan()
+    with torch.cuda.device(dev):
+        need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc)) if workspace_bytes is None else int(workspace_bytes)
+        ws = _workspace(dev, torch._C._cuda_getCurrentRawStream(dev), need) if need > 0 else None
+        rc = lib.tlb200_gemm_plan_query_call(ctypes.byref(desc), a.data_ptr(), b.data_ptr(), c.data_ptr(),
+                                             ws.data_ptr() if ws is not None else None, need if ws is not None else 0,
+                                             ctypes.byref(out))
+    _abi.check(rc, "tlb200_gemm_plan_query_call")
+    return out.as_dict()
+
+
+def is_own_device_memory(ptr: int, nbytes: int) -> bool:
+    """tlb200_is_own_device_memory on the current device: the condition under which TMA multicast loads are used."""
+    return bool(_abi.load().tlb200_is_own_device_memory(ctypes.c_void_p(int(ptr)), int(nbytes)))

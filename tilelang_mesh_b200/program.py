@@ -141,6 +141,7 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
     kloop = next(li for li in tr.loops if li.var is g.loop)
     A_s, B_s, C_acc = _buf(g.A), _buf(g.B), _buf(g.C)
     notes = []
+    used = [g]  # ops the pattern accounts for; every other recorded op makes the program something else (swept at the end)
 
     def through_fragment(b, nm):
         # gemm_rs / gemm_sr / gemm_rr forms of the reference's tile-library tests (matmul_rs: T.copy(A_shared, A_frag);
@@ -154,6 +155,7 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
             _fail(f"T.gemm operand {nm} is a fragment that is not a plain copy of a shared tile filled in the same K loop")
         notes.append(f"operand {nm} read from a fragment copy of its shared tile (gemm_{'r' if nm == 'A' else 's'}* form): "
                      "tcgen05.mma reads the shared tile directly")
+        used.append(cs[0])
         return _buf(cs[0].src)
 
     A_s, B_s = through_fragment(A_s, "A"), through_fragment(B_s, "B")
@@ -180,11 +182,19 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
     # ---- staging copies: global -> A_shared / B_shared inside the K loop
     def staging(tile, nm):
         cs = [o for o in tr.ops if isinstance(o, T.CopyOp) and _buf(o.dst) is tile]
-        cs += [_elementwise_staging(o, nm) for o in tr.ops
-               if isinstance(o, T.ElemStore) and o.buffer is tile and isinstance(o.value, T.BufferRegion)]
+        raw = list(cs)
+        for o in tr.ops:
+            if isinstance(o, T.ElemStore) and o.buffer is tile:
+                # any element-wise write to an operand tile other than the staging fill itself (e.g. scaling the tile
+                # in place between T.copy and T.gemm) changes what is multiplied
+                if not isinstance(o.value, T.BufferRegion):
+                    _fail(f"{nm}_shared is modified element-wise ({o.value!r}) besides being filled from global memory")
+                cs.append(_elementwise_staging(o, nm))
+                raw.append(o)
         if len(cs) != 1:
             _fail(f"expected one T.copy into {nm}_shared, found {len(cs)}")
         c = cs[0]
+        used.append(raw[0])
         if c.loop is not g.loop:
             _fail(f"T.copy into {nm}_shared is not in the same K loop as T.gemm")
         src = _buf(c.src)
@@ -265,7 +275,10 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
         _fail("a single tile does not cover the output and no block index walks it")
 
     # ---- accumulator initialisation: T.clear before the loop, or clear_accum = (k == 0)
-    cleared = any(isinstance(o, T.ClearOp) and o.buffer is C_acc and o.value == 0.0 and o.loop is None for o in tr.ops)
+    pre = tr.ops[:tr.ops.index(g)]
+    clears = [o for o in pre if isinstance(o, T.ClearOp) and o.buffer is C_acc and o.value == 0.0 and o.loop is None]
+    cleared = bool(clears)
+    used.extend(clears)
     ca = g.clear_accum
     clear_first = False
     if isinstance(ca, BinOp) and ca.op == "==":
@@ -317,6 +330,7 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
                 region = o.dst
             C_g, c_org = region.buffer, _tile_origin(region, {}, f"T.atomic_add ->{region.buffer.name}")
             accumulate = True
+            used.append(o)
             break
         if isinstance(o, T.CopyOp):
             if o.loop is not None:
@@ -324,6 +338,7 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
             if _buf(o.src) is not cur:
                 _fail(f"epilogue copies a buffer ({_buf(o.src).name}) that does not hold the accumulator")
             dst = _buf(o.dst)
+            used.append(o)
             if dst.is_global:
                 C_g, c_org = dst, _tile_origin(o.dst, {}, f"T.copy ->{dst.name}")
                 break
@@ -331,6 +346,11 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
                 _fail(f"epilogue staging buffer {dst.name} has shape {dst.shape}, expected {(bM, bN)}")
             cur = dst
         elif isinstance(o, T.ElemStore):
+            if o.loop is not None:
+                # inside the K loop it runs once per K block (a geometric rescaling of the running sum), which no
+                # whole-problem alpha expresses
+                _fail("element-wise update of the accumulator inside the K loop (only a post-loop epilogue is fused)")
+            used.append(o)
             if o.buffer is not cur or len(o.index) != 2 or len(o.parallel_vars) != 2 or \
                     any(a is not b for a, b in zip(o.index, o.parallel_vars)):
                 _fail("element-wise epilogue must be `C[i, j] = f(C[i, j])` over the whole accumulator tile")
@@ -357,6 +377,13 @@ def recognize_gemm(func: "T.PrimFunc", env: Optional[dict] = None) -> GemmProgra
             _fail("T.clear/T.fill after T.gemm")
     if C_g is None:
         _fail("the accumulator is never copied to a global tensor")
+    # Sweep: the pattern above accounts for the staging copies, the gemm, the accumulator clear and the post-loop
+    # epilogue chain.  Any other recorded operation (a second write to an operand tile, work after the store, an op
+    # type this recogniser does not know) means the program computes something else.
+    for o in tr.ops:
+        if not any(o is u for u in used):
+            where = "inside the K loop" if getattr(o, "loop", None) is not None else "outside the K loop"
+            _fail(f"unexpected {type(o).__name__} {where} that is not part of the copy -> gemm -> epilogue -> store pattern")
     if split and not accumulate:
         _fail("a program that cuts K over a grid dimension must add its partial tiles into C (T.atomic_add)")
     if tuple(cv(x) for x in C_g.shape) != (M, N):
