@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the tcgen05 GEMM path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dtype bf16|fp8]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dtype bf16|fp8] [--no-extra]
 
 A "step" is one dense contraction C[M,N] = A[M,K] . B[N,K]^T (benchmark/matmul's NT layout,
 fp32 accumulate) of 8192 x 8192 x 8192 per GPU on synthetic randn data: at N=1 that is
@@ -12,12 +12,22 @@ Printed line (rank 0): value = whole-job TFLOP/s with operands resident in HBM, 
 events over exactly K back-to-back launches (max over ranks); e2e = the same contraction through
 the C ABI's host-buffer entry point (pinned host A, B, C; H2D + kernel + D2H inside the timed
 region); roofline = tensor-pipe fraction of the MEASURED cuBLAS peak; cpu_baseline = the
-reference's CPU path for T.gemm (torch.matmul on host cores; T.gemm has no C/LLVM lowering) on a
-bounded sample.  --impl reference times that CPU path alone.
+reference's CPU path for T.gemm (torch.matmul on host cores; T.gemm has no C/LLVM lowering) on the
+same 8192^3 problem.  --impl reference times that CPU path alone, on the same config.
+
+At N=1 the line also carries `extra`: the other BASELINE.json configs and the figures that explain the
+headline, each with its own ms_per_step / roofline / clocks, next to the library GEMM (cuBLAS; cuBLASLt fp8
+through torch._scaled_mm) timed the same way in the same run: `sustained_bf16` (>= 2 s loop), `c3_fp8`
+(8192^3 e4m3, burst and >= 2 s; its roofline peak is the library fp8 rate measured here, not an assumed
+2x), `c4_mlp_up` / `c4_mlp_down` (16384 x 14336 x 4096 and 16384 x 4096 x 14336 bf16).
+At N>1 it carries `nshard`: the N-sharded 65536 x 8192 x 8192 variant whose epilogue stores every C tile
+into all ranks' copies of C over NVLink, against GEMM + ncclAllGather and the link floor.  Every rank
+checks a sample of rows of its C against an fp32 torch.matmul outside the timed region (`verified`).
 """
 import argparse
 import ctypes
 import json
+import math
 import os
 import sys
 import threading
@@ -30,10 +40,22 @@ if ROOT not in sys.path:
 M_PER_GPU, N_DIM, K_DIM = 8192, 8192, 8192
 NOMINAL = {"bf16": 2250.0, "fp8": 4500.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel bench.py times, from the
-# `ncu --set full` captures profiles/prof_bf16_r1d.txt and profiles/prof_fp8_r1d.txt (8192^3, default plan).
+# `ncu --set full` captures named in NCU_TRAFFIC_SOURCE (8192^3, default plan).
 NCU_DRAM_TRAFFIC = {"bf16": 853_894_912 + 119_959_296, "fp8": 229_277_440 + 115_448_832}
+NCU_TRAFFIC_SOURCE = {"bf16": "profiles/prof_bf16_r1e.txt", "fp8": "profiles/prof_fp8_r1e.txt"}
+NVLINK_GBS = 770.0  # measured unidirectional NVLink rate per GPU on this pool (profiles/r1_notes.md)
 METRIC = {"bf16": "GEMM TFLOP/s (bf16, 8192^3 per GPU, fp32 accumulate)",
           "fp8": "GEMM TFLOP/s (fp8 e4m3, 8192^3 per GPU, per-tensor scales, fp32 accumulate)"}
+SUSTAINED_S = 2.0  # a loop at least this long runs at the power-capped clock
+
+
+def workload_config(dtype, world):
+    """`config` of the JSON line: identical for this arm and for --impl reference."""
+    fp8 = dtype == "fp8"
+    return {"workload": "benchmark/matmul%s GEMM M=N=K=8192 per GPU, NT, fp32-accumulate, bf16 out (C2%s; N ranks = M-sharded %dx8192x8192, "
+                        "B replicated, no collective)" % ("_fp8 e4m3 per-tensor-scaled" if fp8 else " bf16", "->C3" if fp8 else "", M_PER_GPU * world),
+            "m_per_gpu": M_PER_GPU, "n": N_DIM, "k": K_DIM,
+            "l2": "inputs (A+B = %d MiB) exceed the 126 MB L2; no flush" % ((M_PER_GPU + N_DIM) * K_DIM * (1 if fp8 else 2) >> 20)}
 
 
 def load_peaks():
@@ -87,14 +109,14 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def cpu_path_tflops(dtype, sample_rows, repeats, seed=0):
+def cpu_path_tflops(dtype, repeats, seed=0):
     """The reference's CPU path for this contraction (north_star: torch.matmul on host cores, since
-    T.gemm has no C/LLVM lowering), through the oracle's fp32 restatement, on `sample_rows` rows."""
+    T.gemm has no C/LLVM lowering), through the oracle's fp32 restatement, on the full 8192^3 problem."""
     import torch
     from oracle import gemm_ref as R
     torch.manual_seed(seed)
     torch.set_num_threads(os.cpu_count() or 1)
-    a = torch.randn(sample_rows, K_DIM)
+    a = torch.randn(M_PER_GPU, K_DIM)
     b = torch.randn(N_DIM, K_DIM)
     if dtype == "fp8":
         a, b = a.half().to(torch.float8_e4m3fn), b.half().to(torch.float8_e4m3fn)
@@ -107,7 +129,7 @@ def cpu_path_tflops(dtype, sample_rows, repeats, seed=0):
         t0 = time.perf_counter()
         R.matmul_fp32(af, bf)
         best = min(best, time.perf_counter() - t0)
-    flop = 2.0 * sample_rows * N_DIM * K_DIM
+    flop = 2.0 * M_PER_GPU * N_DIM * K_DIM
     return flop / best / 1e12, best, torch.get_num_threads()
 
 
@@ -115,42 +137,228 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    rows = 2048
-    steps = max(1, args.steps)
-    t_all, best_tf = 0.0, 0.0
-    # each step = one bounded sample (rows x 8192 x 8192) of the workload on all host threads
+    # each step = the whole 8192 x 8192 x 8192 contraction on all host threads (about half a second)
     import torch
     from oracle import gemm_ref as R
     torch.set_num_threads(os.cpu_count() or 1)
     torch.manual_seed(0)
-    a = torch.randn(rows, K_DIM).bfloat16().float()
+    a = torch.randn(M_PER_GPU, K_DIM).bfloat16().float()
     b = torch.randn(N_DIM, K_DIM).bfloat16().float()
-    for _ in range(max(1, min(args.warmup, 2))):
-        R.matmul_fp32(a[:512], b)
+    for _ in range(max(1, min(args.warmup, 3))):
+        R.matmul_fp32(a[:1024], b)
     budget_s = 150.0
-    done = 0
+    steps = max(1, args.steps)
+    t_all, done = 0.0, 0
     for _ in range(steps):
         t0 = time.perf_counter()
         R.matmul_fp32(a, b)
-        dt = time.perf_counter() - t0
-        t_all += dt
+        t_all += time.perf_counter() - t0
         done += 1
-        best_tf = max(best_tf, 2.0 * rows * N_DIM * K_DIM / dt / 1e12)
         if t_all > budget_s:
             break
-    value = 2.0 * rows * N_DIM * K_DIM * done / t_all / 1e12
+    flop = 2.0 * M_PER_GPU * N_DIM * K_DIM
+    value = flop * done / t_all / 1e12
     cores = torch.get_num_threads()
-    sample = f"{rows}x{N_DIM}x{K_DIM} row-block of the 8192^3 workload per step, fp32 torch.matmul of the bf16 inputs, {done} steps"
+    sample = f"the whole {M_PER_GPU}x{N_DIM}x{K_DIM} contraction per step, fp32 torch.matmul of the bf16 inputs on host cores, {done} steps"
     line = {"impl": "reference", "metric": METRIC["bf16"], "value": round(value, 4), "unit": "TFLOP/s", "n_gpus": args.gpus,
             "steps": done, "warmup": args.warmup, "ms_per_step": round(t_all / done * 1e3, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "benchmark/matmul bf16 GEMM M=N=K=8192 fp32-accumulate (C2), CPU path: torch.matmul on host cores (T.gemm has no CPU lowering)",
-                       "sample_rows": rows},
+            "config": workload_config("bf16", max(1, args.gpus)),
+            "cpu_path": "torch.matmul on host cores (T.gemm has no C/LLVM lowering: src/tl_templates/cpp/gemm.h)",
             "cpu_baseline": {"value": round(value, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": round(value, 4), "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm helpers
+def timed_loop(fn, steps, device_index, min_seconds=0.0, warm=3):
+    """`steps` back-to-back calls of fn between two CUDA events on the current stream (at least `min_seconds` of
+    them when given: the step count is then derived from a short calibration), clocks sampled through NVML."""
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    if min_seconds > 0:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        steps = max(steps, int(math.ceil(min_seconds / (e0.elapsed_time(e1) / 5 * 1e-3) * 1.3)))
+    sampler = ClockSampler(device_index)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    sampler.start()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    sampler.stop_flag = True
+    sampler.join(timeout=1.0)
+    return e0.elapsed_time(e1), steps, sampler.summary()
+
+
+def rate_record(workload, flop, ms, steps, clocks, peak, peak_kind, nominal, launches=None, library=None):
+    tf = flop * steps / (ms * 1e-3) / 1e12
+    rec = {"workload": workload, "value": round(tf, 2), "unit": "TFLOP/s", "steps": steps, "ms_per_step": round(ms / steps, 5),
+           "region_s": round(ms * 1e-3, 3),
+           "roofline": {"bound": "tensor", "achieved": round(tf, 2), "peak": round(peak, 1), "unit": "TFLOP/s",
+                        "frac": round(tf / peak, 4), "peak_kind": peak_kind, "frac_nominal": round(tf / nominal, 4),
+                        "nominal_peak": nominal},
+           "clocks": clocks}
+    if launches is not None:
+        rec["gpu_launches"] = int(launches)
+    if library is not None:
+        rec["library"] = library
+    return rec
+
+
+def verify_rows(torch, a, b, c, alpha, rtol, rows=256, seed=0):
+    """A sample of rows of C against north_star's oracle definition (fp32 torch.matmul of the up-cast inputs), with
+    the reference's comparison rule (isclose(rtol, atol=rtol), at most 1 % of elements outside)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    idx = torch.randperm(a.shape[0], generator=g)[:rows].to(a.device)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        want = (a[idx].float() @ b.float().t()) * alpha
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    got = c[idx].float()
+    bad = (~torch.isclose(got, want.to(c.dtype).float(), rtol=rtol, atol=rtol)).float().mean().item()
+    return bad <= 0.01 and bool(torch.isfinite(got).all())
+
+
+def extras_single_gpu(torch, G, lib, dev, local, steps, peaks):
+    """The other BASELINE.json configs and the sustained figures, each next to the library GEMM in the same run."""
+    out = {}
+    bf = torch.bfloat16
+
+    def ours_vs_cublas(key, workload, m, n, k, min_seconds, tag):
+        torch.manual_seed(1)
+        a = torch.randn(m, k, device=dev).bfloat16()
+        b = torch.randn(n, k, device=dev).bfloat16()
+        c = torch.empty(m, n, device=dev, dtype=bf)
+        c2 = torch.empty(m, n, device=dev, dtype=bf)
+        flop = 2.0 * m * n * k
+        ms_l, st_l, ck_l = timed_loop(lambda: torch.matmul(a, b.t(), out=c2), steps, local, min_seconds)
+        lib_tf = flop * st_l / (ms_l * 1e-3) / 1e12
+        n0 = lib.tlb200_launch_count()
+        ms, st, ck = timed_loop(lambda: G.gemm(a, b, c), steps, local, min_seconds)
+        launches = lib.tlb200_launch_count() - n0
+        ok = verify_rows(torch, a, b, c, 1.0, 1e-2)
+        rec = rate_record(workload, flop, ms, st, ck, lib_tf, "cuBLAS bf16 (torch.matmul) on the same shape, %s, timed in this run" % tag,
+                          NOMINAL["bf16"], launches,
+                          {"name": "cuBLAS bf16 via torch.matmul", "value": round(lib_tf, 2), "ms_per_step": round(ms_l / st_l, 5),
+                           "steps": st_l, "clocks": ck_l})
+        rec["verified"] = ok
+        rec["plan"] = G.plan_for(a, b, c)
+        out[key] = rec
+        del a, b, c, c2
+
+    ours_vs_cublas("sustained_bf16", "C2 bf16 8192^3, loop of >= %.0f s (power-capped clock)" % SUSTAINED_S, 8192, 8192, 8192, SUSTAINED_S,
+                   ">= %.0f s loop" % SUSTAINED_S)
+    ours_vs_cublas("c4_mlp_up", "C4 Llama-3-8B MLP up/gate: tokens 16384, 4096 -> 14336, bf16 (M=16384 N=14336 K=4096)", 16384, 14336, 4096, 0.0,
+                   "%d back-to-back launches" % steps)
+    ours_vs_cublas("c4_mlp_down", "C4 Llama-3-8B MLP down: tokens 16384, 14336 -> 4096, bf16 (M=16384 N=4096 K=14336)", 16384, 4096, 14336, 0.0,
+                   "%d back-to-back launches" % steps)
+
+    # ---- C3: fp8 e4m3 8192^3, per-tensor scales; the library figure is cuBLASLt's fp8 GEMM through torch._scaled_mm
+    m = n = k = 8192
+    torch.manual_seed(2)
+    af, bfl = torch.randn(m, k, device=dev), torch.randn(n, k, device=dev)
+    sa, sb = af.abs().max().item() / 448.0, bfl.abs().max().item() / 448.0
+    a8, b8 = (af / sa).to(torch.float8_e4m3fn), (bfl / sb).to(torch.float8_e4m3fn)
+    del af, bfl
+    c = torch.empty(m, n, device=dev, dtype=bf)
+    flop = 2.0 * m * n * k
+    sa_t, sb_t = torch.tensor(sa, device=dev), torch.tensor(sb, device=dev)
+    lib_rates = {}
+    try:
+        def lib_fp8():
+            return torch._scaled_mm(a8, b8.t(), scale_a=sa_t, scale_b=sb_t, out_dtype=bf)
+        lib_fp8()
+        for tag, secs in (("burst", 0.0), ("sustained", SUSTAINED_S)):
+            ms_l, st_l, ck_l = timed_loop(lib_fp8, steps, local, secs)
+            lib_rates[tag] = {"name": "cuBLASLt fp8 e4m3 via torch._scaled_mm", "value": round(flop * st_l / (ms_l * 1e-3) / 1e12, 2),
+                              "ms_per_step": round(ms_l / st_l, 5), "steps": st_l, "clocks": ck_l}
+    except Exception as e:  # noqa: BLE001 - the library fp8 GEMM is only the yardstick
+        lib_rates = {"error": repr(e)[:200]}
+    for tag, secs in (("burst", 0.0), ("sustained", SUSTAINED_S)):
+        n0 = lib.tlb200_launch_count()
+        ms, st, ck = timed_loop(lambda: G.gemm(a8, b8, c, alpha=sa * sb), steps, local, secs)
+        launches = lib.tlb200_launch_count() - n0
+        if tag in lib_rates:
+            peak, kind = lib_rates[tag]["value"], "cuBLASLt fp8 (torch._scaled_mm) on the same shape, %s, timed in this run" % tag
+        else:
+            peak = 2.0 * (peaks["sustained"] if secs else peaks["burst"])
+            kind = "ASSUMED 2x the measured bf16 figure (no library fp8 GEMM could be timed: %s)" % lib_rates.get("error", "?")
+        rec = rate_record("C3 benchmark/matmul_fp8 e4m3 8192^3, per-tensor scales, bf16 out, %s" % (">= %.0f s loop" % secs if secs else "%d back-to-back launches" % st),
+                          flop, ms, st, ck, peak, kind, NOMINAL["fp8"], launches, lib_rates.get(tag))
+        rec["roofline"]["traffic"] = NCU_DRAM_TRAFFIC["fp8"]
+        rec["roofline"]["traffic_source"] = "ncu capture %s (bytes per launch)" % NCU_TRAFFIC_SOURCE["fp8"]
+        rec["roofline"]["algorithmic_bytes_per_launch"] = 2 * m * k + m * n * 2
+        rec["verified"] = verify_rows(torch, a8, b8, c, sa * sb, 5e-2)
+        if tag == "burst":
+            rec["plan"] = G.plan_for(a8, b8, c)
+        out["c3_fp8" if tag == "burst" else "c3_fp8_sustained"] = rec
+    return out
+
+
+def nshard_record(torch, dist, G, dev, world, rank, steps):
+    """C5's optional variant: B split by rows over the ranks, every rank ends with the full C.  Fused = the GEMM
+    kernel's epilogue stores each C tile into every rank's copy of C over NVLink (tlb200_gemm_bcast, one kernel,
+    no NCCL on the data path); baseline = local GEMM followed by ncclAllGather."""
+    from tilelang_mesh_b200.parallel import ShardedGemm
+    M, N, K = M_PER_GPU * world, N_DIM, K_DIM
+    torch.manual_seed(7)
+    A = torch.randn(M, K, device=dev).bfloat16()
+    lo, hi = rank * (N // world), (rank + 1) * (N // world)
+    torch.manual_seed(8)
+    B_full = torch.randn(N, K, device=dev).bfloat16()
+    B = B_full[lo:hi].contiguous()
+    iters = max(3, min(steps, 10))
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    sf = ShardedGemm(M, N, K, mode="N", fused=True)
+    sn = ShardedGemm(M, N, K, mode="N", panel_rows=8192)
+    cl = torch.empty(M, hi - lo, device=dev, dtype=torch.bfloat16)
+    t_f = timed(lambda: sf.run(A, B))
+    t_n = timed(lambda: sn.run(A, B))
+    t_g = timed(lambda: G.gemm(A, B, cl))
+    full_f = sf.run(A, B)
+    torch.cuda.synchronize()
+    same = torch.equal(full_f.view(torch.int16), sn.run(A, B).view(torch.int16))
+    ok = verify_rows(torch, A, B_full, full_f, 1.0, 1e-2, rows=128, seed=rank)
+    flags = torch.tensor([int(same), int(ok)], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    recv = M * (N - (hi - lo)) * 2
+    floor_ms = recv / (NVLINK_GBS * 1e9) * 1e3
+    flop = 2.0 * M * N * K
+    return {"workload": "C5 optional variant: N-sharded %dx%dx%d bf16, full C on every rank" % (M, N, K),
+            "ms_fused": round(t_f, 3), "ms_gemm_then_nccl_allgather": round(t_n, 3), "ms_local_gemm_only": round(t_g, 3),
+            "tflops_fused": round(flop / t_f / 1e9, 1), "tflops_gemm_then_nccl": round(flop / t_n / 1e9, 1),
+            "bytes_received_per_gpu": recv, "nvlink_floor_ms": round(floor_ms, 3), "nvlink_gbs_assumed": NVLINK_GBS,
+            "frac": round(floor_ms / t_f, 4), "frac_meaning": "link floor / fused time (1.0 = the NVLink receive rate is the only cost)",
+            "fused_equals_nccl_path": bool(flags[0].item()), "verified": bool(flags[1].item()), "iters": iters}
 
 
 def run_ours(args):
@@ -183,7 +391,7 @@ def run_ours(args):
     else:
         a, b = a.bfloat16(), b.bfloat16()
     c = torch.empty(m, n, device=dev, dtype=torch.bfloat16)
-    plan = G.plan(m, n, k, a.dtype, c.dtype)
+    plan = G.plan_for(a, b, c, alpha=alpha)
 
     def step():
         G.gemm(a, b, c, alpha=alpha)
@@ -218,6 +426,12 @@ def run_ours(args):
     flop_step = 2.0 * m * n * k
     value = flop_step * world * args.steps / (ms * 1e-3) / 1e12
     per_gpu = value / world
+    # outside the timed region: every rank checks rows of the C it just computed
+    verified = verify_rows(torch, a, b, c, alpha, 5e-2 if fp8 else 1e-2, seed=rank)
+    if world > 1:
+        v = torch.tensor([int(verified)], device=dev)
+        dist.all_reduce(v, op=dist.ReduceOp.MIN)
+        verified = bool(v.item())
 
     # ---- e2e: host buffers through the C ABI (H2D A,B + kernel + D2H C inside the timed region)
     e2e_steps = max(1, min(args.steps, 20))
@@ -246,38 +460,60 @@ def run_ours(args):
         e2e_s = t.item()
     e2e_val = flop_step * world * e2e_steps / e2e_s / 1e12
     same = bool(torch.equal(hc.view(torch.int16), c.cpu().view(torch.int16)))
+    del ws, ha, hb, hc
+
+    peaks = load_peaks()
+    nshard = None
+    if world > 1 and not args.no_extra and n % world == 0:
+        try:
+            nshard = nshard_record(torch, dist, G, dev, world, rank, args.steps)
+        except Exception as e:  # noqa: BLE001 - the sub-record must not take the headline down with it
+            nshard = {"error": repr(e)[:300]}
+    extra = None
+    if world == 1 and not args.no_extra:
+        del a, b, c
+        torch.cuda.empty_cache()
+        extra = extras_single_gpu(torch, G, lib, dev, local, min(max(args.steps, 10), 200), peaks)
 
     if rank == 0:
-        peaks = load_peaks()
         region_s = ms * 1e-3
         sustained = region_s >= 1.0
         peak = peaks["sustained"] if sustained else peaks["burst"]
+        peak_kind = ("sustained" if sustained else "burst") + ", " + peaks["source"]
         if fp8:
-            peak *= 2.0  # no measured fp8 figure exists: fp8 tensor rate is 2x bf16 on the same clocks
+            lib_rec = (extra or {}).get("c3_fp8_sustained" if sustained else "c3_fp8", {}).get("library")
+            if lib_rec:
+                peak, peak_kind = lib_rec["value"], "cuBLASLt fp8 (torch._scaled_mm) timed in this run, " + ("sustained" if sustained else "burst")
+            else:
+                peak, peak_kind = peak * 2.0, peak_kind + " x2 (ASSUMED for fp8: no library fp8 figure in this run)"
+        es = 1 if fp8 else 2
         line = {"metric": METRIC[args.dtype], "value": round(value, 2), "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if not fp8 else "fp8_e4m3", "data": "synthetic",
-                "config": {"workload": "benchmark/matmul%s GEMM M=N=K=8192 per GPU, NT, fp32-accumulate, bf16 out (C2%s; N ranks = M-sharded %dx8192x8192, B replicated, no collective)" %
-                           ("_fp8 e4m3 per-tensor-scaled" if fp8 else " bf16", "->C3" if fp8 else "", m * world),
-                           "m_per_gpu": m, "n": n, "k": k, "tile": "%dx%dx%d" % (plan["block_m"], plan["block_n"], plan["block_k"]),
-                           "cta_group": plan["cta_group"], "stages": plan["stages"], "l2": "inputs (A+B = %d MiB) exceed the 126 MB L2; no flush" %
-                           ((a.numel() * a.element_size() + b.numel() * b.element_size()) >> 20)},
+                "config": workload_config(args.dtype, world),
+                "plan": {"tile": "%dx%dx%d" % (plan["block_m"], plan["block_n"], plan["block_k"]), "cta_group": plan["cta_group"],
+                         "stages": plan["stages"], "multicast": plan["multicast"], "split_k": plan["split_k"], "raster": plan["raster"]},
+                "verified": verified,
                 "roofline": {"bound": "tensor", "achieved": round(per_gpu, 2), "peak": round(peak, 1), "unit": "TFLOP/s",
                              "frac": round(per_gpu / peak, 4), "traffic": NCU_DRAM_TRAFFIC[args.dtype],
-                             "traffic_source": "ncu capture profiles/prof_%s_r1e.txt (bytes per launch)" % ("fp8" if fp8 else "bf16"),
-                             "peak_kind": ("sustained" if sustained else "burst") + (" x2 (fp8)" if fp8 else "") + ", " + peaks["source"],
+                             "traffic_source": "ncu capture %s (bytes per launch)" % NCU_TRAFFIC_SOURCE[args.dtype],
+                             "peak_kind": peak_kind,
                              "frac_nominal": round(per_gpu / NOMINAL[args.dtype], 4), "nominal_peak": NOMINAL[args.dtype],
                              "algorithmic_flop_per_launch": flop_step,
-                             "algorithmic_bytes_per_launch": a.numel() * a.element_size() + b.numel() * b.element_size() + c.numel() * 2},
+                             "algorithmic_bytes_per_launch": (m * k + n * k) * es + m * n * 2},
                 "clocks": sampler.summary(),
-                "e2e": {"value": round(e2e_val, 2), "unit": "TFLOP/s", "h2d_bytes_per_step": (ha.numel() * ha.element_size() + hb.numel() * hb.element_size()) * world,
-                        "d2h_bytes_per_step": hc.numel() * 2 * world, "steps": e2e_steps, "matches_device_path": same,
+                "e2e": {"value": round(e2e_val, 2), "unit": "TFLOP/s", "h2d_bytes_per_step": (m * k + n * k) * es * world,
+                        "d2h_bytes_per_step": m * n * 2 * world, "steps": e2e_steps, "matches_device_path": same,
                         "api": "tlb200_gemm_host (C ABI, pinned host buffers)"},
                 "gpu_launches": int(launches)}
+        if nshard is not None:
+            line["nshard"] = nshard
+        if extra is not None:
+            line["extra"] = extra
         if world == 1:
-            tf, secs, cores = cpu_path_tflops(args.dtype, 2048, 3)
+            tf, secs, cores = cpu_path_tflops(args.dtype, 2)
             line["cpu_baseline"] = {"value": round(tf, 4), "unit": "TFLOP/s", "cores": cores, "kind": "port",
-                                    "sample": "2048x8192x8192 row-block of the workload, fp32 torch.matmul of the same-dtype inputs on host cores, best of 3 (%.2f s)" % secs}
+                                    "sample": "the whole 8192x8192x8192 contraction, fp32 torch.matmul of the same-dtype inputs on host cores, best of 2 (%.2f s)" % secs}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -291,6 +527,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp8"])
+    ap.add_argument("--no-extra", action="store_true", help="headline line only (no `extra` / `nshard` sub-records)")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps == 2000:

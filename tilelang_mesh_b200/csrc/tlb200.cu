@@ -1380,10 +1380,13 @@ int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* d) {
   // Whether a call takes the A-multicast plan depends on where its A lives: size for the larger of the two plans.
   // The tail part is optional: a smaller workspace simply runs without the tail split.
   Resolved r;
-  if (resolve(d, sms, nullptr, &r, true, nullptr, nullptr, false)) return -1;
-  long long need = r.ws_bytes + r.tail_bytes;
-  if (!g_no_multicast && resolve(d, sms, nullptr, &r, true, nullptr, nullptr, true) == 0 && r.ws_bytes + r.tail_bytes > need)
-    need = r.ws_bytes + r.tail_bytes;
+  long long need = -1;
+  for (int with_mc = 0; with_mc < 2; ++with_mc) {
+    if (with_mc ? g_no_multicast : (d && d->cfg_cta_group == 4)) continue;  // a plan family this descriptor cannot take
+    if (resolve(d, sms, nullptr, &r, true, nullptr, nullptr, with_mc != 0) == 0 && r.ws_bytes + r.tail_bytes > need)
+      need = r.ws_bytes + r.tail_bytes;
+  }
+  if (need < 0) return -1;  // the error text of the last resolve stands
   g_err[0] = 0;
   return need;
 }
