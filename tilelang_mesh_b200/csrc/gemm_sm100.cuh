@@ -97,7 +97,17 @@ struct alignas(64) GemmKernelParams {
   int accumulate;  // C = C_in + alpha * acc (predicated-store epilogue only)
   int l2_policy;
   float alpha;
+  long long* trace;  // development builds (-DTLB200_TRACE): per-tile clock64 stamps of CTA 0; null otherwise
 };
+
+#ifdef TLB200_TRACE
+// slot layout per tile of CTA 0 (16 slots): 0 MMA warp holds both accumulators, 1 first K block landed, 2 last commit
+// issued, 3/4 epilogue warp 0 sees accumulator 0 full / has drained it, 5/6 same for accumulator 1, 7-10 the same four
+// for epilogue warp 4 (the other column half), 11 producer warp 0 issues its first K block of the tile
+#define TLB_TRACE(seq, slot) do { if (p.trace && blockIdx.x == 0 && lane == 0) p.trace[(seq) * 16 + (slot)] = clock64(); } while (0)
+#else
+#define TLB_TRACE(seq, slot) do { } while (0)
+#endif
 
 // ---------------------------------------------------------------- output conversion helpers
 template <int kOut>
@@ -257,8 +267,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
 #pragma unroll
             for (int pk = 0; pk < kPacketsPerLd; ++pk) w[h * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
           }
-          if (!slab_free) {  // the TMA store that last read this slab must have drained it
-            if (lane == 0) {
+          if (!slab_free) {  // the TMA stores that last read this slab must have drained it
+            // (bulk groups are per thread: every lane that issues stores waits for its own)
+            if (lane <= o.n_peer) {
               if (nslabs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
             }
             __syncwarp();
@@ -276,13 +287,24 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
       }
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
       __syncwarp();
-      if (lane == 0) {
+      if (o.n_peer == 0) {
+        if (lane == 0) {
+          if (row0 + q * 32 < row_limit) {
+            // C is write-once: evict_first keeps the operands in L2
+            if (o.evict_first) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
+            else tma_store_2d(o.tm, slab, col0 + cs, row_off + row0 + q * 32);
+          }
+          tma_store_commit();
+        }
+      } else if (lane <= o.n_peer) {
+        // Fused all-gather: the same slab goes into the local C and straight into every peer GPU's C over NVLink.
+        // One lane per destination issues (and later waits for) its own store, so the up-to-8 stores of a slab enter
+        // the TMA queue together instead of one after another from a single thread; the lane -> destination map is
+        // rotated per CTA and slab so that the CTAs of a wave do not all address the same peer at the same moment.
         if (row0 + q * 32 < row_limit) {
-          // C is write-once: evict_first keeps the operands in L2
-          if (o.evict_first) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
-          else tma_store_2d(o.tm, slab, col0 + cs, row_off + row0 + q * 32);
-          // fused all-gather: the same slab goes straight into every peer GPU's C over NVLink
-          for (int g = 0; g < o.n_peer; ++g) tma_store_2d(&p.tm_c_peer[g], slab, col0 + cs, row_off + row0 + q * 32);
+          const int dst = (lane + static_cast<int>(blockIdx.x) + slab_iter) % (o.n_peer + 1);  // n_peer = the local C
+          if (dst == o.n_peer) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
+          else tma_store_2d(&p.tm_c_peer[dst], slab, col0 + cs, row_off + row0 + q * 32);
         }
         tma_store_commit();
       }
@@ -487,6 +509,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       const int kb_off = p.b_mn_major ? b_goff : 0;
       int kb0, kb1;
       k_range(t, kb0, kb1);
+      if (warp == 0) TLB_TRACE((t - cluster_id) / num_clusters, 11);
       for (int kb = kb0; kb < kb1; ++kb) {
         const bool mine = turn == pidx;
         if (++turn == kProducers) turn = 0;
@@ -582,11 +605,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           mbar_wait(bar_tempty, aph ^ 1u, 1);
           mbar_wait(bar_tempty + 8, aph ^ 1u, 4);
           tc_fence_after();
+          TLB_TRACE((t - cluster_id) / num_clusters, 0);
           int kb0, kb1;
           k_range(t, kb0, kb1);
           for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(bar_full + 8 * s, ph, 2);
             tc_fence_after();
+            if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
             if (elected) {
               const uint32_t a_lo = a_lo0 + s * a_step;
               const uint32_t b_lo = b_lo0 + s * b_step;
@@ -606,6 +631,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             __syncwarp();
             if (++s == stages) { s = 0; ph ^= 1u; }
           }
+          TLB_TRACE((t - cluster_id) / num_clusters, 2);
           aph ^= 1u;
         }
       }
@@ -646,6 +672,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         const int bi = (kNSub == 2) ? h : as;  // barrier / accumulator slot
         mbar_wait(bar_tfull + 8 * bi, aph, 3);
         tc_fence_after();
+        if ((ew & 3) == 0) TLB_TRACE((t - cluster_id) / num_clusters, 3 + 2 * h + (ew >> 2) * 4);
         const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
         const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
         if (rows_in_range) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
@@ -665,12 +692,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * bi);
           else mbar_arrive(bar_tempty + 8 * bi);
         }
+        if ((ew & 3) == 0) TLB_TRACE((t - cluster_id) / num_clusters, 4 + 2 * h + (ew >> 2) * 4);
       }
       if constexpr (kNSub == 2) { aph ^= 1u; } else if (++as == acc_stages) { as = 0; aph ^= 1u; }
     }
     // The staging slabs must have been read before the CTA's shared memory goes away; the writes themselves are
     // complete when the grid is.  Stores into peer GPUs' memory are waited for in full.
-    if (p.epi_tma && lane == 0) {
+    if (p.epi_tma && lane <= p.n_peer) {
       if (p.n_peer > 0) tma_store_wait_all<0>(); else tma_store_wait_read<0>();
     }
   }

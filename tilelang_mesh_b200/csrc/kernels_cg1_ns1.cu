@@ -1,0 +1,13 @@
+// Instantiations of gemm_tcgen05_kernel<1, *, 1, 1> (one translation unit per (cta_group, accumulators) pair).
+#include "kernel_table.h"
+
+namespace tlb200 {
+GemmKernelFn kernel_cg1_ns1(int kind) {
+  switch (kind) {
+    case kKindF8: return gemm_tcgen05_kernel<1, kKindF8, 1>;
+    case kKindTF32: return gemm_tcgen05_kernel<1, kKindTF32, 1>;
+    case kKindI8: return gemm_tcgen05_kernel<1, kKindI8, 1>;
+    default: return gemm_tcgen05_kernel<1, kKindF16, 1>;
+  }
+}
+}  // namespace tlb200

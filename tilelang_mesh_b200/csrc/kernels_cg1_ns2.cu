@@ -1,0 +1,13 @@
+// Instantiations of gemm_tcgen05_kernel<1, *, 2, 1> (one translation unit per (cta_group, accumulators) pair).
+#include "kernel_table.h"
+
+namespace tlb200 {
+GemmKernelFn kernel_cg1_ns2(int kind) {
+  switch (kind) {
+    case kKindF8: return gemm_tcgen05_kernel<1, kKindF8, 2>;
+    case kKindTF32: return gemm_tcgen05_kernel<1, kKindTF32, 2>;
+    case kKindI8: return gemm_tcgen05_kernel<1, kKindI8, 2>;
+    default: return gemm_tcgen05_kernel<1, kKindF16, 2>;
+  }
+}
+}  // namespace tlb200

@@ -14,8 +14,7 @@
 #include <cstring>
 #include <mutex>
 
-#include "gemm_blockscaled_sm100.cuh"
-#include "gemm_sm100.cuh"
+#include "kernel_table.h"
 
 namespace {
 
@@ -645,29 +644,11 @@ int launch_repitch(const void* src, long long ld_src, void* dst, long long ld_ds
   return 0;
 }
 
-typedef void (*GemmKernelFn)(const GemmKernelParams);
-template <int kCg, int kKind>
-GemmKernelFn pick_nsub(int n_sub) {
-  return n_sub == 2 ? gemm_tcgen05_kernel<kCg, kKind, 2> : gemm_tcgen05_kernel<kCg, kKind, 1>;
+GemmKernelFn pick_kernel(int cg, int kind, int n_sub) {
+  if (cg == 2) return n_sub == 2 ? kernel_cg2_ns2(kind) : kernel_cg2_ns1(kind);
+  return n_sub == 2 ? kernel_cg1_ns2(kind) : kernel_cg1_ns1(kind);
 }
-template <int kCg>
-GemmKernelFn pick_kind(int kind, int n_sub) {
-  switch (kind) {
-    case kKindF8: return pick_nsub<kCg, kKindF8>(n_sub);
-    case kKindTF32: return pick_nsub<kCg, kKindTF32>(n_sub);
-    case kKindI8: return pick_nsub<kCg, kKindI8>(n_sub);
-    default: return pick_nsub<kCg, kKindF16>(n_sub);
-  }
-}
-GemmKernelFn pick_kernel(int cg, int kind, int n_sub) { return cg == 2 ? pick_kind<2>(kind, n_sub) : pick_kind<1>(kind, n_sub); }
-GemmKernelFn pick_kernel_mc(int kind) {  // pairs, one accumulator per tile, A multicast across two pairs
-  switch (kind) {
-    case kKindF8: return gemm_tcgen05_kernel<2, kKindF8, 1, 2>;
-    case kKindTF32: return gemm_tcgen05_kernel<2, kKindTF32, 1, 2>;
-    case kKindI8: return gemm_tcgen05_kernel<2, kKindI8, 1, 2>;
-    default: return gemm_tcgen05_kernel<2, kKindF16, 1, 2>;
-  }
-}
+GemmKernelFn pick_kernel_mc(int kind) { return kernel_mc(kind); }
 std::array<const void*, 20> all_kernels() {
   std::array<const void*, 20> k;
   int i = 0;
@@ -678,11 +659,7 @@ std::array<const void*, 20> all_kernels() {
   return k;
 }
 
-typedef void (*BlockScaledFn)(const BlockScaledParams);
-BlockScaledFn pick_blockscaled(int cg, int bn) {
-  if (cg == 2) return bn == 128 ? gemm_blockscaled_kernel<2, 128> : gemm_blockscaled_kernel<2, 256>;
-  return bn == 128 ? gemm_blockscaled_kernel<1, 128> : gemm_blockscaled_kernel<1, 256>;
-}
+BlockScaledFn pick_blockscaled(int cg, int bn) { return kernel_blockscaled(cg, bn); }
 
 int out_kind_of(int dt) {
   switch (dt) {
@@ -979,6 +956,11 @@ int tlb200_init(int device) {
   return rc;
 }
 
+#ifdef TLB200_TRACE
+static long long* g_trace = nullptr;
+extern "C" void tlb200_debug_set_trace(long long* p) { g_trace = p; }
+#endif
+
 static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
                      void* stream_v, void* const* peers = nullptr, int n_peer = 0, const int32_t* group_rows = nullptr,
                      int n_groups = 0) {
@@ -1137,6 +1119,9 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.accumulate = (!split && (d->epilogue & TLB200_EPI_ACCUMULATE)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
   kp.l2_policy = d->reserved[2];
+#ifdef TLB200_TRACE
+  kp.trace = g_trace;
+#endif
 
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -1212,6 +1197,15 @@ int tlb200_gemm_bcast(const tlb200_gemm_desc* d, const void* a, const void* b, v
   }
   if (d && d->reserved[1] > 1) return fail("tlb200_gemm_bcast: split-K cannot be combined with multiple destinations");
   if (d && (d->epilogue & TLB200_EPI_ACCUMULATE)) return fail("tlb200_gemm_bcast: TLB200_EPI_ACCUMULATE is not offered with multiple destinations");
+  // Stores into peer memory drain at NVLink speed, so a tile's epilogue takes several times longer than on one GPU.
+  // A 512-wide tile fills TMEM (single-buffered accumulator) and would expose all of that to the tensor pipe: the
+  // automatic plan is therefore restricted to double-buffered tiles (<= 256 columns) when there are peer destinations.
+  tlb200_gemm_desc d1;
+  if (d && n_c > 1 && d->cfg_block_n == 0 && d->m > kBlockM && d->n >= 256 && dtype_bytes(d->ab_dtype) == 2) {
+    d1 = *d;
+    d1.cfg_block_n = 256;
+    d = &d1;
+  }
   return gemm_impl(d, a, b, c_list[0], nullptr, 0, stream_v, c_list + 1, n_c - 1);
 }
 

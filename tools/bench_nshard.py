@@ -11,8 +11,9 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 M = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
-N = K = 8192
+N = 8192
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 10
+K = int(sys.argv[3]) if len(sys.argv) > 3 else 8192  # a small K makes the stores (the NVLink side) the whole cost
 torch.manual_seed(0)
 A = torch.randn(M, K, device="cuda").bfloat16()
 lo, hi = rank * (N // world), (rank + 1) * (N // world)

@@ -1,0 +1,34 @@
+"""Per-tile timeline of CTA 0 from a -DTLB200_TRACE build of the library (clock64 stamps, cycles):
+  TLB200_LIB=tools/_ab/libtlb200_trace.so python tools/trace_tiles.py [m n k] [fp8]
+Build: nvcc ... -DTLB200_TRACE -o tools/_ab/libtlb200_trace.so tilelang_mesh_b200/csrc/tlb200.cu"""
+import ctypes, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from tilelang_mesh_b200 import _abi, gemm as G
+args = [a for a in sys.argv[1:] if a.isdigit()]
+m, n, k = (int(x) for x in args[:3]) if len(args) >= 3 else (8192, 8192, 8192)
+dt = torch.float8_e4m3fn if "fp8" in sys.argv else torch.bfloat16
+cfg = {}
+for a in sys.argv[1:]:
+    if "=" in a:
+        kk, v = a.split("="); cfg[kk] = int(v)
+lib = _abi.load()
+lib.tlb200_debug_set_trace.argtypes = [ctypes.c_void_p]
+a = torch.randn(m, k, device="cuda").to(dt); b = torch.randn(n, k, device="cuda").to(dt)
+c = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+tr = torch.zeros(256 * 16, dtype=torch.int64, device="cuda")
+for _ in range(3): G.gemm(a, b, c, **cfg)
+torch.cuda.synchronize()
+lib.tlb200_debug_set_trace(tr.data_ptr())
+G.gemm(a, b, c, **cfg)
+torch.cuda.synchronize()
+lib.tlb200_debug_set_trace(None)
+t = tr.cpu().view(-1, 16)
+print("plan", G.plan_for(a, b, c, **cfg))
+rows = [r for r in t.tolist() if r[2] != 0]
+t0 = rows[0][0]
+print("tile | acc free->1st kb | mainloop (1st kb->last commit) | commit->epi0 sees full | epi0 acc0 drain | epi0 acc1 wait | acc1 drain | epi4: acc0 drain, acc1 drain | last drain -> next tile's MMA holds acc | producer lead (1st issue before acc free)")
+for i, r in enumerate(rows):
+    nxt = rows[i + 1][0] if i + 1 < len(rows) else 0
+    last_done = max(r[6], r[10])
+    print(f"{i:3d} | {r[1]-r[0]:6d} | {r[2]-r[1]:7d} | {r[3]-r[2]:6d} | {r[4]-r[3]:6d} | {r[5]-r[4]:6d} | {r[6]-r[5]:6d} | {r[8]-r[7]:6d} {r[10]-r[9]:6d} | {(nxt-last_done) if nxt else 0:6d} | {r[0]-r[11]:7d}   exposed(commit->next acc free) {(nxt - r[2]) if nxt else 0}")
