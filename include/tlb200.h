@@ -89,7 +89,8 @@ typedef struct tlb200_gemm_desc {
   int32_t cfg_block_n;   /* 0 auto, else a multiple of 32 in [32,256] or of 64 in (256,512] */
   int32_t cfg_stages;    /* 0 auto */
   int32_t cfg_raster;    /* 0 auto, else tile-rows per L2 raster group */
-  int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores, 2 = smem + TMA store */
+  int32_t cfg_epilogue;  /* 0 auto, 1 = direct global stores from registers, 2 = swizzled smem slab + TMA store,
+                            3 = swizzled smem slab + coalesced st.global (full 128-byte lines, no TMA store) */
   int32_t reserved[3];   /* [0] = cfg_epi_warps: 0 auto, 4 or 8 epilogue warps;
                           * [1] = cfg_split_k: 0 auto, 1 off (no split-K, no tail split), n = at most n K slices,
                           *       -1 = no split-K but force the tail split (both need a workspace);

@@ -55,14 +55,6 @@ struct alignas(64) BlockScaledParams {
   int l2_policy;
 };
 
-template <int kRegs>
-__device__ __forceinline__ void setmaxnreg_inc() {
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
-}
-template <int kRegs>
-__device__ __forceinline__ void setmaxnreg_dec() {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
-}
 
 // Two independent IEEE fp32 fmas in one instruction (fma.rn.f32x2, sm_100): {d0, d1} += {x0, x1} * {s, s}.
 // Same results as two fmaf; half the issue slots of the promotion loop.

@@ -37,7 +37,7 @@ constexpr int kUmmaKBytes = 32;       // K bytes consumed by one tcgen05.mma
 constexpr int kMaxThreads = 384;      // 4 control warps + up to 8 epilogue warps
 constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple of 4)
 constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
-constexpr int kEpiSlabs = 8;               // slabs per CTA: 4 warps x 2 or 8 warps x 1 (32 KiB)
+constexpr int kEpiSlabs = 8;               // staging slabs per CTA by default: 4 warps x 2 or 8 warps x 1 (32 KiB); 16 = 8 warps x 2
 constexpr int kMaxStages = 12;
 constexpr int kMaxGroups = 64;   // grouped GEMM: row groups of A/C, each with its own B
 constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
@@ -79,6 +79,7 @@ struct alignas(64) GemmKernelParams {
   int n_sub;             // accumulators per tile (1, or 2 for 512-wide tiles sharing the A stage)
   int acc_stages;        // 2 = double-buffered accumulator (block_n <= 256), 1 = the tile fills TMEM
   int epi_warps;         // 4 or 8
+  int epi_slabs;         // staging slabs per CTA: 8, or 16 (two per warp with 8 epilogue warps)
   int stages;
   int k_elems_per_block;  // 128 / sizeof(ab)
   int a_mn_major, b_mn_major;
@@ -93,6 +94,7 @@ struct alignas(64) GemmKernelParams {
   int out_kind;
   int acc_int;  // accumulators hold int32 (int8 operands)
   int epi_tma;
+  int epi_lsu;  // with epi_tma: slabs leave shared memory through coalesced st.global (no TMA store)
   int relu;
   int accumulate;  // C = C_in + alpha * acc (predicated-store epilogue only)
   int l2_policy;
@@ -193,17 +195,29 @@ __device__ __forceinline__ float load_out(const void* c, long long idx) {
   }
 }
 
-// One accumulator element -> the value to be cast: alpha, relu; int32 accumulators (int8 operands) are
-// converted to float unless the output is int32 too, in which case the raw integer bits are carried.
-template <int kOut>
-__device__ __forceinline__ float epi_value(uint32_t raw, float alpha, bool relu, bool acc_int) {
+// 32 accumulator elements (one tcgen05.ld) -> the values to be cast: alpha, relu.  Kept to ONE instruction per
+// element on the ordinary path (an FMUL): two epilogue warps share a scheduler and every instruction here is
+// issued 32-64 times per slab, so a per-element select between integer and float accumulators or a per-element
+// relu test made the drain of a 128 x 256 accumulator issue-bound (4.5k cycles, profiles/r2_notes.md).  kAccInt is
+// a property of the kernel instantiation (int8 operands); relu is a warp-uniform branch around a second pass.
+// int32 accumulators are converted to float unless the output is int32 too: then the raw integer bits are carried.
+template <int kOut, bool kAccInt>
+__device__ __forceinline__ void epi_values(const uint32_t (&raw)[32], float (&v)[32], float alpha, bool relu) {
   if constexpr (kOut == kOutI32) {
-    int xi = static_cast<int>(raw);
-    if (relu) xi = max(xi, 0);
-    return __int_as_float(xi);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = __int_as_float(max(__float_as_int(v[i]), 0));
+    }
   } else {
-    float x = (acc_int ? static_cast<float>(static_cast<int>(raw)) : __uint_as_float(raw)) * alpha;
-    return relu ? fmaxf(x, 0.f) : x;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      v[i] = (kAccInt ? static_cast<float>(static_cast<int>(raw[i])) : __uint_as_float(raw[i])) * alpha;
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+    }
   }
 }
 
@@ -216,16 +230,115 @@ struct EpiOut {
   int n;                  // columns of the destination matrix (stores are clipped to it)
   float alpha;
   int relu, accumulate, tma, n_peer;
+  int lsu;                // staged slabs leave shared memory through coalesced st.global instead of a TMA store
   int evict_first;        // C is write-once: keep it from displacing the operands in L2
+  int trace_seq;          // development builds: tile sequence number for TLB_TRACE, -1 = do not trace this call
 };
+#ifdef TLB200_TRACE
+#define TLB_TRACE_EPI(slot) do { if (o.trace_seq >= 0 && cs == cbeg + kColsPerSlab) TLB_TRACE(o.trace_seq, slot); } while (0)
+#else
+#define TLB_TRACE_EPI(slot) do { } while (0)
+#endif
 
 // ---------------------------------------------------------------- epilogue for one tile
-// Executed by the 4 epilogue warps.  Warp `q` owns TMEM lanes / tile rows [32q, 32q+32).
-// tmem_acc = TMEM address of the accumulator (lane 0, first column).
+// What one epilogue warp needs to drain its share of an accumulator (always inlined: a context passed by reference).
+struct EpiCtx {
+  const GemmKernelParams& p;
+  const EpiOut& o;
+  uint32_t lane_taddr;  // TMEM address of this warp's lane quarter, column 0 of the accumulator
+  int q, lane, row0, row_limit, row_off, col0;
+  uint32_t stage_smem;
+  int nslabs;
+};
+
+// registers -> swizzled slab -> global (TMA store, or coalesced st.global)
 template <int kOut>
+__device__ __forceinline__ void epi_stage(const EpiCtx& e, int cs, const uint4 (&w)[8], int& slab_iter) {
+  constexpr int kOB = OutTraits<kOut>::kBytes;
+  const EpiOut& o = e.o;
+  const int lane = e.lane;
+  const uint32_t slab = e.stage_smem + (e.nslabs == 2 ? (slab_iter & 1) : 0) * kEpiBufBytes;
+  const int first_row = e.row0 + e.q * 32;
+  if (!o.lsu) {  // the TMA stores that last read this slab must have drained it
+    // (bulk groups are per thread: every lane that issues stores waits for its own)
+    if (lane <= o.n_peer) {
+      if (e.nslabs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int chunk = 0; chunk < 8; ++chunk) {  // 16 B chunk index in the 128 B row
+    const uint32_t addr = slab + lane * 128 + ((chunk ^ (lane & 7)) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[chunk].x), "r"(w[chunk].y),
+                 "r"(w[chunk].z), "r"(w[chunk].w)
+                 : "memory");
+  }
+  if (o.lsu) {
+    // Coalesced read-back: every instruction moves 4 rows x 128 B (8 lanes x 16 B per row), so each row segment
+    // reaches L2 as one full 128-byte line, and no asynchronous agent reads the slab.  Measured equal to the TMA
+    // store on one GPU (profiles/r2_notes.md); kept as cfg_epilogue = 3.
+    __syncwarp();
+    const int rsub = lane >> 3, chunk = lane & 7;
+    const long long row_bytes = o.ldc * kOB;
+    const long long col_byte = static_cast<long long>(e.col0 + cs) * kOB + chunk * 16;
+    const bool col_ok = col_byte < static_cast<long long>(o.n) * kOB;  // the row length is a multiple of 16 bytes
+    char* gptr = reinterpret_cast<char*>(o.c) + static_cast<long long>(e.row_off + first_row + rsub) * row_bytes + col_byte;
+    uint4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int row = j * 4 + rsub;
+      const uint32_t addr = slab + row * 128 + ((chunk ^ (row & 7)) << 4);
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "r"(addr) : "memory");
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (col_ok && first_row + j * 4 + rsub < e.row_limit)
+        asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(gptr + static_cast<long long>(j) * 4 * row_bytes),
+                     "r"(v[j].x), "r"(v[j].y), "r"(v[j].z), "r"(v[j].w) : "memory");
+    }
+    __syncwarp();  // the slab may be rewritten once every lane has its data in registers
+    ++slab_iter;
+    return;
+  }
+  fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+  __syncwarp();
+  if (o.n_peer == 0) {
+    if (lane == 0) {
+      if (first_row < e.row_limit) {
+        // C is write-once: evict_first keeps the operands in L2
+        if (o.evict_first) tma_store_2d_hint(o.tm, slab, e.col0 + cs, e.row_off + first_row, policy_evict_first());
+        else tma_store_2d(o.tm, slab, e.col0 + cs, e.row_off + first_row);
+      }
+      tma_store_commit();
+    }
+  } else if (lane <= o.n_peer) {
+    // Fused all-gather: the same slab goes into the local C and straight into every peer GPU's C over NVLink.
+    // One lane per destination issues (and later waits for) its own store, so the up-to-8 stores of a slab enter
+    // the TMA queue together instead of one after another from a single thread; the lane -> destination map is
+    // rotated per CTA and slab so that the CTAs of a wave do not all address the same peer at the same moment.
+    if (first_row < e.row_limit) {
+      const int dst = (lane + static_cast<int>(blockIdx.x) + slab_iter) % (o.n_peer + 1);  // n_peer = the local C
+      if (dst == o.n_peer) tma_store_2d_hint(o.tm, slab, e.col0 + cs, e.row_off + first_row, policy_evict_first());
+      else tma_store_2d(&e.p.tm_c_peer[dst], slab, e.col0 + cs, e.row_off + first_row);
+    }
+    tma_store_commit();
+  }
+  ++slab_iter;
+}
+
+// Executed by the epilogue warps.  Warp `q` owns TMEM lanes / tile rows [32q, 32q+32) and the accumulator
+// columns [cbeg, cend).  tmem_acc = TMEM address of the accumulator (lane 0, first column).
+//
+// The accumulator goes back to the MMA warp the moment this warp's LAST tcgen05.ld of it has completed: what
+// follows for that last slab (cast, wait for the TMA engine to have read the staging slab, st.shared, proxy fence,
+// TMA store) works from registers while the tensor pipe is already on the next tile.  Before this the accumulator
+// was held until the last store had been issued - 4.5k cycles per 128 x 256 accumulator, all of them exposed for a
+// tile that fills TMEM (profiles/r2_notes.md).
+template <int kOut, bool kAccInt>
 __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const EpiOut& o, uint32_t tmem_acc, int q,
                                               int lane, int row0, int row_limit, int row_off, int col0, int cbeg, int cend,
-                                              uint32_t stage_smem, int nslabs, int& slab_iter) {
+                                              uint32_t stage_smem, int nslabs, int& slab_iter, uint32_t tempty_bar,
+                                              bool tempty_remote) {
   constexpr int kOB = OutTraits<kOut>::kBytes;
   constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
   constexpr int kPacketsPerLd = 32 * kOB / 16;  // 16 B packets produced by one x32 load
@@ -234,95 +347,63 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
   const uint32_t lane_taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
   const float alpha = o.alpha;
   const bool relu = o.relu != 0;
-  const bool acc_int = p.acc_int != 0;
+  // All tcgen05.ld of this warp have completed (wait::ld): hand the accumulator back.
+  auto release_accumulator = [&]() {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) {
+      if (tempty_remote) mbar_arrive_cluster(tempty_bar);
+      else mbar_arrive(tempty_bar);
+    }
+  };
 
   // A TMA store writes the warp's whole 32-row slab: use it only when all 32 rows belong to this tile's
   // row range (always true for an ordinary GEMM, where the tensor map clips at M; a grouped GEMM's last
   // row tile of a group falls back to predicated stores).
   const bool slab_rows_ok = p.n_groups == 0 || row0 + q * 32 + 32 <= row_limit;
   if (o.tma && slab_rows_ok) {
-    // Per 128-byte-wide slab: TMEM loads (two x32 loads in flight) and the cast run BEFORE waiting
-    // for the TMA store that last read the slab, so that store's smem read is hidden behind them.
+    const EpiCtx e{p, o, lane_taddr, q, lane, row0, row_limit, row_off, col0, stage_smem, nslabs};
+    // slabs of this warp that hold at least one column of C (warp-uniform)
+    int nsl = 0;
+    for (int cs = cbeg; cs < cend && col0 + cs < o.n; cs += kColsPerSlab) ++nsl;
+    if (nsl == 0) release_accumulator();
     constexpr int kLdsPerSlab = kColsPerSlab / 32;
-    constexpr int kPair = kLdsPerSlab >= 2 ? 2 : 1;
-    for (int cs = cbeg; cs < cend; cs += kColsPerSlab) {
-      if (col0 + cs >= o.n) break;  // warp-uniform: remaining slabs are fully out of range
-      const uint32_t slab = stage_smem + (nslabs == 2 ? (slab_iter & 1) : 0) * kEpiBufBytes;
-      bool slab_free = false;
+    constexpr int kPair = kLdsPerSlab >= 2 ? 2 : 1;  // x32 loads in flight
+    for (int i = 0; i < nsl; ++i) {
+      const int cs = cbeg + i * kColsPerSlab;
+      uint4 w[8];
 #pragma unroll
       for (int l0 = 0; l0 < kLdsPerSlab; l0 += kPair) {
-        if (cs + l0 * 32 < cend) {
-          uint32_t r[kPair][32];
-          tmem_ld_32x32(lane_taddr + cs + l0 * 32, r[0]);
-          if constexpr (kPair == 2) tmem_ld_32x32(lane_taddr + cs + (l0 + 1) * 32, r[1]);
-          tmem_ld_wait();
-          uint4 w[kPair * kPacketsPerLd];
+        uint32_t r[kPair][32];
+        tmem_ld_32x32(lane_taddr + cs + l0 * 32, r[0]);
+        if constexpr (kPair == 2) tmem_ld_32x32(lane_taddr + cs + (l0 + 1) * 32, r[1]);
+        tmem_ld_wait();
+        if (l0 + kPair >= kLdsPerSlab && i + 1 == nsl) release_accumulator();  // that was the last read
 #pragma unroll
-          for (int h = 0; h < kPair; ++h) {
-            float v[32];
+        for (int h = 0; h < kPair; ++h) {
+          float v[32];
+          epi_values<kOut, kAccInt>(r[h], v, alpha, relu);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              v[i] = epi_value<kOut>(r[h][i], alpha, relu, acc_int);
-            }
-#pragma unroll
-            for (int pk = 0; pk < kPacketsPerLd; ++pk) w[h * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
-          }
-          if (!slab_free) {  // the TMA stores that last read this slab must have drained it
-            // (bulk groups are per thread: every lane that issues stores waits for its own)
-            if (lane <= o.n_peer) {
-              if (nslabs == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>();
-            }
-            __syncwarp();
-            slab_free = true;
-          }
-#pragma unroll
-          for (int pk = 0; pk < kPair * kPacketsPerLd; ++pk) {
-            const int chunk = l0 * kPacketsPerLd + pk;  // 16 B chunk index in the 128 B row
-            const uint32_t addr = slab + lane * 128 + ((chunk ^ (lane & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[pk].x), "r"(w[pk].y),
-                         "r"(w[pk].z), "r"(w[pk].w)
-                         : "memory");
-          }
+          for (int pk = 0; pk < kPacketsPerLd; ++pk) w[(l0 + h) * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
         }
       }
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
-      __syncwarp();
-      if (o.n_peer == 0) {
-        if (lane == 0) {
-          if (row0 + q * 32 < row_limit) {
-            // C is write-once: evict_first keeps the operands in L2
-            if (o.evict_first) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
-            else tma_store_2d(o.tm, slab, col0 + cs, row_off + row0 + q * 32);
-          }
-          tma_store_commit();
-        }
-      } else if (lane <= o.n_peer) {
-        // Fused all-gather: the same slab goes into the local C and straight into every peer GPU's C over NVLink.
-        // One lane per destination issues (and later waits for) its own store, so the up-to-8 stores of a slab enter
-        // the TMA queue together instead of one after another from a single thread; the lane -> destination map is
-        // rotated per CTA and slab so that the CTAs of a wave do not all address the same peer at the same moment.
-        if (row0 + q * 32 < row_limit) {
-          const int dst = (lane + static_cast<int>(blockIdx.x) + slab_iter) % (o.n_peer + 1);  // n_peer = the local C
-          if (dst == o.n_peer) tma_store_2d_hint(o.tm, slab, col0 + cs, row_off + row0 + q * 32, policy_evict_first());
-          else tma_store_2d(&p.tm_c_peer[dst], slab, col0 + cs, row_off + row0 + q * 32);
-        }
-        tma_store_commit();
-      }
-      ++slab_iter;
+      epi_stage<kOut>(e, cs, w, slab_iter);
     }
   } else {
     const bool row_ok = grow < row_limit;
     const bool vec_ok = ((o.ldc * kOB) % 16 == 0) && ((reinterpret_cast<uintptr_t>(o.c) % 16) == 0);
+    bool released = false;
     for (int cs = cbeg; cs < cend; cs += 32) {
       if (col0 + cs >= o.n) break;
       uint32_t r[32];
       tmem_ld_32x32(lane_taddr + cs, r);
       tmem_ld_wait();
-      float v[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        v[i] = epi_value<kOut>(r[i], alpha, relu, acc_int);
+      if (cs + 32 >= cend || col0 + cs + 32 >= o.n) {  // that was the last read of this accumulator
+        release_accumulator();
+        released = true;
       }
+      float v[32];
+      epi_values<kOut, kAccInt>(r, v, alpha, relu);
       if (row_ok) {
         const int gcol = col0 + cs;
         const long long base = static_cast<long long>(grow + row_off) * o.ldc + gcol;
@@ -346,6 +427,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
       }
       __syncwarp();  // tcgen05.ld is .sync.aligned: re-converge after the predicated stores
     }
+    if (!released) release_accumulator();
   }
 }
 
@@ -386,7 +468,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t smem_a = smem_base;
   const uint32_t smem_b = smem_a + stages * kABytesPerStage;
   const uint32_t smem_epi = smem_b + stages * b_stage_bytes;
-  const uint32_t smem_bar = smem_epi + kEpiSlabs * kEpiBufBytes;
+  const uint32_t smem_bar = smem_epi + p.epi_slabs * kEpiBufBytes;
   const uint32_t bar_full = smem_bar;                    // [stages]
   const uint32_t bar_empty = bar_full + 8 * stages;      // [stages]
   const uint32_t bar_tfull = bar_empty + 8 * stages;     // [2]
@@ -597,10 +679,22 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           if (++as == acc_stages) { as = 0; aph ^= 1u; }
         }
       } else {
-        // Two accumulators per tile sharing every A stage (they fill TMEM, so there is no second
-        // buffer: the epilogue of a tile is exposed).  tmem_full/empty[h] belong to accumulator h; the
-        // epilogue hands accumulator 0 back first.  (Letting accumulator 0 of the next tile run ahead
-        // while accumulator 1 drains was measured: no gain on a power-capped part — profiles/r1_notes.md.)
+        // Two accumulators per tile sharing every A stage (they fill TMEM, so there is no second buffer: what the
+        // epilogue cannot hide is exposed).  tmem_full/empty[h] belong to accumulator h.  The K blocks are issued
+        // interleaved (both accumulators consume a stage, then it is released) except for the LAST `tail` blocks, all
+        // of which are resident at once: there accumulator 0 runs through all of them first and is published, then
+        // accumulator 1 - so the epilogue drains accumulator 0 while the tensor pipe still works on accumulator 1
+        // (2048 cycles for four stages) instead of after it.
+        auto mma_half = [&](int stage, uint32_t d_tmem, uint32_t b_extra, bool first_kb) {
+          const uint32_t a_lo = a_lo0 + stage * a_step;
+          const uint32_t b_lo = b_lo0 + stage * b_step + b_extra;
+#pragma unroll
+          for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
+            const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
+            const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
+            umma_ss<kCta, kKind>(d_tmem, da, db, idesc, (first_kb && k == 0) ? 0u : 1u);
+          }
+        };
         for (int t = cluster_id; t < num_tiles; t += num_clusters) {
           mbar_wait(bar_tempty, aph ^ 1u, 1);
           mbar_wait(bar_tempty + 8, aph ^ 1u, 4);
@@ -608,7 +702,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           TLB_TRACE((t - cluster_id) / num_clusters, 0);
           int kb0, kb1;
           k_range(t, kb0, kb1);
-          for (int kb = kb0; kb < kb1; ++kb) {
+          const int tail = min(stages, kb1 - kb0);
+          for (int kb = kb0; kb < kb1 - tail; ++kb) {
             mbar_wait(bar_full + 8 * s, ph, 2);
             tc_fence_after();
             if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
@@ -623,10 +718,31 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
                 umma_ss<kCta, kKind>(tmem_base + umma_n, da, hi_b | ((b_lo + b_sub + k * kadv_b) & 0x3FFFu), idesc, acc);
               }
               umma_commit<kCta>(bar_empty + 8 * s);
-              if (kb + 1 == kb1) {
-                umma_commit<kCta>(bar_tfull);
-                umma_commit<kCta>(bar_tfull + 8);
-              }
+            }
+            __syncwarp();
+            if (++s == stages) { s = 0; ph ^= 1u; }
+          }
+          // tail, accumulator 0: every remaining stage (no stage is released yet)
+          {
+            int s1 = s;
+            uint32_t ph1 = ph;
+            for (int kb = kb1 - tail; kb < kb1; ++kb) {
+              mbar_wait(bar_full + 8 * s1, ph1, 2);
+              tc_fence_after();
+              if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
+              if (elected) mma_half(s1, tmem_base, 0u, kb == kb0);
+              __syncwarp();
+              if (++s1 == stages) { s1 = 0; ph1 ^= 1u; }
+            }
+            if (elected) umma_commit<kCta>(bar_tfull);
+            __syncwarp();
+          }
+          // tail, accumulator 1: the same stages again (their barriers have been observed), releasing each
+          for (int kb = kb1 - tail; kb < kb1; ++kb) {
+            if (elected) {
+              mma_half(s, tmem_base + umma_n, b_sub, kb == kb0);
+              umma_commit<kCta>(bar_empty + 8 * s);
+              if (kb + 1 == kb1) umma_commit<kCta>(bar_tfull + 8);
             }
             __syncwarp();
             if (++s == stages) { s = 0; ph ^= 1u; }
@@ -641,7 +757,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const int ew = warp - kEpiWarp0;
     const int q = ew & 3;            // == warp % 4: the TMEM lane quarter this warp may read
     const int chalf = ew >> 2;       // with 8 epilogue warps: which half of the tile's columns
-    const int nslabs = kEpiSlabs / p.epi_warps;  // 2 or 1 staging slabs per warp
+    const int nslabs = p.epi_slabs / p.epi_warps;  // 2 or 1 staging slabs per warp
     const uint32_t my_stage = smem_epi + ew * nslabs * kEpiBufBytes;
     const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, leader_rank) : bar_tempty;
     // Column range of this warp inside ONE accumulator (all warps drain accumulator 0, then 1).
@@ -662,10 +778,10 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       const int row_off = (tail_mode ? 0 : t / tiles_mn) * p.split_row_pitch;
       if (tail_item) row_limit = 0x7fffffff;
       // partial sums of a tail slice go to the workspace raw; everything else is the final C
-      const EpiOut o{tail_item ? &p.tm_ws : &p.tm_c, tail_item ? p.ws : p.c, tail_item ? (long long)p.block_n : p.ldc,
+      EpiOut o{tail_item ? &p.tm_ws : &p.tm_c, tail_item ? p.ws : p.c, tail_item ? (long long)p.block_n : p.ldc,
                      tail_item ? p.block_n : p.n, tail_item ? 1.0f : p.alpha, tail_item ? 0 : p.relu,
                      tail_item ? 0 : p.accumulate, tail_item ? 1 : p.epi_tma, tail_item ? 0 : p.n_peer,
-                     (!tail_item && p.l2_policy != 1) ? 1 : 0};
+                     tail_item ? 0 : p.epi_lsu, (!tail_item && p.l2_policy != 1) ? 1 : 0, -1};
       const int out_kind = tail_item ? static_cast<int>(kOutF32) : p.out_kind;
 #pragma unroll
       for (int h = 0; h < kNSub; ++h) {
@@ -674,23 +790,42 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         tc_fence_after();
         if ((ew & 3) == 0) TLB_TRACE((t - cluster_id) / num_clusters, 3 + 2 * h + (ew >> 2) * 4);
         const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
+#ifdef TLB200_TRACE
+        o.trace_seq = (ew == 0 && h == 0) ? (t - cluster_id) / num_clusters : -1;
+#endif
         const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
-        if (rows_in_range) {  // warp-uniform; a fully out-of-range half-tile has nothing to store
-          switch (out_kind) {
-            case kOutBF16: epilogue_tile<kOutBF16>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF16: epilogue_tile<kOutF16>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutF32: epilogue_tile<kOutF32>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutE4M3: epilogue_tile<kOutE4M3>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            case kOutI32: epilogue_tile<kOutI32>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
-            default: epilogue_tile<kOutE5M2>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter); break;
+        // Nothing to read (a fully out-of-range half-tile, or an output type this instantiation cannot produce - the
+        // host rejects those): hand the accumulator straight back.  Otherwise epilogue_tile does so itself, as soon as
+        // its last tcgen05.ld has completed.
+        auto release_unread = [&]() {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * bi);
+            else mbar_arrive(bar_tempty + 8 * bi);
           }
-        }
-        // All tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back.
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * bi);
-          else mbar_arrive(bar_tempty + 8 * bi);
+        };
+        if (rows_in_range) {  // warp-uniform
+          constexpr bool kAccInt = kKind == kKindI8;  // int8 operands accumulate in int32
+#define TLB_EPI(K) epilogue_tile<K, kAccInt>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter, \
+                                             (kCta == 2 ? tempty_leader : bar_tempty) + 8 * bi, kCta == 2)
+          switch (out_kind) {
+            case kOutBF16: TLB_EPI(kOutBF16); break;
+            case kOutF16: TLB_EPI(kOutF16); break;
+            case kOutF32: TLB_EPI(kOutF32); break;
+            case kOutI32:
+              if constexpr (kAccInt) TLB_EPI(kOutI32); else release_unread();  // int32 output exists for int8 operands only
+              break;
+            case kOutE4M3:
+              if constexpr (!kAccInt) TLB_EPI(kOutE4M3); else release_unread();
+              break;
+            default:
+              if constexpr (!kAccInt) TLB_EPI(kOutE5M2); else release_unread();
+              break;
+          }
+#undef TLB_EPI
+        } else {
+          release_unread();
         }
         if ((ew & 3) == 0) TLB_TRACE((t - cluster_id) / num_clusters, 4 + 2 * h + (ew >> 2) * 4);
       }
@@ -698,7 +833,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     }
     // The staging slabs must have been read before the CTA's shared memory goes away; the writes themselves are
     // complete when the grid is.  Stores into peer GPUs' memory are waited for in full.
-    if (p.epi_tma && lane <= p.n_peer) {
+    if (p.epi_tma && (!p.epi_lsu || tail_mode) && lane <= p.n_peer) {
       if (p.n_peer > 0) tma_store_wait_all<0>(); else tma_store_wait_read<0>();
     }
   }

@@ -59,9 +59,13 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Arrive on a barrier addressed in the shared::cluster window (possibly another CTA's).
+// Arrive on a barrier addressed in the shared::cluster window (possibly another CTA's).  Relaxed: the barriers this
+// is used for hand back TENSOR memory whose reads have already completed (tcgen05.wait::ld) and are ordered by
+// tcgen05.fence::before_thread_sync; no global or shared memory is published.  The .release.cluster form compiles to
+// MEMBAR.ALL.GPU + ERRBAR, which also waits for every TMA store the thread has in flight: ~1.8k cycles per
+// accumulator hand-back in the epilogue (profiles/r2_notes.md).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar)
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar)
                : "memory");
 }
 __device__ __forceinline__ uint32_t mapa(uint32_t smem_addr, uint32_t cta_rank) {
@@ -130,6 +134,18 @@ __device__ __forceinline__ void tc_fence_after() {
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
                    : "memory");
+}
+
+// ----------------------------------------------------------------------------- register budget per warpgroup
+// setmaxnreg moves registers between the warpgroups (4 consecutive warps) of a CTA: the control warpgroup gives
+// most of its share away, the epilogue warpgroups take it.  Every warp of a warpgroup must execute the same one.
+template <int kRegs>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+template <int kRegs>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
 }
 
 // ----------------------------------------------------------------------------- programmatic dependent launch

@@ -61,7 +61,8 @@ struct HostPipe {
 HostPipe g_pipe[kMaxDevices];
 
 constexpr int kSmemLimit = 232448;  // 227 KiB opt-in per block on sm_100
-constexpr int kSmemFixed = 1024 /*alignment slack*/ + kEpiSlabs * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16;
+constexpr int smem_fixed(int epi_slabs) { return 1024 /*alignment slack*/ + epi_slabs * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16; }
+constexpr int kSmemFixed = smem_fixed(kEpiSlabs);
 
 int dtype_bytes(int dt) {
   switch (dt) {
@@ -142,11 +143,11 @@ struct Resolved {
   int es, ob;             // operand / output element bytes
   int span;               // elements per 128 B of an operand row
   bool a_mn, b_mn;
-  int n_sub, umma_n, acc_stages, epi_warps;
+  int n_sub, umma_n, acc_stages, epi_warps, epi_slabs;
   int mc;                 // 2 = clusters of two pairs sharing every A box by TMA multicast, else 1
   int b_rows_per_cta;
   int num_k_blocks;
-  bool epi_tma;
+  bool epi_tma, epi_lsu;
   // split-K: the main kernel writes fp32 partial tiles into a workspace, a second kernel reduces
   int split_k, kb_per_split, m_pad;
   long long ws_ld, ws_bytes;  // ws_bytes = aligned operand copies + split-K partial sums
@@ -179,6 +180,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     return fail("tlb200: unsupported operand dtype %d (float16, bfloat16, float8_e4m3, float8_e5m2)", d->ab_dtype);
   if (dtype_bytes(d->c_dtype) == 0 || d->c_dtype == TLB200_INT8) return fail("tlb200: unsupported output dtype %d", d->c_dtype);
   if (d->c_dtype == TLB200_INT32 && d->ab_dtype != TLB200_INT8) return fail("tlb200: int32 output needs int8 operands");
+  if (d->ab_dtype == TLB200_INT8 && (d->c_dtype == TLB200_FLOAT8_E4M3 || d->c_dtype == TLB200_FLOAT8_E5M2))
+    return fail("tlb200: int8 operands produce int32, float32, float16 or bfloat16 output (not fp8)");
   if (d->c_dtype == TLB200_INT32 && d->alpha != 1.0f) return fail("tlb200: int32 output cannot be scaled (alpha must be 1)");
   r->es = dtype_bytes(d->ab_dtype);
   r->ob = dtype_bytes(d->c_dtype);
@@ -319,7 +322,14 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   r->b_rows_per_cta = r->umma_n / cg;
   const int per_stage = kABytesPerStage + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
   int stages = d->cfg_stages;
-  const int max_stages = (kSmemLimit - kSmemFixed) / per_stage;
+  // Eight epilogue warps get two staging slabs each (so a slab can be refilled while the TMA store of the previous
+  // one is still reading it) whenever at least three pipeline stages still fit, or the stage count the caller asked for.
+  r->epi_slabs = kEpiSlabs;
+  if (ew == 8) {
+    const int fit16 = (kSmemLimit - smem_fixed(16)) / per_stage;
+    if (stages == 0 ? fit16 >= 3 : stages <= fit16) r->epi_slabs = 16;
+  }
+  const int max_stages = (kSmemLimit - smem_fixed(r->epi_slabs)) / per_stage;
   if (stages == 0) stages = max_stages < kMaxStages ? max_stages : kMaxStages;
   if (stages < 2 || stages > kMaxStages || stages > max_stages)
     return fail("tlb200: cfg_stages=%d out of range [2,%d]", stages, max_stages < kMaxStages ? max_stages : kMaxStages);
@@ -390,14 +400,14 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.grid = static_cast<int>(clusters) * cg * mc;
   p.multicast = mc;
   p.threads = 128 + 32 * r->epi_warps;
-  p.smem_bytes = kSmemFixed + stages * per_stage;
+  p.smem_bytes = smem_fixed(r->epi_slabs) + stages * per_stage;
   p.raster = d->cfg_raster > 0 ? d->cfg_raster : ((bn > 256 || r->es == 1) ? 16 : 16 / cg);
   int epi = d->cfg_epilogue;
   const bool accumulate = (d->epilogue & TLB200_EPI_ACCUMULATE) != 0;
   if (accumulate) {
     if (d->epilogue & TLB200_EPI_RELU) return fail("tlb200: TLB200_EPI_ACCUMULATE cannot be combined with TLB200_EPI_RELU");
     if (d->c_dtype == TLB200_INT32) return fail("tlb200: TLB200_EPI_ACCUMULATE is not offered for int32 output");
-    if (epi == 2) return fail("tlb200: TLB200_EPI_ACCUMULATE uses the predicated-store epilogue (cfg_epilogue 0 or 1)");
+    if (epi >= 2) return fail("tlb200: TLB200_EPI_ACCUMULATE uses the predicated-store epilogue (cfg_epilogue 0 or 1)");
     epi = 1;
   }
   // A TMA store clips at the tensor's last column only in whole 16-byte units (measured: tools/pad_probe.py), so a
@@ -408,12 +418,13 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
   const bool slab_ok = (r->umma_n / (r->epi_warps / 4)) % (128 / r->ob) == 0;
   if (epi == 0) epi = (tma_ok && slab_ok) ? 2 : 1;
-  if (epi == 2 && !tma_ok) return fail("tlb200: TMA-store epilogue needs a 16-byte aligned C, row pitch and row length (n * element size)");
-  if (epi == 2 && !slab_ok)
-    return fail("tlb200: TMA-store epilogue needs block_n (%d) to be a multiple of %d for %d-byte outputs", bn, 128 / r->ob, r->ob);
-  if (epi != 1 && epi != 2) return fail("tlb200: cfg_epilogue must be 0, 1 or 2");
+  if (epi >= 2 && !tma_ok) return fail("tlb200: the staged epilogues (cfg_epilogue 2, 3) need a 16-byte aligned C, row pitch and row length (n * element size)");
+  if (epi >= 2 && !slab_ok)
+    return fail("tlb200: the staged epilogues (cfg_epilogue 2, 3) need block_n (%d) to be a multiple of %d for %d-byte outputs", bn, 128 / r->ob, r->ob);
+  if (epi < 1 || epi > 3) return fail("tlb200: cfg_epilogue must be 0, 1, 2 or 3");
   p.epilogue = epi;
-  r->epi_tma = epi == 2;
+  r->epi_tma = epi >= 2;
+  r->epi_lsu = epi == 3;
   const int acc_cols = bn * r->acc_stages;
   p.tmem_cols = acc_cols <= 32 ? 32 : acc_cols <= 64 ? 64 : acc_cols <= 128 ? 128 : acc_cols <= 256 ? 256 : 512;
   p.umma_n = r->umma_n;
@@ -1094,6 +1105,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.n_sub = r.n_sub;
   kp.acc_stages = r.acc_stages;
   kp.epi_warps = r.epi_warps;
+  kp.epi_slabs = r.epi_slabs;
   kp.stages = pl.stages;
   kp.k_elems_per_block = bk;
   kp.a_mn_major = r.a_mn; kp.b_mn_major = r.b_mn;
@@ -1115,6 +1127,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.out_kind = split ? static_cast<int>(kOutF32) : out_kind;
   kp.acc_int = d->ab_dtype == TLB200_INT8;
   kp.epi_tma = split ? ws_tma : r.epi_tma;
+  kp.epi_lsu = (!split && r.epi_lsu && n_peer == 0) ? 1 : 0;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
   kp.accumulate = (!split && (d->epilogue & TLB200_EPI_ACCUMULATE)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;

@@ -31,4 +31,5 @@ print("tile | acc free->1st kb | mainloop (1st kb->last commit) | commit->epi0 s
 for i, r in enumerate(rows):
     nxt = rows[i + 1][0] if i + 1 < len(rows) else 0
     last_done = max(r[6], r[10])
-    print(f"{i:3d} | {r[1]-r[0]:6d} | {r[2]-r[1]:7d} | {r[3]-r[2]:6d} | {r[4]-r[3]:6d} | {r[5]-r[4]:6d} | {r[6]-r[5]:6d} | {r[8]-r[7]:6d} {r[10]-r[9]:6d} | {(nxt-last_done) if nxt else 0:6d} | {r[0]-r[11]:7d}   exposed(commit->next acc free) {(nxt - r[2]) if nxt else 0}")
+    print(f"{i:3d} | {r[1]-r[0]:6d} | {r[2]-r[1]:7d} | {r[3]-r[2]:6d} | {r[4]-r[3]:6d} | {r[5]-r[4]:6d} | {r[6]-r[5]:6d} | {r[8]-r[7]:6d} {r[10]-r[9]:6d} | {(nxt-last_done) if nxt else 0:6d} | {r[0]-r[11]:7d}   exposed(commit->next acc free) {(nxt - r[2]) if nxt else 0}"
+          f" | epi0 acc0, 2nd slab: full->ld done {r[12]-r[3]}, ->store-read wait done {r[13]-r[12]}, ->st.shared+fence {r[14]-r[13]}, ->store issued {r[15]-r[14]}")
