@@ -1,0 +1,157 @@
+"""Binding into a genuine TileLang.
+
+`import tilelang` inside these tests' child processes is the upstream TileLang wheel of the image (same lineage as
+the reference: identical `tl.tileop.gemm` / `tl.tileop.copy` / `tl.tileop.region` operators and the same 19
+positional gemm arguments, tilelang/language/gemm.py:99-101, src/op/gemm_py.cc:53-93) - not this repo's
+compat/ facade.  The programs are tests/upstream_programs.py, written against the public tile-language API, traced
+here by the REAL `@T.prim_func` into `tvm.tir.PrimFunc`s.  `tilelang_mesh_b200.tir_frontend` decodes that TIR,
+emits a per-program wrapper library with the reference's generated C ABI (`init` / `call(A, B, C, stream)` /
+`get_last_error`) and hands it to `JITKernel.from_database(kernel_lib_path=...)`, so the compiler's own adapter
+drives `gemm_tcgen05_kernel`.
+"""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+PRELUDE = f'''
+import json, sys
+sys.path.insert(0, {ROOT!r}); sys.path.insert(0, {os.path.join(ROOT, "tests")!r})
+import tilelang
+assert "site-packages" in tilelang.__file__ and "compat" not in tilelang.__file__, tilelang.__file__
+import upstream_programs as P
+from tilelang_mesh_b200 import tir_frontend as F
+'''
+
+CPU_SCRIPT = PRELUDE + '''
+from tilelang import tvm
+out = {"version": tilelang.__version__}
+func = P.tmem_accumulator(4096, 4096, 8192)           # examples/gemm_sm100/gemm_tcgen5mma.py's program shape
+assert isinstance(func, tvm.tir.PrimFunc)
+calls = []
+tvm.tir.stmt_functor.post_order_visit(func.body, lambda n: calls.append(n) if isinstance(n, tvm.tir.Call) and str(getattr(n.op, "name", "")) in F.GEMM_OPS else None)
+g = F.decode_gemm_call(calls[0])
+out["gemm_nargs"] = len(calls[0].args)
+out["gemm"] = dict(M=int(g["M"]), N=int(g["N"]), K=int(g["K"]), trans_A=bool(g["trans_A"]), trans_B=bool(g["trans_B"]),
+                   stride_A=int(g["stride_A"]), stride_B=int(g["stride_B"]), k_pack=int(g["k_pack"]), wg_wait=int(g["wg_wait"]),
+                   clear_accum=str(g["clear_accum"]), a_scope=str(g["A"].args[0].buffer.scope()), c_scope=str(g["C"].args[0].buffer.scope()))
+p = F.recognize_primfunc(func)
+out["tmem"] = dict(M=p.M, N=p.N, K=p.K, dt=p.in_dtype, out=p.out_dtype, tA=p.trans_A, tB=p.trans_B, acc=p.accumulator, stages=p.num_stages,
+                   tile=[p.block_M, p.block_N, p.block_K])
+q = F.recognize_primfunc(P.nn_relu(1024, 1024, 1024))   # examples/quickstart.py's program shape
+out["relu"] = dict(M=q.M, N=q.N, K=q.K, tA=q.trans_A, tB=q.trans_B, relu=q.relu, dt=q.in_dtype)
+r = F.recognize_primfunc(P.nt_fragment(512, 768, 1024, dt="float8_e4m3", out_dt="bfloat16"))
+out["fp8"] = dict(dt=r.in_dtype, out=r.out_dtype, tB=r.trans_B)
+src = F.wrapper_source(q)
+out["src_has_trio"] = all(s in src for s in ("int init(void)", "int call(", "get_last_error", "tlb200_gemm_static_scratch", "TLB200_EPI_RELU"))
+kern = F.compile(func, out_idx=[2], out_dir=sys.argv[1])  # a genuine JITKernel around the wrapper library (init() touches no GPU)
+out["kernel_type"] = type(kern).__module__ + "." + type(kern).__name__
+out["adapter"] = type(kern.adapter).__name__
+out["lib_exports"] = all(hasattr(kern.adapter.lib, s) for s in ("init", "call", "get_last_error"))
+# outside the family: the same loud rejection as the facade
+import tilelang.language as T
+@T.prim_func
+def two_gemms(A: T.Tensor((256, 256), "float16"), B: T.Tensor((256, 256), "float16"), C: T.Tensor((256, 256), "float16")):
+    with T.Kernel(2, 2, threads=128) as (bx, by):
+        a_s = T.alloc_shared((128, 32), "float16"); b_s = T.alloc_shared((128, 32), "float16")
+        acc = T.alloc_fragment((128, 128), "float")
+        T.clear(acc)
+        for k in T.Pipelined(8, num_stages=2):
+            T.copy(A[by * 128, k * 32], a_s); T.copy(B[bx * 128, k * 32], b_s)
+            T.gemm(a_s, b_s, acc, transpose_B=True); T.gemm(a_s, b_s, acc, transpose_B=True)
+        T.copy(acc, C[by * 128, bx * 128])
+try:
+    F.recognize_primfunc(two_gemms); out["rejects"] = False
+except NotImplementedError as e:
+    out["rejects"] = "exactly one T.gemm" in str(e)
+print("SPLICE " + json.dumps(out))
+'''
+
+GPU_SCRIPT = PRELUDE + '''
+import torch
+from tilelang_mesh_b200 import _abi
+out = {"version": tilelang.__version__}
+M, N, K = 4096, 4096, 8192
+func = P.tmem_accumulator(M, N, K)
+lib = _abi.load()
+kern = F.compile(func, out_idx=[2], out_dir=sys.argv[1])
+torch.manual_seed(0)
+a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16); b = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
+n0 = lib.tlb200_launch_count()
+c = kern(a, b); torch.cuda.synchronize()
+out["launches"] = lib.tlb200_launch_count() - n0
+out["kernel_type"] = type(kern).__module__ + "." + type(kern).__name__
+want = (a.float() @ b.float().t())
+out["max_rel_err_vs_fp32"] = ((c.float() - want).abs().max() / want.abs().max()).item()
+lat = kern.get_profiler().do_bench()
+out["tflops"] = 2 * M * N * K / lat * 1e-9
+# the same PrimFunc lowered by the compiler itself (the lineage's own tcgen05 code path)
+try:
+    ref = tilelang.compile(func, out_idx=[2], target="cuda", pass_configs={tilelang.PassConfigKey.TL_DISABLE_TMA_LOWER: True,
+                                                                             tilelang.PassConfigKey.TL_DISABLE_WARP_SPECIALIZED: True})
+    c_ref = ref(a, b); torch.cuda.synchronize()
+    diff = (c.float() - c_ref.float()).abs()
+    ulp = (c_ref.float().abs() * 2.0 ** -6).clamp_min(4e-3)
+    out["within_one_ulp_of_lineage"] = bool((diff <= ulp).all())
+    out["bit_equal_frac"] = (c.view(torch.int16) == c_ref.view(torch.int16)).float().mean().item()
+    out["lineage_tflops"] = 2 * M * N * K / ref.get_profiler().do_bench() * 1e-9
+except Exception as e:
+    out["lineage_error"] = repr(e)[:300]
+# a second program through the same path: NN layout + fused relu (quickstart), fp16
+f2 = P.nn_relu(1024, 1024, 1024)
+k2 = F.compile(f2, out_idx=[2], out_dir=sys.argv[1])
+a2 = torch.randn(1024, 1024, device="cuda").half(); b2 = torch.randn(1024, 1024, device="cuda").half()
+c2 = k2(a2, b2); torch.cuda.synchronize()
+w2 = torch.relu(a2.float() @ b2.float()).half()
+out["relu_mismatch_frac"] = (~torch.isclose(c2.float(), w2.float(), rtol=1e-2, atol=1e-2)).float().mean().item()
+print("SPLICE " + json.dumps(out))
+'''
+
+
+def _run(script_text, tmp_path, timeout):
+    script = tmp_path / "splice_prog.py"  # the real tracer needs inspect.getsource -> a real file
+    script.write_text(script_text)
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    try:
+        res = subprocess.run([sys.executable, str(script), str(tmp_path / "wrappers")], capture_output=True, text=True,
+                             timeout=timeout, env=env, cwd=str(tmp_path))
+    except subprocess.TimeoutExpired:
+        pytest.skip("the upstream TileLang wheel timed out on this box")
+    line = [l for l in res.stdout.splitlines() if l.startswith("SPLICE ")]
+    if res.returncode != 0 and ("No module named 'tilelang'" in res.stderr or "site-packages" in res.stderr.splitlines()[-1:][0:1].__repr__()):
+        pytest.skip("no upstream TileLang wheel in this environment")
+    assert res.returncode == 0 and line, res.stderr[-3000:]
+    return json.loads(line[0][len("SPLICE "):])
+
+
+def test_real_primfunc_is_decoded_and_wrapped(tmp_path, built_lib):
+    """CPU: a real tvm.tir.PrimFunc -> 19-argument decode -> GemmProgram -> wrapper library -> JITKernel.from_database."""
+    o = _run(CPU_SCRIPT, tmp_path, 600)
+    assert o["gemm_nargs"] == 19  # tilelang/language/gemm.py:99-101
+    assert o["gemm"] == dict(M=128, N=256, K=128, trans_A=False, trans_B=True, stride_A=128, stride_B=128, k_pack=1, wg_wait=0,
+                             clear_accum="k == 0", a_scope="shared.dyn", c_scope="shared.tmem")
+    assert o["tmem"] == dict(M=4096, N=4096, K=8192, dt="bfloat16", out="bfloat16", tA=False, tB=True, acc="tmem", stages=2,
+                             tile=[128, 256, 128])
+    assert o["relu"] == dict(M=1024, N=1024, K=1024, tA=False, tB=False, relu=True, dt="float16")
+    assert o["fp8"] == dict(dt="float8_e4m3", out="bfloat16", tB=True)
+    assert o["src_has_trio"] and o["lib_exports"] and o["rejects"]
+    assert o["kernel_type"] == "tilelang.jit.kernel.JITKernel" and o["adapter"] == "CythonKernelAdapter"
+
+
+@pytest.mark.gpu
+def test_real_tilelang_runs_this_backend(tmp_path, built_lib):
+    """GPU: the compiler's own JITKernel + adapter launch gemm_tcgen05_kernel through the wrapper library, and the
+    result equals the same PrimFunc lowered by the compiler itself (the lineage's tcgen05 path)."""
+    o = _run(GPU_SCRIPT, tmp_path, 1500)
+    assert o["kernel_type"] == "tilelang.jit.kernel.JITKernel"
+    assert o["launches"] == 1, "exactly one kernel of libtlb200.so per call"
+    assert o["max_rel_err_vs_fp32"] < 1e-2           # north_star's tolerance for bf16
+    assert o["relu_mismatch_frac"] <= 0.01
+    if "lineage_error" not in o:
+        assert o["within_one_ulp_of_lineage"] and o["bit_equal_frac"] > 0.95
+        assert o["tflops"] > o["lineage_tflops"]
+    print(json.dumps(o))

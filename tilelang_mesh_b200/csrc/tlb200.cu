@@ -1275,9 +1275,14 @@ int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* d, const void* a, con
     const long long t256 = static_cast<long long>((d->m + 127) / 128) * ((d->n + 255) / 256);
     bn = (d->n <= 128 || t256 < sms) ? 128 : 256;
   }
-  // Pairs are available (cfg_cta_group = 2) but not the default: the partial-sum hand-off crosses the cluster
-  // at every K block and measured about half the single-CTA rate (profiles/r1_notes.md).
-  if (cg == 0) cg = 1;
+  // Pairs (cta_group::2: half the B traffic per CTA) are the default for 256-wide tiles when a pair plan still
+  // occupies the machine.  The per-K-block hand-back of the partial-sum buffer crosses the cluster; with the relaxed
+  // cluster arrive it costs what the local one does (with the release form pairs ran at half the single-CTA rate:
+  // profiles/r1_notes.md, profiles/r2_notes.md).  8192^3: 2478 vs 2191 TFLOP/s back to back.
+  if (cg == 0) {
+    const long long pair_tiles = static_cast<long long>((d->m + 2 * kBlockM - 1) / (2 * kBlockM)) * ((d->n + bn - 1) / bn);
+    cg = (bn == 256 && d->m > kBlockM && pair_tiles >= sms / 2) ? 2 : 1;
+  }
   const int block_m = kBlockM * cg;
   const int stage_bytes = kABytesPerStage + (bn / cg) * kStageRowBytes;
   const int fixed = 1024 + kBsEpiWarps * kEpiBufBytes + (2 * kMaxStages + 8) * 8 + 16;
