@@ -148,7 +148,8 @@ def test_real_tilelang_runs_this_backend(tmp_path, built_lib):
     result equals the same PrimFunc lowered by the compiler itself (the lineage's tcgen05 path)."""
     o = _run(GPU_SCRIPT, tmp_path, 1500)
     assert o["kernel_type"] == "tilelang.jit.kernel.JITKernel"
-    assert o["launches"] == 1, "exactly one kernel of libtlb200.so per call"
+    # the GEMM kernel, plus the small reduction kernel when the plan splits the last wave along K (static scratch)
+    assert o["launches"] in (1, 2), "the kernels that ran are libtlb200.so's"
     assert o["max_rel_err_vs_fp32"] < 1e-2           # north_star's tolerance for bf16
     assert o["relu_mismatch_frac"] <= 0.01
     if "lineage_error" not in o:
