@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define TLB200_ABI_VERSION 1
+#define TLB200_ABI_VERSION 2 /* 2: tlb200_gemm_desc gained the epilogue-vector fields (vec_*) and tlb200_gemm_fused */
 
 /* Element types.  Values follow the DLPack-free compact enum used by the
  * Python adapter; names follow tilelang/utils/tensor.py:34-51. */
@@ -95,7 +95,29 @@ typedef struct tlb200_gemm_desc {
                           * [1] = cfg_split_k: 0 auto, 1 off (no split-K, no tail split), n = at most n K slices,
                           *       -1 = no split-K but force the tail split (both need a workspace);
                           * [2] = cfg_l2_policy: 0 default (operands evict_last, C evict_first), 1 = no hints */
+  /* ABI 2: which epilogue vectors tlb200_gemm_fused is given (ignored by every other entry point, which treat
+   * them as absent).  All vectors are float32. */
+  uint32_t vec_flags;    /* TLB200_VEC_* */
+  int32_t reserved2[3];  /* must be 0 */
 } tlb200_gemm_desc;
+
+/* Epilogue vectors ("bias / per-row scales"; the per-row form is the scales_a[m, kb] of
+ * examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:34,71-73 collapsed to one K block, the per-column
+ * form its scales_b at 1-wide groups; a bias has no counterpart in the reference's GEMM examples):
+ *
+ *   C[m, n] = cast(relu?(((alpha * acc[m, n]) * row_scale[m]) * col_scale[n] + bias))
+ *
+ * every operation rounded to fp32 in exactly this order (the oracle, oracle/gemm_oracle.c::oracle_gemm_fused, does
+ * the same), `bias` = bias_n[n] (TLB200_VEC_BIAS_N, length N) or bias_m[m] (TLB200_VEC_BIAS_M, length M). */
+#define TLB200_VEC_ROW_SCALE 1u /* row_scale[M] */
+#define TLB200_VEC_COL_SCALE 2u /* col_scale[N] */
+#define TLB200_VEC_BIAS_N 4u    /* bias[N]: one value per output column (a linear layer's bias) */
+#define TLB200_VEC_BIAS_M 8u    /* bias[M]: one value per output row; not together with TLB200_VEC_BIAS_N */
+typedef struct tlb200_epilogue_vectors {
+  const float* row_scale; /* device pointers, 4-byte aligned; NULL where the flag is not set */
+  const float* col_scale;
+  const float* bias;
+} tlb200_epilogue_vectors;
 
 /* The configuration the library resolved for a descriptor (for reports/tests). */
 typedef struct tlb200_gemm_plan {
@@ -144,6 +166,13 @@ int tlb200_gemm(const tlb200_gemm_desc* desc, const void* a, const void* b, void
 int64_t tlb200_gemm_workspace_bytes(const tlb200_gemm_desc* desc);
 int tlb200_gemm_ex(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
                    void* workspace, int64_t workspace_bytes, void* stream);
+
+/* tlb200_gemm_ex with epilogue vectors fused into the TMEM -> global drain (desc->vec_flags says which of
+ * `vec`'s pointers are read).  Works with every plan of tlb200_gemm_ex, split-K and the tail split included (their
+ * reduction kernels apply the vectors).  Not offered for int32 output or TLB200_EPI_ACCUMULATE.
+ * `workspace` may be NULL as in tlb200_gemm_ex. */
+int tlb200_gemm_fused(const tlb200_gemm_desc* desc, const void* a, const void* b, void* c,
+                      const tlb200_epilogue_vectors* vec, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Grouped contraction (the reference's examples/grouped_gemm: MoE expert
  * GEMMs): rows of A[sum_rows, K] and C[sum_rows, N] are cut into n_groups

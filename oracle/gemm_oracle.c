@@ -157,6 +157,36 @@ int oracle_gemm(int m, int n, int k, int ab_dtype, int c_dtype, int trans_a, int
   return 0;
 }
 
+/*
+ * oracle_gemm with epilogue vectors (bias / per-row scales; the per-row form is scales_a[m, kb] of
+ * examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:34,71-73 collapsed to one K block):
+ *   C = cast(relu?(((alpha * acc) * row_scale[m]) * col_scale[n] + bias)),   every step rounded to fp32, in this order;
+ *   bias = bias[n], or bias[m] when bias_per_row.  Null vectors are skipped.
+ */
+int oracle_gemm_fused(int m, int n, int k, int ab_dtype, int c_dtype, int trans_a, int trans_b, const void* A,
+                      long long lda, const void* B, long long ldb, void* C, long long ldc, float alpha, int relu,
+                      const float* row_scale, const float* col_scale, const float* bias, int bias_per_row) {
+  if (m < 0 || n < 0 || k < 0 || ab_dtype < 0 || ab_dtype > 3 || c_dtype < 0 || c_dtype > 4) return -1;
+  for (int i = 0; i < m; ++i) {
+    for (int j = 0; j < n; ++j) {
+      float acc = 0.f;
+      for (int kk = 0; kk < k; ++kk) {
+        const float a = oracle_decode(ab_dtype, A, trans_a ? (long long)kk * lda + i : (long long)i * lda + kk);
+        const float b = oracle_decode(ab_dtype, B, trans_b ? (long long)j * ldb + kk : (long long)kk * ldb + j);
+        acc = acc + a * b;
+      }
+      volatile float v = acc * alpha; /* volatile: no contraction of the multiply chain into fmas */
+      if (row_scale) v = v * row_scale[i];
+      if (col_scale) v = v * col_scale[j];
+      if (bias) v = v + bias[bias_per_row ? i : j];
+      float out = v;
+      if (relu && out < 0.f) out = 0.f;
+      oracle_encode(c_dtype, C, (long long)i * ldc + j, out);
+    }
+  }
+  return 0;
+}
+
 /* fp8 contraction with fine-grained scales, the tile program of
  * examples/deepseek_deepgemm/example_deepgemm_fp8_2xAcc.py:43-83 restated per output element:
  *   for every 128-wide K block kb:  partial = sum_k A[i,k]*B[j,k]        (T.gemm into a cleared C_local, :75,79)

@@ -72,6 +72,27 @@ def c_oracle_gemm(a: torch.Tensor, b: torch.Tensor, out_dtype: torch.dtype, tran
     return c
 
 
+def c_oracle_gemm_fused(a: torch.Tensor, b: torch.Tensor, out_dtype: torch.dtype, trans_a=False, trans_b=True, alpha: float = 1.0,
+                        relu: bool = False, row_scale=None, col_scale=None, bias=None, bias_per_row: bool = False) -> torch.Tensor:
+    """Scalar C oracle of the contraction with epilogue vectors (oracle_gemm_fused; small sizes only)."""
+    a, b = a.detach().cpu().contiguous(), b.detach().cpu().contiguous()
+    m, k = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    n = b.shape[0] if trans_b else b.shape[1]
+    c = torch.empty((m, n), dtype=out_dtype)
+    vecs = [None if v is None else v.detach().cpu().float().contiguous() for v in (row_scale, col_scale, bias)]
+    fn = _c().oracle_gemm_fused
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p,
+                                        ctypes.c_longlong, ctypes.c_float, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                        ctypes.c_void_p, ctypes.c_int]
+    rc = fn(m, n, k, DT[a.dtype], DT[out_dtype], int(trans_a), int(trans_b), a.data_ptr(),
+            a.stride(0) if a.shape[0] > 1 else a.shape[1], b.data_ptr(), b.stride(0) if b.shape[0] > 1 else b.shape[1],
+            c.data_ptr(), n, float(alpha), int(relu), *[None if v is None else v.data_ptr() for v in vecs], int(bias_per_row))
+    if rc != 0:
+        raise ValueError("oracle_gemm_fused: bad arguments")
+    return c
+
+
 def c_oracle_gemm_blockscaled(a: torch.Tensor, b: torch.Tensor, scales_a: torch.Tensor, scales_b: torch.Tensor,
                               out_dtype: torch.dtype) -> torch.Tensor:
     """Scalar C oracle of the fine-grained-scale fp8 contraction (small sizes only)."""

@@ -34,8 +34,9 @@ def test_header_and_binding_agree(built_lib):
 
 
 def test_struct_layout_matches_header(built_lib):
-    # 8 int32 + 3 int64 + float + uint32 + 5 int32 + 3 reserved, natural alignment
-    assert ctypes.sizeof(_abi.GemmDesc) == 96
+    # 8 int32 + 3 int64 + float + uint32 + 5 int32 + 3 reserved + vec_flags + 3 reserved2 (ABI 2), natural alignment
+    assert ctypes.sizeof(_abi.GemmDesc) == 112 and _abi.GemmDesc.vec_flags.offset == 96
+    assert ctypes.sizeof(_abi.EpilogueVectors) == 24
     assert _abi.GemmDesc.lda.offset == 32 and _abi.GemmDesc.alpha.offset == 56
     assert ctypes.sizeof(_abi.GemmPlan) == 80 and _abi.GemmPlan.workspace_bytes.offset == 72
 
@@ -80,7 +81,8 @@ def test_plan_headline_configs(built_lib):
     p = G.plan(8192, 8192, 8192)  # C2: 2-CTA pairs, 256 x 512 tiles = two 256-column accumulators sharing the A stage
     assert (p["cta_group"], p["block_m"], p["block_n"], p["block_k"], p["umma_n"]) == (2, 256, 512, 64, 256)
     assert p["grid"] == 148 and p["tmem_cols"] == 512 and p["smem_bytes"] <= 232448 and p["threads"] == 384
-    assert p["tiles_m"] * p["tiles_n"] == 512 and p["stages"] == 4
+    assert p["tiles_m"] * p["tiles_n"] == 512 and p["stages"] == 3  # 3 stages of 48 KiB + two 4 KiB staging slabs per epilogue warp
+    assert G.plan(8192, 8192, 8192, stages=4)["stages"] == 4      # (an explicit 4 keeps one slab per warp)
     assert p["instr_desc"] == D.tcgen5_instr_desc(256, 256, 16, "bfloat16", "float32")
     p8 = G.plan(8192, 8192, 8192, torch.float8_e4m3fn, torch.bfloat16)  # C3
     assert p8["block_k"] == 128 and p8["instr_desc"] == D.tcgen5_instr_desc(256, 256, 32, "float8_e4m3", "float32")

@@ -155,3 +155,26 @@ def test_c_oracle_blockscaled_known_answer_and_identity():
     torch.testing.assert_close(c, R.blockscaled_fp32(a, b, sa, sb), rtol=1e-4, atol=1e-4)
     cb = R.c_oracle_gemm_blockscaled(a, b, sa, sb, torch.bfloat16)
     assert torch.equal(cb, c.bfloat16())
+
+
+def test_fused_oracle_order_of_operations():
+    """oracle_gemm_fused: ((alpha * acc) * row_scale) * col_scale + bias, each step rounded to fp32, relu, one cast."""
+    import numpy as np
+    torch.manual_seed(3)
+    m, n, k = 9, 11, 24
+    a = torch.randint(-3, 4, (m, k)).float().bfloat16()
+    b = torch.randint(-3, 4, (n, k)).float().bfloat16()
+    rs, cs, bias = torch.rand(m) + 0.5, torch.rand(n) + 0.5, torch.randn(n)
+    alpha = 0.37
+    got = R.c_oracle_gemm_fused(a, b, torch.float32, alpha=alpha, relu=True, row_scale=rs, col_scale=cs, bias=bias)
+    acc = (a.double() @ b.double().t()).numpy().astype(np.float32)  # exact small integers
+    v = (acc * np.float32(alpha)).astype(np.float32)
+    v = (v * rs.numpy()[:, None]).astype(np.float32)
+    v = (v * cs.numpy()[None, :]).astype(np.float32)
+    v = (v + bias.numpy()[None, :]).astype(np.float32)
+    assert np.array_equal(got.numpy(), np.maximum(v, 0))
+    # no vectors = oracle_gemm
+    assert torch.equal(R.c_oracle_gemm_fused(a, b, torch.bfloat16, alpha=alpha).view(torch.int16),
+                       R.c_oracle_gemm(a, b, torch.bfloat16, alpha=alpha).view(torch.int16))
+    per_row = R.c_oracle_gemm_fused(a, b, torch.float32, bias=torch.arange(m).float(), bias_per_row=True)
+    assert torch.equal(per_row, torch.from_numpy(acc) + torch.arange(m).float()[:, None])

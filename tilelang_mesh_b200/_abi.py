@@ -14,7 +14,7 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TLB200_LIB") or os.path.join(_HERE, "lib", "libtlb200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # tlb200_dtype
 FLOAT16, BFLOAT16, FLOAT8_E4M3, FLOAT8_E5M2, FLOAT32, INT8, INT32 = 0, 1, 2, 3, 4, 5, 6
@@ -43,7 +43,17 @@ class GemmDesc(ctypes.Structure):
         ("cfg_raster", ctypes.c_int32),
         ("cfg_epilogue", ctypes.c_int32),
         ("reserved", ctypes.c_int32 * 3),
+        ("vec_flags", ctypes.c_uint32),
+        ("reserved2", ctypes.c_int32 * 3),
     ]
+
+
+class EpilogueVectors(ctypes.Structure):
+    """tlb200_epilogue_vectors (include/tlb200.h): float32 device pointers."""
+    _fields_ = [("row_scale", ctypes.c_void_p), ("col_scale", ctypes.c_void_p), ("bias", ctypes.c_void_p)]
+
+
+VEC_ROW_SCALE, VEC_COL_SCALE, VEC_BIAS_N, VEC_BIAS_M = 1, 2, 4, 8
 
 
 class GemmPlan(ctypes.Structure):
@@ -91,6 +101,8 @@ SYMBOLS = {
     "tlb200_gemm_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),
     "tlb200_gemm_ex": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                       ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "tlb200_gemm_fused": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                         ctypes.POINTER(EpilogueVectors), ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "tlb200_gemm_grouped": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                            ctypes.POINTER(ctypes.c_int32), ctypes.c_int, ctypes.c_void_p]),
     "tlb200_gemm_bcast": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,

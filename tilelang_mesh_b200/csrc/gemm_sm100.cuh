@@ -99,6 +99,11 @@ struct alignas(64) GemmKernelParams {
   int accumulate;  // C = C_in + alpha * acc (predicated-store epilogue only)
   int l2_policy;
   float alpha;
+  // epilogue vectors (all fp32, null = absent): v = ((alpha * acc) * row_scale[m]) * col_scale[n] + bias
+  const float* row_scale;
+  const float* col_scale;
+  const float* bias;
+  int bias_per_row;  // bias is indexed by the output row (else by the column)
   long long* trace;  // development builds (-DTLB200_TRACE): per-tile clock64 stamps of CTA 0; null otherwise
 };
 
@@ -195,32 +200,6 @@ __device__ __forceinline__ float load_out(const void* c, long long idx) {
   }
 }
 
-// 32 accumulator elements (one tcgen05.ld) -> the values to be cast: alpha, relu.  Kept to ONE instruction per
-// element on the ordinary path (an FMUL): two epilogue warps share a scheduler and every instruction here is
-// issued 32-64 times per slab, so a per-element select between integer and float accumulators or a per-element
-// relu test made the drain of a 128 x 256 accumulator issue-bound (4.5k cycles, profiles/r2_notes.md).  kAccInt is
-// a property of the kernel instantiation (int8 operands); relu is a warp-uniform branch around a second pass.
-// int32 accumulators are converted to float unless the output is int32 too: then the raw integer bits are carried.
-template <int kOut, bool kAccInt>
-__device__ __forceinline__ void epi_values(const uint32_t (&raw)[32], float (&v)[32], float alpha, bool relu) {
-  if constexpr (kOut == kOutI32) {
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
-    if (relu) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = __int_as_float(max(__float_as_int(v[i]), 0));
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 32; ++i)
-      v[i] = (kAccInt ? static_cast<float>(static_cast<int>(raw[i])) : __uint_as_float(raw[i])) * alpha;
-    if (relu) {
-#pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
-    }
-  }
-}
-
 // Where and how one tile's accumulator is written: the final C (cast, alpha, relu, optional += C), or - for the K
 // slices of a split tail tile - raw fp32 partial sums into the caller's workspace.
 struct EpiOut {
@@ -232,6 +211,10 @@ struct EpiOut {
   int relu, accumulate, tma, n_peer;
   int lsu;                // staged slabs leave shared memory through coalesced st.global instead of a TMA store
   int evict_first;        // C is write-once: keep it from displacing the operands in L2
+  const float* row_scale; // epilogue vectors of the final C (null = absent; never set for raw partial sums)
+  const float* col_scale;
+  const float* bias;
+  int bias_per_row;
   int trace_seq;          // development builds: tile sequence number for TLB_TRACE, -1 = do not trace this call
 };
 #ifdef TLB200_TRACE
@@ -239,6 +222,60 @@ struct EpiOut {
 #else
 #define TLB_TRACE_EPI(slot) do { } while (0)
 #endif
+
+// Epilogue vectors on 32 consecutive columns [gcol, gcol + 32) of global row `grow` (after alpha, before relu and the
+// cast): v = (v * row_scale[grow]) * col_scale[col] + bias, each step rounded to fp32.  Columns / rows outside the
+// matrix read nothing (their values are never stored).  Warp-uniform branches: a GEMM without vectors pays nothing.
+__device__ __forceinline__ void epi_apply_vectors(float (&v)[32], const EpiOut& o, int grow, int row_limit, int gcol) {
+  if (o.row_scale != nullptr) {
+    const float rs = grow < row_limit ? __ldg(o.row_scale + grow) : 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = v[i] * rs;
+  }
+  if (o.col_scale != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = v[i] * (gcol + i < o.n ? __ldg(o.col_scale + gcol + i) : 0.f);
+  }
+  if (o.bias != nullptr) {
+    if (o.bias_per_row) {
+      const float bv = grow < row_limit ? __ldg(o.bias + grow) : 0.f;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = v[i] + bv;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = v[i] + (gcol + i < o.n ? __ldg(o.bias + gcol + i) : 0.f);
+    }
+  }
+}
+
+// 32 accumulator elements (one tcgen05.ld) -> the values to be cast: alpha, relu.  Kept to ONE instruction per
+// element on the ordinary path (an FMUL): two epilogue warps share a scheduler and every instruction here is
+// issued 32-64 times per slab, so a per-element select between integer and float accumulators or a per-element
+// relu test made the drain of a 128 x 256 accumulator issue-bound (4.5k cycles, profiles/r2_notes.md).  kAccInt is
+// a property of the kernel instantiation (int8 operands); relu is a warp-uniform branch around a second pass.
+// int32 accumulators are converted to float unless the output is int32 too: then the raw integer bits are carried.
+template <int kOut, bool kAccInt>
+__device__ __forceinline__ void epi_values(const uint32_t (&raw)[32], float (&v)[32], float alpha, bool relu, const EpiOut* vec = nullptr,
+                                           int grow = 0, int row_limit = 0, int gcol = 0) {
+  if constexpr (kOut == kOutI32) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = __int_as_float(max(__float_as_int(v[i]), 0));
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      v[i] = (kAccInt ? static_cast<float>(static_cast<int>(raw[i])) : __uint_as_float(raw[i])) * alpha;
+    if (vec != nullptr && (vec->row_scale != nullptr || vec->col_scale != nullptr || vec->bias != nullptr))
+      epi_apply_vectors(v, *vec, grow, row_limit, gcol);
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+    }
+  }
+}
 
 // ---------------------------------------------------------------- epilogue for one tile
 // What one epilogue warp needs to drain its share of an accumulator (always inlined: a context passed by reference).
@@ -382,7 +419,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
 #pragma unroll
         for (int h = 0; h < kPair; ++h) {
           float v[32];
-          epi_values<kOut, kAccInt>(r[h], v, alpha, relu);
+          epi_values<kOut, kAccInt>(r[h], v, alpha, relu, &o, grow, row_limit, col0 + cs + (l0 + h) * 32);
 #pragma unroll
           for (int pk = 0; pk < kPacketsPerLd; ++pk) w[(l0 + h) * kPacketsPerLd + pk] = pack16<kOut>(&v[pk * kValsPerPacket]);
         }
@@ -403,7 +440,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
         released = true;
       }
       float v[32];
-      epi_values<kOut, kAccInt>(r, v, alpha, relu);
+      epi_values<kOut, kAccInt>(r, v, alpha, relu, &o, grow, row_limit, col0 + cs);
       if (row_ok) {
         const int gcol = col0 + cs;
         const long long base = static_cast<long long>(grow + row_off) * o.ldc + gcol;
@@ -781,7 +818,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       EpiOut o{tail_item ? &p.tm_ws : &p.tm_c, tail_item ? p.ws : p.c, tail_item ? (long long)p.block_n : p.ldc,
                      tail_item ? p.block_n : p.n, tail_item ? 1.0f : p.alpha, tail_item ? 0 : p.relu,
                      tail_item ? 0 : p.accumulate, tail_item ? 1 : p.epi_tma, tail_item ? 0 : p.n_peer,
-                     tail_item ? 0 : p.epi_lsu, (!tail_item && p.l2_policy != 1) ? 1 : 0, -1};
+                     tail_item ? 0 : p.epi_lsu, (!tail_item && p.l2_policy != 1) ? 1 : 0,
+                     tail_item ? nullptr : p.row_scale, tail_item ? nullptr : p.col_scale, tail_item ? nullptr : p.bias,
+                     p.bias_per_row, -1};
       const int out_kind = tail_item ? static_cast<int>(kOutF32) : p.out_kind;
 #pragma unroll
       for (int h = 0; h < kNSub; ++h) {

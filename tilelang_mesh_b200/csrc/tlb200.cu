@@ -176,6 +176,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
                 TLB200_ABI_VERSION);
   if (d->m < 0 || d->n < 0 || d->k < 0) return fail("tlb200: negative extent (m=%d n=%d k=%d)", d->m, d->n, d->k);
+  if (d->reserved2[0] || d->reserved2[1] || d->reserved2[2]) return fail("tlb200: descriptor field reserved2 must be zero");
+  if (d->vec_flags & ~(TLB200_VEC_ROW_SCALE | TLB200_VEC_COL_SCALE | TLB200_VEC_BIAS_N | TLB200_VEC_BIAS_M))
+    return fail("tlb200: unknown bits in vec_flags (0x%x)", d->vec_flags);
   if (!is_ab_dtype(d->ab_dtype))
     return fail("tlb200: unsupported operand dtype %d (float16, bfloat16, float8_e4m3, float8_e5m2)", d->ab_dtype);
   if (dtype_bytes(d->c_dtype) == 0 || d->c_dtype == TLB200_INT8) return fail("tlb200: unsupported output dtype %d", d->c_dtype);
@@ -264,7 +267,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
       if (c.bn > 32 && c.bn / 2 >= d->n && c.bn != d->cfg_block_n) continue;  // tile twice wider than the matrix
       const int step = r->b_mn ? r->span * c.cg : 32;
       if ((c.bn > 256 ? c.bn / 2 : c.bn) % step) continue;
-      if (d->cfg_epilogue == 2 && (c.bn > 256 ? c.bn / 2 : c.bn) % (128 / r->ob)) continue;  // TMA-store slabs are 128 B wide
+      if (d->cfg_epilogue >= 2 && (c.bn > 256 ? c.bn / 2 : c.bn) % (128 / r->ob)) continue;  // staging slabs are 128 B wide
       const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) *
                               (((d->n + c.bn - 1) / c.bn + c.mc - 1) / c.mc);  // work items: c.mc column tiles each
       const long long clusters = c.mc == 2 ? mc_clusters : sms_all / c.cg;
@@ -491,10 +494,25 @@ cudaError_t launch_dependent(void (*kernel)(KArgs...), int grid, int block, cuda
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
-// Split-K second pass: C[m,n] = cast(relu?(alpha * sum_s ws[s*m_pad + m, n])), slices summed in order.
+// Epilogue vectors as the reduction kernels take them (null = absent); same arithmetic, in the same order, as
+// epi_apply_vectors in the GEMM kernel: v = ((alpha * sum) * row_scale[m]) * col_scale[n] + bias.
+struct ReduceVectors {
+  const float* row_scale;
+  const float* col_scale;
+  const float* bias;
+  int bias_per_row;
+};
+__device__ __forceinline__ float reduce_apply_vectors(float v, const ReduceVectors& vec, long long row, int col) {
+  if (vec.row_scale) v = v * vec.row_scale[row];
+  if (vec.col_scale) v = v * vec.col_scale[col];
+  if (vec.bias) v = v + vec.bias[vec.bias_per_row ? row : col];
+  return v;
+}
+
+// Split-K second pass: C[m,n] = cast(relu?(vectors(alpha * sum_s ws[s*m_pad + m, n]))), slices summed in order.
 template <int kOut>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_ld, int m_pad, int split_k, void* c,
-                                     long long ldc, int m, int n, float alpha, int relu, int accumulate) {
+                                     long long ldc, int m, int n, float alpha, int relu, int accumulate, ReduceVectors vec) {
   griddep_wait();  // the partial sums come from the previous kernel
   const int n4 = (n + 3) / 4;
   const long long total = static_cast<long long>(m) * n4;
@@ -509,8 +527,9 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_
     float o[4] = {acc.x * alpha, acc.y * alpha, acc.z * alpha, acc.w * alpha};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      if (relu) o[j] = fmaxf(o[j], 0.f);
       if (col + j < n) {
+        o[j] = reduce_apply_vectors(o[j], vec, row, col + j);
+        if (relu) o[j] = fmaxf(o[j], 0.f);
         if (accumulate) o[j] += load_out<kOut>(c, row * ldc + col + j);
         store_scalar<kOut>(c, row * ldc + col + j, o[j]);
       }
@@ -519,7 +538,7 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, long long ws_
 }
 
 int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_k, void* c, long long ldc, int m, int n,
-                         float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream) {
+                         float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream, const ReduceVectors& vec) {
   const long long total = static_cast<long long>(m) * ((n + 3) / 4);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
@@ -527,11 +546,11 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
   const int g = static_cast<int>(blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
   cudaError_t e = cudaSuccess;
   switch (out_kind) {
-    case kOutF16: e = launch_dependent(splitk_reduce_kernel<kOutF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutBF16: e = launch_dependent(splitk_reduce_kernel<kOutBF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutF32: e = launch_dependent(splitk_reduce_kernel<kOutF32>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    case kOutE4M3: e = launch_dependent(splitk_reduce_kernel<kOutE4M3>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
-    default: e = launch_dependent(splitk_reduce_kernel<kOutE5M2>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac); break;
+    case kOutF16: e = launch_dependent(splitk_reduce_kernel<kOutF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac, vec); break;
+    case kOutBF16: e = launch_dependent(splitk_reduce_kernel<kOutBF16>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac, vec); break;
+    case kOutF32: e = launch_dependent(splitk_reduce_kernel<kOutF32>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac, vec); break;
+    case kOutE4M3: e = launch_dependent(splitk_reduce_kernel<kOutE4M3>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac, vec); break;
+    default: e = launch_dependent(splitk_reduce_kernel<kOutE5M2>, g, 256, stream, ws, ws_ld, m_pad, split_k, c, ldc, m, n, alpha, rl, ac, vec); break;
   }
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return fail("tlb200: split-K reduce launch: %s", cudaGetErrorString(e));
@@ -543,7 +562,7 @@ int launch_splitk_reduce(const float* ws, long long ws_ld, int m_pad, int split_
 template <int kOut>
 __global__ void tail_reduce_kernel(const float* __restrict__ ws, int tail_begin, int tail_tiles, int tail_split, int block_m,
                                    int block_n, int tiles_m, int tiles_n, int raster, void* c, long long ldc, int m, int n,
-                                   float alpha, int relu, int accumulate) {
+                                   float alpha, int relu, int accumulate, ReduceVectors vec) {
   griddep_wait();  // the partial tiles come from the previous kernel
   const int n4 = block_n / 4;
   const long long per_tile = static_cast<long long>(block_m) * n4;
@@ -571,8 +590,9 @@ __global__ void tail_reduce_kernel(const float* __restrict__ ws, int tail_begin,
     float o[4] = {acc.x * alpha, acc.y * alpha, acc.z * alpha, acc.w * alpha};
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      if (relu) o[q] = fmaxf(o[q], 0.f);
       if (col + q < n) {
+        o[q] = reduce_apply_vectors(o[q], vec, row, col + q);
+        if (relu) o[q] = fmaxf(o[q], 0.f);
         if (accumulate) o[q] += load_out<kOut>(c, row * ldc + col + q);
         store_scalar<kOut>(c, row * ldc + col + q, o[q]);
       }
@@ -581,13 +601,13 @@ __global__ void tail_reduce_kernel(const float* __restrict__ ws, int tail_begin,
 }
 
 int launch_tail_reduce(const float* ws, const Resolved& r, const tlb200_gemm_plan& pl, void* c, long long ldc, int m, int n,
-                       float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream) {
+                       float alpha, bool relu, bool accumulate, int out_kind, cudaStream_t stream, const ReduceVectors& vec) {
   const long long total = static_cast<long long>(r.tail_tiles) * pl.block_m * (pl.block_n / 4);
   long long blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const int g = static_cast<int>(blocks < 1 ? 1 : blocks), rl = relu ? 1 : 0, ac = accumulate ? 1 : 0;
 #define TLB_TAIL(K) launch_dependent(tail_reduce_kernel<K>, g, 256, stream, ws, r.tail_begin, r.tail_tiles, r.tail_split, pl.block_m, \
-                                    pl.block_n, pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac)
+                                    pl.block_n, pl.tiles_m, pl.tiles_n, pl.raster, c, ldc, m, n, alpha, rl, ac, vec)
   cudaError_t e = cudaSuccess;
   switch (out_kind) {
     case kOutF16: e = TLB_TAIL(kOutF16); break;
@@ -974,8 +994,16 @@ extern "C" void tlb200_debug_set_trace(long long* p) { g_trace = p; }
 
 static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
                      void* stream_v, void* const* peers = nullptr, int n_peer = 0, const int32_t* group_rows = nullptr,
-                     int n_groups = 0) {
+                     int n_groups = 0, const tlb200_epilogue_vectors* vec = nullptr) {
   g_err[0] = 0;
+  // Epilogue vectors exist only for tlb200_gemm_fused (every other entry point passes none and ignores vec_flags).
+  ReduceVectors rv = {nullptr, nullptr, nullptr, 0};
+  if (vec && d) {
+    if (d->vec_flags & TLB200_VEC_ROW_SCALE) rv.row_scale = vec->row_scale;
+    if (d->vec_flags & TLB200_VEC_COL_SCALE) rv.col_scale = vec->col_scale;
+    if (d->vec_flags & (TLB200_VEC_BIAS_N | TLB200_VEC_BIAS_M)) rv.bias = vec->bias;
+    rv.bias_per_row = (d->vec_flags & TLB200_VEC_BIAS_M) ? 1 : 0;
+  }
   int dev;
   if (int rc = current_device_ready(&dev)) return rc;
   Resolved r;
@@ -992,6 +1020,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   cudaError_t e;
   if (d->k == 0) {  // empty contraction: C = 0 (T.clear semantics), in every destination
     if (d->epilogue & TLB200_EPI_ACCUMULATE) return 0;  // C += 0
+    if (rv.bias) return fail("tlb200_gemm_fused: k = 0 with a bias vector is not offered (C would be the broadcast bias)");
     const int blocks = 148 * 4;
     for (int g = -1; g < n_peer; ++g) {
       void* dst = g < 0 ? c : peers[g];
@@ -1132,6 +1161,9 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.accumulate = (!split && (d->epilogue & TLB200_EPI_ACCUMULATE)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
   kp.l2_policy = d->reserved[2];
+  if (!split) {  // with split-K the reduction kernel applies them to the summed slices
+    kp.row_scale = rv.row_scale; kp.col_scale = rv.col_scale; kp.bias = rv.bias; kp.bias_per_row = rv.bias_per_row;
+  }
 #ifdef TLB200_TRACE
   kp.trace = g_trace;
 #endif
@@ -1160,17 +1192,35 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   g_launches++;
   if (tail) {
     if (int rc = launch_tail_reduce(static_cast<const float*>(kp.ws), r, pl, c, d->ldc, d->m, d->n, d->alpha,
-                                    (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream))
+                                    (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream, rv))
       return rc;
     g_launches++;
   }
   if (split) {
     if (int rc = launch_splitk_reduce(static_cast<const float*>(ws), r.ws_ld, r.m_pad, r.split_k, c, d->ldc, d->m, d->n, d->alpha,
-                                      (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream))
+                                      (d->epilogue & TLB200_EPI_RELU) != 0, (d->epilogue & TLB200_EPI_ACCUMULATE) != 0, out_kind, stream, rv))
       return rc;
     g_launches++;
   }
   return 0;
+}
+
+int tlb200_gemm_fused(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, const tlb200_epilogue_vectors* vec,
+                      void* ws, int64_t ws_bytes, void* stream_v) {
+  if (!d) return fail("tlb200_gemm_fused: null descriptor");
+  if (ws && ws_bytes < 0) return fail("tlb200_gemm_fused: negative workspace size");
+  const uint32_t f = d->vec_flags;
+  if (f && !vec) return fail("tlb200_gemm_fused: vec_flags = 0x%x but no vector struct was given", f);
+  if ((f & TLB200_VEC_BIAS_N) && (f & TLB200_VEC_BIAS_M)) return fail("tlb200_gemm_fused: a bias is per column or per row, not both");
+  if (f && d->c_dtype == TLB200_INT32) return fail("tlb200_gemm_fused: epilogue vectors are not offered for int32 output");
+  if (f && (d->epilogue & TLB200_EPI_ACCUMULATE)) return fail("tlb200_gemm_fused: epilogue vectors cannot be combined with TLB200_EPI_ACCUMULATE");
+  if (vec) {
+    const void* ptrs[3] = {(f & TLB200_VEC_ROW_SCALE) ? vec->row_scale : (const float*)16, (f & TLB200_VEC_COL_SCALE) ? vec->col_scale : (const float*)16,
+                           (f & (TLB200_VEC_BIAS_N | TLB200_VEC_BIAS_M)) ? vec->bias : (const float*)16};
+    for (const void* p : ptrs)
+      if (!p || reinterpret_cast<uintptr_t>(p) % 4) return fail("tlb200_gemm_fused: a vector named in vec_flags is null or not 4-byte aligned");
+  }
+  return gemm_impl(d, a, b, c, ws, ws_bytes, stream_v, nullptr, 0, nullptr, 0, f ? vec : nullptr);
 }
 
 int tlb200_gemm(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* stream_v) {

@@ -72,7 +72,7 @@ def _row_pitch(t: torch.Tensor, name: str) -> int:
 
 def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha=1.0, relu=False,
               cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0, split_k=0, l2_policy=0,
-              accumulate=False) -> _abi.GemmDesc:
+              accumulate=False, vec_flags=0) -> _abi.GemmDesc:
     d = _abi.GemmDesc()
     d.abi_version = _abi.ABI_VERSION
     d.m, d.n, d.k = int(m), int(n), int(k)
@@ -86,13 +86,24 @@ def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha
     d.reserved[0] = int(epi_warps)
     d.reserved[1] = int(split_k)
     d.reserved[2] = int(l2_policy)
+    d.vec_flags = int(vec_flags)
     return d
+
+
+def _vector(v, n, name, device):
+    if not isinstance(v, torch.Tensor) or v.dtype != torch.float32 or v.dim() != 1 or v.numel() != n or v.device != device:
+        raise ValueError(f"gemm: {name} must be a float32 vector of {n} elements on {device}")
+    return v if v.is_contiguous() else v.contiguous()
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, trans_a: bool = False,
          trans_b: bool = True, out_dtype: Optional[torch.dtype] = None, alpha: float = 1.0,
-         relu: bool = False, **cfg) -> torch.Tensor:
+         relu: bool = False, row_scale: Optional[torch.Tensor] = None, col_scale: Optional[torch.Tensor] = None,
+         bias: Optional[torch.Tensor] = None, bias_per_row: bool = False, **cfg) -> torch.Tensor:
     """C = alpha * op(A) @ op(B) with fp32 accumulation on the tcgen05 path.
+
+    ``row_scale`` [M], ``col_scale`` [N] and ``bias`` ([N], or [M] with ``bias_per_row``) are float32 vectors fused
+    into the epilogue: C = cast(relu?(((alpha * acc) * row_scale[m]) * col_scale[n] + bias)) (tlb200_gemm_fused).
 
     ``trans_a`` / ``trans_b`` have T.gemm's meaning (tilelang/language/gemm.py:105-116):
     A is [K, M] if trans_a else [M, K]; B is [N, K] if trans_b else [K, N].
@@ -137,12 +148,21 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
         _ensure_init(dev)
     # Descriptor + workspace size are cached per problem signature: filling ~25 ctypes fields and a plan query cost
     # more host time than a small contraction takes on the GPU.
-    key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, tuple(sorted(cfg.items())) if cfg else ())
+    vec_flags = 0
+    if row_scale is not None or col_scale is not None or bias is not None:
+        if row_scale is not None:
+            row_scale, vec_flags = _vector(row_scale, m, "row_scale", a.device), vec_flags | _abi.VEC_ROW_SCALE
+        if col_scale is not None:
+            col_scale, vec_flags = _vector(col_scale, n, "col_scale", a.device), vec_flags | _abi.VEC_COL_SCALE
+        if bias is not None:
+            bias = _vector(bias, m if bias_per_row else n, "bias", a.device)
+            vec_flags |= _abi.VEC_BIAS_M if bias_per_row else _abi.VEC_BIAS_N
+    key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, vec_flags, tuple(sorted(cfg.items())) if cfg else ())
     hit = _desc_cache.get(key)
     lib = _lib or _load_lib()
     if hit is None:
         desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, lda, ldb,
-                         ldc, alpha, relu, **cfg)
+                         ldc, alpha, relu, vec_flags=vec_flags, **cfg)
         need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc))
         if need < 0:
             _abi.check(-1, "tlb200_gemm_workspace_bytes")
@@ -155,7 +175,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
         torch.cuda.set_device(dev)
     try:
         stream = torch._C._cuda_getCurrentRawStream(dev)
-        if need > 0:  # split-K partial sums and/or re-pitched copies of operands TMA cannot address
+        if vec_flags:
+            vec = _abi.EpilogueVectors(row_scale.data_ptr() if row_scale is not None else None,
+                                       col_scale.data_ptr() if col_scale is not None else None,
+                                       bias.data_ptr() if bias is not None else None)
+            ws = _workspace(dev, stream, need) if need > 0 else None
+            rc = lib.tlb200_gemm_fused(desc_ref, a.data_ptr(), b.data_ptr(), c.data_ptr(), ctypes.byref(vec),
+                                       ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0, stream)
+        elif need > 0:  # split-K partial sums and/or re-pitched copies of operands TMA cannot address
             ws = _workspace(dev, stream, need)
             rc = lib.tlb200_gemm_ex(desc_ref, a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         else:
