@@ -165,3 +165,34 @@ def test_product_does_not_import_oracle():
                 txt = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
                 assert "oracle/" not in txt or f == "README.md", f
+
+
+def test_plan_cache_roundtrip_and_lookup(tmp_path, monkeypatch):
+    """Measured plans persist as JSON and are found again by problem signature (tilelang/autotuner/tuner.py:281-287,
+    tilelang/cache/kernel_cache.py:69-113 persist tuned configs the same way)."""
+    from tilelang_mesh_b200 import plan_cache as PC
+    path = tmp_path / "plans.json"
+    monkeypatch.setenv("TLB200_PLAN_CACHE", str(path))
+    PC.reset()
+    assert PC.lookup(148, 512, 2048, 4096, torch.bfloat16, torch.bfloat16, False, True) is None or True  # shipped table may hold it
+    k = PC.key(777, 2048, 4096, torch.bfloat16, torch.bfloat16, False, True)
+    assert k == "777x2048x4096|bf16->bf16|NT"
+    PC.store(148, k, {"cfg": {"cta_group": 2, "block_n": 64, "split_k": 1}, "us": 41.5, "auto_us": 45.0, "candidates": 30})
+    assert PC.lookup(148, 777, 2048, 4096, torch.bfloat16, torch.bfloat16, False, True) == {"cta_group": 2, "block_n": 64, "split_k": 1}
+    assert PC.lookup(148, 777, 2048, 4096, torch.float8_e4m3fn, torch.bfloat16, False, True) is None
+    assert PC.lookup(132, 777, 2048, 4096, torch.bfloat16, torch.bfloat16, False, True) is None or True
+    import json
+    assert json.load(open(path))[k]["us"] == 41.5
+    monkeypatch.setenv("TLB200_PLAN_CACHE", "off")
+    PC.reset()
+    assert PC.lookup(148, 777, 2048, 4096, torch.bfloat16, torch.bfloat16, False, True) is None
+    # every plan of the search space is a legal descriptor or is rejected with a message (never crashes)
+    n_ok = 0
+    for cfg in PC.plan_space(512, 2048, 4096, 2):
+        try:
+            G.plan(512, 2048, 4096, **cfg)
+            n_ok += 1
+        except RuntimeError:
+            pass
+    assert n_ok >= 10
+    PC.reset()

@@ -91,6 +91,25 @@ class AutoTuner:
                 last = e
         raise RuntimeError(f"autotune: no config yields a valid GEMM tile program (last error: {last})")
 
+    @staticmethod
+    def _persist(kernel, latency_ms, hints):
+        """What the reference does with `save_to_disk` (tuner.py:281-287): the winning plan of this problem goes into
+        the persisted plan table, where every later `gemm` of the same problem finds it (plan_cache.py)."""
+        import torch
+
+        from .. import plan_cache
+        from ..program import GemmProgram
+        from ..utils.tensor import map_torch_type
+        p = getattr(kernel, "program", None)
+        if not isinstance(p, GemmProgram) or latency_ms is None or not hints:
+            return
+        try:
+            sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+            k = plan_cache.key(p.M, p.N, p.K, map_torch_type(p.in_dtype), map_torch_type(p.out_dtype), p.trans_A, p.trans_B)
+            plan_cache.store(sm, k, {"cfg": dict(hints), "us": round(latency_ms * 1e3, 2), "auto_us": None, "candidates": len(PLAN_CANDIDATES)})
+        except OSError as e:  # a read-only home directory must not break tuning
+            logger.debug("autotune: could not persist the plan: %s", e)
+
     def _tune(self, args, kwargs):
         key = (args, tuple(sorted(kwargs.items())))
         if key in self._cache:
@@ -119,6 +138,7 @@ class AutoTuner:
                     prof.assert_allclose(self.ref_prog, input_tensors=ins, rtol=self.rtol, atol=self.atol,
                                          max_mismatched_ratio=self.max_mismatched_ratio)
             kernel.update_tuner_result(best, dict(cfg, backend_plan=best_hints), ref_lat)
+            self._persist(kernel, best, best_hints)
         else:
             kernel.update_tuner_result(None, dict(cfg), None)
         self._cache[key] = kernel

@@ -10,11 +10,22 @@ PyTorch is plumbing only (memory + streams); the arithmetic is the CUDA kernel.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
 
-from . import _abi
+from . import _abi, plan_cache
+
+_PLAN_HINTS = {"cta_group", "block_n", "stages", "raster", "split_k", "epi_warps", "epilogue"}
+_sm_counts = {}
+
+
+def _sm_count(dev: int) -> int:
+    n = _sm_counts.get(dev)
+    if n is None:
+        n = _sm_counts[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
+    return n
 
 _TORCH2TLB = {
     torch.float16: _abi.FLOAT16,
@@ -157,12 +168,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
         if bias is not None:
             bias = _vector(bias, m if bias_per_row else n, "bias", a.device)
             vec_flags |= _abi.VEC_BIAS_M if bias_per_row else _abi.VEC_BIAS_N
-    key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, vec_flags, tuple(sorted(cfg.items())) if cfg else ())
+    key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, vec_flags, tuple(sorted(cfg.items())) if cfg else (),
+           "TLB200_PLAN_CACHE_BYPASS" in os.environ)
     hit = _desc_cache.get(key)
     lib = _lib or _load_lib()
     if hit is None:
+        plan_cfg = cfg
+        if not (_PLAN_HINTS & cfg.keys()) and "TLB200_PLAN_CACHE_BYPASS" not in os.environ:
+            # no hints from the caller: a measured, persisted plan for this problem wins over the cycle model
+            tuned = plan_cache.lookup(_sm_count(dev), m, n, ka, a.dtype, c.dtype, trans_a, trans_b)
+            if tuned:
+                plan_cfg = dict(cfg, **tuned)
         desc = make_desc(m, n, ka, _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], trans_a, trans_b, lda, ldb,
-                         ldc, alpha, relu, vec_flags=vec_flags, **cfg)
+                         ldc, alpha, relu, vec_flags=vec_flags, **plan_cfg)
         need = lib.tlb200_gemm_workspace_bytes(ctypes.byref(desc))
         if need < 0:
             _abi.check(-1, "tlb200_gemm_workspace_bytes")

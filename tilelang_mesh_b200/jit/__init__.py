@@ -172,7 +172,7 @@ class JITKernel:
         if isinstance(p, BlockScaledProgram):  # fixed plan: tlb200_gemm_blockscaled's default (tlb200.cu)
             sms = torch.cuda.get_device_properties(0).multi_processor_count if torch.cuda.is_available() else 148
             bn = self.tile_hints.get("block_n") or (128 if p.N <= 128 or -(-p.M // 128) * -(-p.N // 256) < sms else 256)
-            cg = self.tile_hints.get("cta_group") or 1
+            cg = self.tile_hints.get("cta_group") or (2 if bn == 256 and p.M > 128 and -(-p.M // 256) * -(-p.N // bn) >= sms // 2 else 1)
             return dict(kernel="gemm_blockscaled_kernel", cta_group=cg, block_m=128 * cg, block_n=bn, block_k=128,
                         tiles_m=-(-p.M // (128 * cg)), tiles_n=-(-p.N // bn), grid=1, threads=384, tmem_cols=2 * bn)
         return G.plan(p.M, p.N, p.K, map_torch_type(p.in_dtype), map_torch_type(p.out_dtype), p.trans_A, p.trans_B,
