@@ -426,7 +426,8 @@ def test_launches_on_callers_stream_and_counts():
     assert lib.tlb200_launch_count() == n0 + 2
 
 
-@pytest.mark.parametrize("m,n,k", [(512, 384, 256), (4100, 640, 320)], ids=["one_panel", "row_panels"])
+@pytest.mark.parametrize("m,n,k", [(512, 384, 256), (4100, 640, 320), (4100, 2600, 320), (2048, 9000, 64)],
+                         ids=["one_panel", "row_panels", "a_and_b_panels_alternate", "many_b_panels"])
 def test_host_buffer_entry_point(m, n, k):
     a = torch.randint(-3, 4, (m, k)).float().bfloat16().pin_memory()
     b = torch.randint(-3, 4, (n, k)).float().bfloat16().pin_memory()

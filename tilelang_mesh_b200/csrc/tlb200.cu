@@ -53,7 +53,7 @@ std::atomic<int> g_sm_count[kMaxDevices];   // zero-initialised (static storage)
 std::atomic<bool> g_dev_ready[kMaxDevices];
 // Host-buffer path: per device one copy-in and one copy-out stream plus an event ring, created at
 // init (streams/events are driver objects, not device memory; the library still allocates none).
-constexpr int kMaxPanels = 16;
+constexpr int kMaxPanels = 32;  // arrivals per call: two operands x up to 16 panels
 struct HostPipe {
   cudaStream_t in = nullptr, out = nullptr;
   cudaEvent_t fork = nullptr, loaded[kMaxPanels] = {}, done[kMaxPanels] = {}, drained = nullptr;
@@ -1502,57 +1502,97 @@ int tlb200_gemm_host(const tlb200_gemm_desc* d, const void* ha, const void* hb, 
   HostPipe& hp = g_pipe[dev];
   cudaError_t e;
 #define TLB_CK(call, what) do { if ((e = (call)) != cudaSuccess) return fail("tlb200_gemm_host: %s: %s", what, cudaGetErrorString(e)); } while (0)
-  // Everything is ordered after the caller's stream; B (needed by every panel) goes first.
+  // Everything is ordered after the caller's stream.
   TLB_CK(cudaEventRecord(hp.fork, stream), "fork");
   TLB_CK(cudaStreamWaitEvent(hp.in, hp.fork, 0), "fork");
   TLB_CK(cudaStreamWaitEvent(hp.out, hp.fork, 0), "fork");
-  // an operand whose host pitch TMA cannot address is re-pitched by the copy itself
-  if (bb) {
-    if (ldb_d == d->ldb) {
-      TLB_CK(cudaMemcpyAsync(db, hb, bb, cudaMemcpyHostToDevice, hp.in), "H2D B");
+  // Shrinking panels: about a third of what remains, between 256 and 2048 rows (8192 rows go as 2048, 2048, 1408, 896,
+  // 640, 384, 256, 256, 256), so that what can only start when the last input byte has arrived is small.
+  auto cut = [](int total, int* rows) {
+    int n = 0, rem = total;
+    while (rem > 0 && n < kMaxPanels / 2 - 1) {
+      int r = (rem / 3 + 127) / 128 * 128;
+      r = r < 256 ? 256 : (r > 2048 ? 2048 : r);
+      if (r > rem) r = rem;
+      rows[n++] = r;
+      rem -= r;
+    }
+    if (rem > 0) rows[n++] = rem;
+    return n;
+  };
+  auto h2d_rows = [&](char* dst, long long ld_d, const void* src, long long ld_h, long long r0, long long rows, long long cols,
+                      const char* what) -> cudaError_t {
+    (void)what;
+    const char* hs = static_cast<const char*>(src) + r0 * ld_h * es;
+    char* ds = dst + r0 * ld_d * es;
+    // an operand whose host pitch TMA cannot address is re-pitched by the copy itself
+    if (ld_d == ld_h) return cudaMemcpyAsync(ds, hs, extent_bytes(rows, cols, ld_d, es), cudaMemcpyHostToDevice, hp.in);
+    return cudaMemcpy2DAsync(ds, ld_d * es, hs, ld_h * es, cols * es, rows, cudaMemcpyHostToDevice, hp.in);
+  };
+  int ev = 0;  // arrival number: loaded[ev] / done[ev]
+  auto multiply = [&](const tlb200_gemm_desc& pd, long long a_off, long long b_off, long long c_off, long long rows, long long cols) -> int {
+    TLB_CK(cudaEventRecord(hp.loaded[ev], hp.in), "record");
+    TLB_CK(cudaStreamWaitEvent(stream, hp.loaded[ev], 0), "wait");
+    if (int rc = tlb200_gemm(&pd, da + a_off, db + b_off, dc + c_off, stream_v)) return rc;
+    TLB_CK(cudaEventRecord(hp.done[ev], stream), "record");
+    TLB_CK(cudaStreamWaitEvent(hp.out, hp.done[ev], 0), "wait");
+    if (cols == d->n && d->ldc == d->n) {
+      TLB_CK(cudaMemcpyAsync(static_cast<char*>(hc) + c_off, dc + c_off, extent_bytes(rows, cols, d->ldc, ob), cudaMemcpyDeviceToHost, hp.out), "D2H C");
     } else {
-      TLB_CK(cudaMemcpy2DAsync(db, ldb_d * es, hb, d->ldb * es, b_cols * es, b_rows, cudaMemcpyHostToDevice, hp.in), "H2D B");
+      TLB_CK(cudaMemcpy2DAsync(static_cast<char*>(hc) + c_off, d->ldc * ob, dc + c_off, d->ldc * ob, cols * ob, rows, cudaMemcpyDeviceToHost, hp.out), "D2H C");
     }
-  }
-  // Row panels of A / C (contiguous when A is [M,K]): panel p+1 is copied in while panel p is
-  // multiplied and panel p-1 is copied out, so PCIe runs in both directions under the GEMM.
-  int panels = 1;
-  if (!d->trans_a && d->k > 0) {
-    panels = d->m / 1024;
-    if (panels > kMaxPanels) panels = kMaxPanels;
-    if (panels < 1) panels = 1;
-  }
-  const int rows_per = ((d->m + panels - 1) / panels + 127) / 128 * 128;
-  int p = 0;
-  for (int r0 = 0; r0 < d->m; r0 += rows_per, ++p) {
-    const int rows = (d->m - r0 < rows_per) ? d->m - r0 : rows_per;
-    tlb200_gemm_desc pd = *d;
-    pd.lda = lda_d;
-    pd.ldb = ldb_d;
-    long long a_off = 0, a_off_h = 0, a_bytes = ab, a_rows_p = a_rows;
-    if (panels > 1) {
-      pd.m = rows;
-      a_off = static_cast<long long>(r0) * lda_d * es;
-      a_off_h = static_cast<long long>(r0) * d->lda * es;
-      a_bytes = extent_bytes(rows, d->k, lda_d, es);
-      a_rows_p = rows;
-    }
-    const long long c_off = static_cast<long long>(r0) * d->ldc * ob;
-    const long long c_bytes = extent_bytes(rows, d->n, d->ldc, ob);
-    if (d->k > 0 && a_bytes) {
-      if (lda_d == d->lda) {
-        TLB_CK(cudaMemcpyAsync(da + a_off, static_cast<const char*>(ha) + a_off_h, a_bytes, cudaMemcpyHostToDevice, hp.in), "H2D A");
-      } else {
-        TLB_CK(cudaMemcpy2DAsync(da + a_off, lda_d * es, static_cast<const char*>(ha) + a_off_h, d->lda * es, a_cols * es, a_rows_p,
-                                 cudaMemcpyHostToDevice, hp.in), "H2D A");
+    ++ev;
+    return 0;
+  };
+  if (!d->trans_a && d->trans_b && d->k > 0 && d->m >= 2048 && d->n >= 2048) {
+    // A[M,K] and B[N,K], both cut into row panels that arrive ALTERNATELY (A0, B0, A1, B1, ...).  With a fraction t of
+    // each operand on the device a fraction t*t of C can be formed, so products - and their way back over PCIe - start
+    // after the first pair of panels instead of after all of B: both directions of the link stay busy almost from the
+    // start and the copy out never becomes a tail of its own.  Every arrival triggers ONE rectangular product with
+    // everything of the other operand that is already there: A_i x B[0:y)^T -> C[rows_i, 0:y), B_j x A[0:x)^T ->
+    // C[0:x, cols_j).
+    int ra[kMaxPanels / 2], rb[kMaxPanels / 2];
+    const int na = cut(d->m, ra), nb = cut(d->n, rb);
+    long long x = 0, y = 0;  // rows of A / B on the device
+    for (int i = 0, j = 0; i < na || j < nb;) {
+      if (i < na && (x <= y || j >= nb)) {  // next A panel
+        TLB_CK(h2d_rows(da, lda_d, ha, d->lda, x, ra[i], d->k, "H2D A"), "H2D A");
+        if (y > 0) {
+          tlb200_gemm_desc pd = *d;
+          pd.lda = lda_d; pd.ldb = ldb_d; pd.m = ra[i]; pd.n = static_cast<int>(y);
+          if (int rc = multiply(pd, x * lda_d * es, 0, x * d->ldc * ob, ra[i], y)) return rc;
+        }
+        x += ra[i++];
+      } else {                               // next B panel
+        TLB_CK(h2d_rows(db, ldb_d, hb, d->ldb, y, rb[j], d->k, "H2D B"), "H2D B");
+        if (x > 0) {
+          tlb200_gemm_desc pd = *d;
+          pd.lda = lda_d; pd.ldb = ldb_d; pd.m = static_cast<int>(x); pd.n = rb[j];
+          if (int rc = multiply(pd, 0, y * ldb_d * es, y * ob, x, rb[j])) return rc;
+        }
+        y += rb[j++];
       }
     }
-    TLB_CK(cudaEventRecord(hp.loaded[p], hp.in), "record");
-    TLB_CK(cudaStreamWaitEvent(stream, hp.loaded[p], 0), "wait");
-    if (int rc = tlb200_gemm(&pd, da + a_off, db, dc + c_off, stream_v)) return rc;
-    TLB_CK(cudaEventRecord(hp.done[p], stream), "record");
-    TLB_CK(cudaStreamWaitEvent(hp.out, hp.done[p], 0), "wait");
-    TLB_CK(cudaMemcpyAsync(static_cast<char*>(hc) + c_off, dc + c_off, c_bytes, cudaMemcpyDeviceToHost, hp.out), "D2H C");
+  } else {
+    // Other layouts: B (needed by every panel) goes first, then row panels of A / C when A is [M,K]: panel p+1 is copied
+    // in while panel p is multiplied and panel p-1 is copied out.
+    if (bb) TLB_CK(h2d_rows(db, ldb_d, hb, d->ldb, 0, b_rows, b_cols, "H2D B"), "H2D B");
+    int rows_of[kMaxPanels];
+    int panels = 1;
+    rows_of[0] = d->m;
+    if (!d->trans_a && d->k > 0 && d->m >= 2048) panels = cut(d->m, rows_of);
+    long long r0 = 0;
+    for (int p = 0; p < panels; r0 += rows_of[p], ++p) {
+      tlb200_gemm_desc pd = *d;
+      pd.lda = lda_d; pd.ldb = ldb_d;
+      if (panels > 1) {
+        pd.m = rows_of[p];
+        if (d->k > 0) TLB_CK(h2d_rows(da, lda_d, ha, d->lda, r0, rows_of[p], d->k, "H2D A"), "H2D A");
+      } else if (d->k > 0 && ab) {
+        TLB_CK(h2d_rows(da, lda_d, ha, d->lda, 0, a_rows, a_cols, "H2D A"), "H2D A");
+      }
+      if (int rc = multiply(pd, panels > 1 ? r0 * lda_d * es : 0, 0, r0 * d->ldc * ob, pd.m, d->n)) return rc;
+    }
   }
   TLB_CK(cudaEventRecord(hp.drained, hp.out), "record");
   TLB_CK(cudaStreamWaitEvent(stream, hp.drained, 0), "join");

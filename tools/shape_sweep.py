@@ -1,14 +1,14 @@
 """Automatic plan vs cuBLAS over a grid of shapes (bf16 and fp8), flush-timed medians + back-to-back rate.
-Output lines go to profiles/shape_sweep_r1.txt."""
+Output lines go to profiles/shape_sweep_rN.txt."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from tilelang_mesh_b200 import gemm as G
 
-shapes = [(256, 256, 256), (512, 512, 512), (1024, 1024, 1024), (2048, 2048, 2048), (4096, 4096, 4096), (8192, 8192, 8192),
+shapes = [(512, 2048, 4096), (2048, 512, 8192), (256, 256, 256), (512, 512, 512), (1024, 1024, 1024), (2048, 2048, 2048), (4096, 4096, 4096), (8192, 8192, 8192),
           (16384, 14336, 4096), (16384, 4096, 14336), (1024, 4096, 4096), (128, 4096, 14336), (64, 8192, 8192),
           (16, 4096, 4096), (256, 256, 16384), (2048, 512, 8192), (4096, 7168, 2048), (8192, 1024, 8192), (1000, 3000, 5000)]
-flush = torch.empty(256 << 20, dtype=torch.int8, device="cuda")
+flush = torch.empty(512 << 20, dtype=torch.int8, device="cuda")  # read, not written: no dirty lines left in L2
 
 
 def med(fn, n=9):
@@ -16,7 +16,7 @@ def med(fn, n=9):
         fn()
     ts = []
     for _ in range(n):
-        flush.zero_()
+        _ = flush.view(torch.int64).sum()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
@@ -56,6 +56,6 @@ for (m, n, k) in shapes:
         except Exception as e:  # noqa: BLE001
             t_ref = tb_ref = float("nan")
         t, tb = med(mine), b2b(mine)
-        p = G.plan(m, n, k, a.dtype, torch.bfloat16)
+        p = G.plan_for(a, b, c)
         print(f"{str((m, n, k)):>22s} {dt:>5s} | {fl / t:7.0f} {fl / t_ref:7.0f} {t_ref / t:5.2f} | {fl / tb:8.0f} {fl / tb_ref:10.0f} | "
               f"{(p['cta_group'], p['block_n'], p['split_k'])}", flush=True)
