@@ -235,6 +235,34 @@ typedef struct tlb200_blockscaled_desc {
 int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* desc, const void* a, const void* b, void* c,
                             const float* scales_a, const float* scales_b, void* stream);
 
+/* Two contractions back to back, the intermediate kept in tensor memory (the "TS" operand mode:
+ * the A operand of the second tcgen05.mma comes from TMEM).  The reference declares the instruction wrapper
+ * `tl::tcgen05mma_ts` (src/tl_templates/cuda/instruction/tcgen05mma.h:26-133) and the emitter hook
+ * (tilelang/intrinsics/tcgen05_macro_generator.py:147-148) but leaves `tcgen5mma_gemm_ts` a TODO
+ * (src/tl_templates/cuda/gemm_sm100.h:419-424); this is that operand mode as a whole-problem call:
+ *
+ *   P[M, N1] = cast_ab(relu?(alpha1 * A[M, K] . B1[N1, K]^T))     fp32 accumulate, ONE rounding to the operand type
+ *   D[M, N2] = cast_c (alpha2 * P[M, N1] . B2[N2, N1]^T)          fp32 accumulate, ONE rounding
+ *
+ * i.e. exactly what two tlb200_gemm calls with an intermediate of the operand type compute (and what the oracle
+ * checks), without the intermediate ever leaving the SM: attention's S = Q K^T -> O = P V step without the softmax,
+ * or a low-rank product x A^T B^T.  A, B1, B2 are K-contiguous float16 or bfloat16 (B2 is [N2, N1]); N1 is a
+ * multiple of 64 and at most 256 (the intermediate of a 128-row tile must fit TMEM beside its fp32 source and one
+ * output accumulator); 16-byte aligned bases and row pitches; C float16 / bfloat16 / float32, any ldc. */
+typedef struct tlb200_chain_desc {
+  int32_t abi_version; /* must be TLB200_ABI_VERSION */
+  int32_t m, k, n1, n2;
+  int32_t ab_dtype;    /* TLB200_FLOAT16 or TLB200_BFLOAT16 (A, B1, B2 and the intermediate) */
+  int32_t c_dtype;     /* TLB200_FLOAT16, TLB200_BFLOAT16 or TLB200_FLOAT32 */
+  int32_t relu_mid;    /* 1: relu on the intermediate before it is rounded */
+  int64_t lda, ldb1, ldb2, ldc; /* row pitches in elements */
+  float alpha1, alpha2;
+  int32_t cfg_stages;  /* 0 auto */
+  int32_t reserved[3]; /* must be 0 */
+} tlb200_chain_desc;
+
+int tlb200_gemm_chain(const tlb200_chain_desc* desc, const void* a, const void* b1, const void* b2, void* c, void* stream);
+
 /* No counterpart in the reference: an allocation-free form of tlb200_gemm_ex.
  *
  * Who needs it: callers that are handed tensor pointers and a stream and nothing

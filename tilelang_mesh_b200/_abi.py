@@ -56,6 +56,15 @@ class EpilogueVectors(ctypes.Structure):
 VEC_ROW_SCALE, VEC_COL_SCALE, VEC_BIAS_N, VEC_BIAS_M = 1, 2, 4, 8
 
 
+class ChainDesc(ctypes.Structure):
+    """tlb200_chain_desc (include/tlb200.h)."""
+    _fields_ = [("abi_version", ctypes.c_int32), ("m", ctypes.c_int32), ("k", ctypes.c_int32), ("n1", ctypes.c_int32),
+                ("n2", ctypes.c_int32), ("ab_dtype", ctypes.c_int32), ("c_dtype", ctypes.c_int32), ("relu_mid", ctypes.c_int32),
+                ("lda", ctypes.c_int64), ("ldb1", ctypes.c_int64), ("ldb2", ctypes.c_int64), ("ldc", ctypes.c_int64),
+                ("alpha1", ctypes.c_float), ("alpha2", ctypes.c_float), ("cfg_stages", ctypes.c_int32),
+                ("reserved", ctypes.c_int32 * 3)]
+
+
 class GemmPlan(ctypes.Structure):
     _fields_ = [
         ("cta_group", ctypes.c_int32),
@@ -109,6 +118,7 @@ SYMBOLS = {
                                          ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_void_p]),
     "tlb200_gemm_blockscaled": (ctypes.c_int, [ctypes.POINTER(BlockScaledDesc), ctypes.c_void_p, ctypes.c_void_p,
                                                ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "tlb200_gemm_chain": (ctypes.c_int, [ctypes.POINTER(ChainDesc)] + [ctypes.c_void_p] * 5),
     "tlb200_gemm_static_scratch": (ctypes.c_int, [ctypes.POINTER(GemmDesc), ctypes.c_void_p, ctypes.c_void_p,
                                                   ctypes.c_void_p, ctypes.c_void_p]),
     "tlb200_gemm_host_workspace_bytes": (ctypes.c_int64, [ctypes.POINTER(GemmDesc)]),

@@ -17,8 +17,8 @@ LIB_DIR = os.path.join(_HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libtlb200.so")
 # the host side plus one translation unit per group of kernel instantiations: compiled in parallel, linked once
 SOURCES = [os.path.join(CSRC, f) for f in ("tlb200.cu", "kernels_cg1_ns1.cu", "kernels_cg1_ns2.cu", "kernels_cg2_ns1.cu",
-                                           "kernels_cg2_ns2.cu", "kernels_mc.cu", "kernels_blockscaled.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, f) for f in ("gemm_sm100.cuh", "gemm_blockscaled_sm100.cuh", "ptx.cuh", "kernel_table.h")] + [
+                                           "kernels_cg2_ns2.cu", "kernels_mc.cu", "kernels_blockscaled.cu", "kernels_chain.cu")]
+DEPS = SOURCES + [os.path.join(CSRC, f) for f in ("gemm_sm100.cuh", "gemm_blockscaled_sm100.cuh", "gemm_chain_sm100.cuh", "ptx.cuh", "kernel_table.h")] + [
     os.path.join(ROOT, "include", "tlb200.h")]
 OBJ_DIR = os.path.join(LIB_DIR, "obj")
 

@@ -333,6 +333,19 @@ __device__ __forceinline__ void epi_stage(const EpiCtx& e, int cs, const uint4 (
         asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(gptr + static_cast<long long>(j) * 4 * row_bytes),
                      "r"(v[j].x), "r"(v[j].y), "r"(v[j].z), "r"(v[j].w) : "memory");
     }
+    // Fused all-gather through the load/store unit: the same registers go to every peer GPU's C as full 128-byte lines
+    // (st.global reaches 701 GB/s per GPU over NVLink, bulk stores of 128-byte rows 669: profiles/nvlink_write_bw_r2.txt)
+    // and the TMA unit stays free for the operand loads.  Destinations are visited in an order rotated per CTA and slab.
+    for (int gi = 0; gi < o.n_peer; ++gi) {
+      const int g = (gi + static_cast<int>(blockIdx.x) + slab_iter) % o.n_peer;
+      char* pptr = gptr - reinterpret_cast<char*>(o.c) + reinterpret_cast<char*>(e.p.c_peer[g]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (col_ok && first_row + j * 4 + rsub < e.row_limit)
+          asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(pptr + static_cast<long long>(j) * 4 * row_bytes),
+                       "r"(v[j].x), "r"(v[j].y), "r"(v[j].z), "r"(v[j].w) : "memory");
+      }
+    }
     __syncwarp();  // the slab may be rewritten once every lane has its data in registers
     ++slab_iter;
     return;

@@ -2,11 +2,13 @@
 // library builds in parallel; the host side (tlb200.cu) reaches them through these getters.
 #pragma once
 #include "gemm_blockscaled_sm100.cuh"
+#include "gemm_chain_sm100.cuh"
 #include "gemm_sm100.cuh"
 
 namespace tlb200 {
 typedef void (*GemmKernelFn)(const GemmKernelParams);
 typedef void (*BlockScaledFn)(const BlockScaledParams);
+typedef void (*ChainFn)(const ChainParams);
 // gemm_tcgen05_kernel<cta_group, kind, accumulators per tile, 1>
 GemmKernelFn kernel_cg1_ns1(int kind);
 GemmKernelFn kernel_cg1_ns2(int kind);
@@ -16,4 +18,6 @@ GemmKernelFn kernel_cg2_ns2(int kind);
 GemmKernelFn kernel_mc(int kind);
 // gemm_blockscaled_kernel<cta_group, block_n>
 BlockScaledFn kernel_blockscaled(int cg, int bn);
+// gemm_chain_kernel
+ChainFn kernel_chain();
 }  // namespace tlb200

@@ -691,6 +691,7 @@ std::array<const void*, 20> all_kernels() {
 }
 
 BlockScaledFn pick_blockscaled(int cg, int bn) { return kernel_blockscaled(cg, bn); }
+constexpr int kChainSmemFixed = 1024 + (2 * kMaxStages + 8) * 8 + 16;
 
 int out_kind_of(int dt) {
   switch (dt) {
@@ -948,6 +949,8 @@ int tlb200_init(int device) {
       for (int bn = 128; bn <= 256 && e == cudaSuccess; bn += 128)
         e = cudaFuncSetAttribute(reinterpret_cast<const void*>(pick_blockscaled(cg, bn)),
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(reinterpret_cast<const void*>(kernel_chain()), cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (e != cudaSuccess) {
       rc = fail("tlb200_init: failed to set the allowed dynamic shared memory size to %d with error: %s", kSmemLimit, cudaGetErrorString(e));
       break;
@@ -1156,7 +1159,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   kp.out_kind = split ? static_cast<int>(kOutF32) : out_kind;
   kp.acc_int = d->ab_dtype == TLB200_INT8;
   kp.epi_tma = split ? ws_tma : r.epi_tma;
-  kp.epi_lsu = (!split && r.epi_lsu && n_peer == 0) ? 1 : 0;
+  kp.epi_lsu = (!split && r.epi_lsu) ? 1 : 0;
   kp.relu = (!split && (d->epilogue & TLB200_EPI_RELU)) ? 1 : 0;
   kp.accumulate = (!split && (d->epilogue & TLB200_EPI_ACCUMULATE)) ? 1 : 0;
   kp.alpha = split ? 1.0f : d->alpha;
@@ -1389,6 +1392,67 @@ int tlb200_gemm_blockscaled(const tlb200_blockscaled_desc* d, const void* a, con
   cudaError_t e = cudaLaunchKernelEx(&cfg, pick_blockscaled(cg, bn), kp);
   if (e != cudaSuccess)
     return fail("tlb200_gemm_blockscaled: launch failed: %s (grid=%d cluster=%d smem=%d)", cudaGetErrorString(e), grid, cg, smem);
+  g_launches++;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Two contractions back to back, the intermediate in tensor memory (gemm_chain_sm100.cuh).
+int tlb200_gemm_chain(const tlb200_chain_desc* d, const void* a, const void* b1, const void* b2, void* c, void* stream_v) {
+  g_err[0] = 0;
+  if (!d) return fail("tlb200_gemm_chain: null descriptor");
+  if (d->abi_version != TLB200_ABI_VERSION)
+    return fail("tlb200_gemm_chain: descriptor abi_version %d != library %d", d->abi_version, TLB200_ABI_VERSION);
+  if (d->reserved[0] || d->reserved[1] || d->reserved[2]) return fail("tlb200_gemm_chain: descriptor field reserved must be zero");
+  if (d->m < 0 || d->k < 0 || d->n1 < 0 || d->n2 < 0) return fail("tlb200_gemm_chain: negative extent");
+  if (d->ab_dtype != TLB200_FLOAT16 && d->ab_dtype != TLB200_BFLOAT16)
+    return fail("tlb200_gemm_chain: operands must be float16 or bfloat16 (got dtype %d)", d->ab_dtype);
+  if (d->c_dtype != TLB200_FLOAT16 && d->c_dtype != TLB200_BFLOAT16 && d->c_dtype != TLB200_FLOAT32)
+    return fail("tlb200_gemm_chain: output must be float16, bfloat16 or float32 (got dtype %d)", d->c_dtype);
+  if (d->n1 < 64 || d->n1 > 256 || d->n1 % 64)
+    return fail("tlb200_gemm_chain: n1 = %d; the intermediate width must be 64, 128, 192 or 256 (it lives in tensor memory)", d->n1);
+  if (d->lda < d->k || d->ldb1 < d->k || d->ldb2 < d->n1 || d->ldc < d->n2)
+    return fail("tlb200_gemm_chain: a row pitch is smaller than its row (lda=%lld ldb1=%lld ldb2=%lld ldc=%lld)", (long long)d->lda,
+                (long long)d->ldb1, (long long)d->ldb2, (long long)d->ldc);
+  if (d->m == 0 || d->n2 == 0) return 0;
+  if (!a || !b1 || !b2 || !c) return fail("tlb200_gemm_chain: null tensor pointer");
+  if ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b1) | reinterpret_cast<uintptr_t>(b2)) % 16 ||
+      (d->lda * 2) % 16 || (d->ldb1 * 2) % 16 || (d->ldb2 * 2) % 16)
+    return fail("tlb200_gemm_chain: A, B1, B2 must be 16-byte aligned with row pitches that are multiples of 16 bytes");
+  if (d->k == 0) return fail("tlb200_gemm_chain: k = 0 is not offered (the result would be all zeros)");
+  int dev;
+  if (int rc = current_device_ready(&dev)) return rc;
+  ChainParams kp;
+  memset(&kp, 0, sizeof(kp));
+  if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, d->lda, 64, kBlockM, "A[M,K]")) return rc;
+  if (int rc = encode_2d(&kp.tm_b1, d->ab_dtype, b1, d->n1, d->k, d->ldb1, 64, d->n1, "B1[N1,K]")) return rc;
+  if (int rc = encode_2d(&kp.tm_b2, d->ab_dtype, b2, d->n2, d->n1, d->ldb2, 64, kChainOWidth, "B2[N2,N1]")) return rc;
+  kp.c = c;
+  kp.ldc = d->ldc;
+  kp.m = d->m; kp.n1 = d->n1; kp.n2 = d->n2;
+  kp.kb1 = (d->k + 63) / 64;
+  kp.kb2 = d->n1 / 64;
+  kp.tiles_m = (d->m + kBlockM - 1) / kBlockM;
+  kp.tiles_n2 = (d->n2 + kChainOWidth - 1) / kChainOWidth;
+  const int max_stages = (kSmemLimit - kChainSmemFixed) / kChainStageBytes;
+  kp.stages = d->cfg_stages > 0 ? d->cfg_stages : max_stages;
+  if (kp.stages < 2 || kp.stages > max_stages || kp.stages > kMaxStages)
+    return fail("tlb200_gemm_chain: cfg_stages=%d out of range [2,%d]", kp.stages, max_stages);
+  kp.idesc1 = instr_desc_impl(kBlockM, d->n1, 16, d->ab_dtype, TLB200_FLOAT32, true, true, 1, 1);
+  kp.idesc2 = instr_desc_impl(kBlockM, kChainOWidth, 16, d->ab_dtype, TLB200_FLOAT32, true, true, 1, 1);
+  if (!kp.idesc1 || !kp.idesc2) return fail("tlb200_gemm_chain: cannot encode the instruction descriptors");
+  kp.desc_hi = static_cast<uint32_t>(smem_desc_impl(0, 0, 1024 >> 4, 0, 0, 2) >> 32);
+  kp.out_kind = out_kind_of(d->c_dtype);
+  kp.mid_bf16 = d->ab_dtype == TLB200_BFLOAT16;
+  kp.relu_mid = d->relu_mid != 0;
+  kp.alpha1 = d->alpha1; kp.alpha2 = d->alpha2;
+  int grid = g_sm_count[dev].load();
+  if (grid > kp.tiles_m) grid = kp.tiles_m;
+  const int smem = kChainSmemFixed + kp.stages * kChainStageBytes;
+  ChainFn chain = kernel_chain();
+  chain<<<grid, kChainThreads, smem, static_cast<cudaStream_t>(stream_v)>>>(kp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail("tlb200_gemm_chain: launch failed: %s (grid=%d smem=%d)", cudaGetErrorString(e), grid, smem);
   g_launches++;
   return 0;
 }

@@ -286,6 +286,38 @@ def gemm_blockscaled(a: torch.Tensor, b: torch.Tensor, scales_a: torch.Tensor, s
     return c
 
 
+def gemm_chain(a: torch.Tensor, b1: torch.Tensor, b2: torch.Tensor, c: Optional[torch.Tensor] = None, *,
+               out_dtype: Optional[torch.dtype] = None, alpha1: float = 1.0, alpha2: float = 1.0, relu_mid: bool = False,
+               stages: int = 0) -> torch.Tensor:
+    """D = alpha2 * cast(relu?(alpha1 * A @ B1^T)) @ B2^T with the [M, N1] intermediate kept in tensor memory
+    (tlb200_gemm_chain: the A operand of the second tcgen05.mma comes from TMEM).  ``a`` [M, K], ``b1`` [N1, K],
+    ``b2`` [N2, N1], float16 or bfloat16, N1 in {64, 128, 192, 256}."""
+    ts = (a, b1, b2)
+    if any(t.dim() != 2 or not t.is_cuda for t in ts) or len({t.dtype for t in ts}) != 1 or a.dtype not in (torch.float16, torch.bfloat16):
+        raise ValueError("gemm_chain: A [M, K], B1 [N1, K], B2 [N2, N1] must be CUDA float16 / bfloat16 tensors of one dtype")
+    if a.shape[1] != b1.shape[1] or b2.shape[1] != b1.shape[0]:
+        raise ValueError(f"gemm_chain: T.gemm K shape check failed: A{tuple(a.shape)} B1{tuple(b1.shape)} B2{tuple(b2.shape)}")
+    m, k, n1, n2 = a.shape[0], a.shape[1], b1.shape[0], b2.shape[0]
+    if c is None:
+        c = torch.empty((m, n2), dtype=out_dtype or a.dtype, device=a.device)
+    elif tuple(c.shape) != (m, n2) or not c.is_cuda:
+        raise ValueError(f"gemm_chain: C must be a CUDA tensor of shape {(m, n2)}")
+    dev = a.device.index if a.device.index is not None else torch.cuda.current_device()
+    _ensure_init(dev)
+    d = _abi.ChainDesc()
+    d.abi_version = _abi.ABI_VERSION
+    d.m, d.k, d.n1, d.n2 = m, k, n1, n2
+    d.ab_dtype, d.c_dtype, d.relu_mid = _TORCH2TLB[a.dtype], _TORCH2TLB[c.dtype], int(bool(relu_mid))
+    d.lda, d.ldb1, d.ldb2, d.ldc = _row_pitch(a, "A"), _row_pitch(b1, "B1"), _row_pitch(b2, "B2"), _row_pitch(c, "C")
+    d.alpha1, d.alpha2, d.cfg_stages = float(alpha1), float(alpha2), int(stages)
+    lib = _abi.load()
+    with torch.cuda.device(dev):
+        rc = lib.tlb200_gemm_chain(ctypes.byref(d), a.data_ptr(), b1.data_ptr(), b2.data_ptr(), c.data_ptr(),
+                                   torch.cuda.current_stream(dev).cuda_stream)
+    _abi.check(rc, "tlb200_gemm_chain")
+    return c
+
+
 def gemm_bcast(a: torch.Tensor, b: torch.Tensor, dst_ptrs, ldc: int, c_dtype: torch.dtype, *, alpha: float = 1.0,
                relu: bool = False, **cfg) -> None:
     """C = A[M,K] @ B[N,K]^T stored into SEVERAL matrices at once (tlb200_gemm_bcast): ``dst_ptrs[0]`` is the

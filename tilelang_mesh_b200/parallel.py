@@ -40,7 +40,8 @@ class ShardedGemm:
     """C[M,N] = A[M,K] @ B[N,K]^T sharded over the ranks of `group`."""
 
     def __init__(self, M: int, N: int, K: int, mode: str = "M", group=None, panel_rows: int = 8192,
-                 local_gemm: Optional[Callable] = None, fused: bool = False, dtype: torch.dtype = torch.bfloat16):
+                 local_gemm: Optional[Callable] = None, fused: bool = False, dtype: torch.dtype = torch.bfloat16,
+                 fused_cfg: Optional[dict] = None):
         if mode not in ("M", "N"):
             raise ValueError("mode must be 'M' (row-sharded A/C, no collective) or 'N' (row-sharded B + all-gather)")
         self.M, self.N, self.K, self.mode, self.group = M, N, K, mode, group
@@ -58,6 +59,7 @@ class ShardedGemm:
         # fused = the GEMM kernel's epilogue stores every C tile into all ranks' copies of C over NVLink
         # (tlb200_gemm_bcast): compute and all-gather are one kernel, no NCCL call on the data path.
         self.fused = bool(fused) and mode == "N" and self.world > 1
+        self.fused_cfg = dict(fused_cfg or {})  # plan hints of the fused kernel (e.g. epilogue=3: peer stores through st.global)
         self._symm_out = self._symm_hdl = None
         if self.fused:
             if self.world > 8:
@@ -104,7 +106,7 @@ class ShardedGemm:
         ptrs = [int(p) for p in hdl.buffer_ptrs]
         order = [self.rank] + [g for g in range(self.world) if g != self.rank]  # destination 0 = local copy
         hdl.barrier(channel=0)  # nobody may still be reading the previous result
-        G.gemm_bcast(a, b, [ptrs[g] + off for g in order], ldc=self.N, c_dtype=out.dtype)
+        G.gemm_bcast(a, b, [ptrs[g] + off for g in order], ldc=self.N, c_dtype=out.dtype, **self.fused_cfg)
         hdl.barrier(channel=1)  # every rank's stores have landed everywhere
         return out
 
