@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(ROOT, "tilelang_mesh_b200", "lib", "libtlb200.so")
 sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, check=True).stdout
 names = subprocess.run(["cu++filt"], input="\n".join(re.findall(r"Function : (\S+)", sass)), capture_output=True, text=True).stdout.split("\n")
-pat = re.compile(r"\b(UTC[A-Z]*MMA(?:\.[A-Z0-9_]+)*|LDTM(?:\.[A-Za-z0-9_]+)*|UTMALDG(?:\.[A-Z0-9_]+)*|UTMASTG(?:\.[A-Z0-9_]+)*|UTCBAR(?:\.[A-Z0-9_]+)*|UTMAPF(?:\.[A-Z0-9_]+)*|SYNCS(?:\.[A-Z0-9_]+)*|ELECT|UTCATOMSWS(?:\.[A-Z0-9_]+)*)")
+pat = re.compile(r"\b(UTC[A-Z]*MMA(?:\.[A-Z0-9_]+)*|LDTM(?:\.[A-Za-z0-9_]+)*|STTM(?:\.[A-Za-z0-9_]+)*|UTMALDG(?:\.[A-Z0-9_]+)*|UTMASTG(?:\.[A-Z0-9_]+)*|UTCBAR(?:\.[A-Z0-9_]+)*|UTMAPF(?:\.[A-Z0-9_]+)*|SYNCS(?:\.[A-Z0-9_]+)*|ELECT|UTCATOMSWS(?:\.[A-Z0-9_]+)*)")
 print("# cuobjdump -sass tilelang_mesh_b200/lib/libtlb200.so  (sm_100a) - mnemonic counts per kernel")
 for i, chunk in enumerate(sass.split("Function : ")[1:]):
     head = chunk.split("\n", 1)[0].strip()
