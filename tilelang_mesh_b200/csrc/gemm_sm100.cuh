@@ -507,6 +507,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t mc_idx = cluster_rank / kCta;              // which of the cluster's column tiles this pair owns
   const uint32_t leader_rank = cluster_rank - cta_rank;     // cluster rank of this pair's leader
   const bool leader = cta_rank == 0;
+  if (warp == 0) TLB_TRACE(0, 13);  // kernel entry
 
   // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -530,42 +531,6 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t acc_cols = static_cast<uint32_t>(p.block_n) * acc_stages;
   const uint32_t tmem_cols = acc_cols <= 32u ? 32u : acc_cols <= 64u ? 64u : acc_cols <= 128u ? 128u
                              : acc_cols <= 256u ? 256u : 512u;
-
-  if (warp == 0) {
-    if (elect_one()) {
-      tma_prefetch_desc(&p.tm_a);
-      tma_prefetch_desc(&p.tm_b);
-      if (p.epi_tma) {
-        tma_prefetch_desc(&p.tm_c);
-        for (int g = 0; g < p.n_peer; ++g) tma_prefetch_desc(&p.tm_c_peer[g]);
-      }
-    }
-  } else if (warp == 1) {
-    if (elect_one()) {
-      for (int s = 0; s < stages; ++s) {
-        mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
-        mbar_init(bar_empty + 8 * s, kMc);  // one tcgen05.commit per pair that reads the stage
-      }
-      for (int a = 0; a < 2; ++a) {
-        mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
-        mbar_init(bar_tempty + 8 * a, p.epi_warps * kCta);    // one arrive per epilogue warp (per CTA)
-      }
-      fence_mbar_init();
-    }
-  } else if (warp == 2) {
-    tmem_alloc<kCta>(smem_tptr, tmem_cols);
-  }
-  __syncwarp();
-  tc_fence_before();
-  if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
-  tc_fence_after();
-  uint32_t tmem_base;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
-  // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may
-  // overlap the tail of the previous kernel in the stream; the next kernel may start its own set-up now.  The warps
-  // that read or write global memory wait for the previous grid first (producers before the first TMA load,
-  // epilogue warps before the first store).
-  griddep_launch_dependents();
 
   const int tiles_n_c = (p.tiles_n + kMc - 1) / kMc;  // column tiles per cluster step (kMc neighbours at a time)
   const int tiles_mn = p.tiles_m * tiles_n_c;
@@ -609,6 +574,113 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     }
   };
 
+  // One pipeline stage: arm `full[s]` with the bytes that will land and issue the A and B boxes of K block `kb`.
+  // K-major operand: box = [rows x 128 B of K], coords {k, row}; MN-major: boxes = [K-block rows x 128 B of M/N],
+  // coords {row + j*span, k}.  Called by one elected lane.
+  auto issue_stage = [&](int s, int kb, int row_a, int row_b, int kb_off, uint64_t pol) {
+    const int kspan = p.k_elems_per_block;
+    const int a_rows_per_box = p.a_box_bytes / kStageRowBytes;
+    const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
+    const uint32_t full = bar_full + 8 * s;
+    if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
+    const int k0 = kb * kspan;
+    const uint32_t dst_a = smem_a + s * kABytesPerStage;
+    const uint32_t dst_b = smem_b + s * b_stage_bytes;
+    for (int j = 0; j < p.a_boxes; ++j) {
+      const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
+      const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
+      if constexpr (kMc == 2) {
+        // K-major A only (host guarantees it): this CTA fetches rows [64*mc_idx, +64) of its 128-row box
+        // and multicasts them to itself and to the CTA of the other pair with the same pair rank.
+        tma_load_2d_pair_mc(dst_a + mc_idx * (kABytesPerStage / 2), &p.tm_a, full, c0, c1 + (int)mc_idx * (kBlockM / 2),
+                            static_cast<uint16_t>(0x5u << cta_rank), pol);
+      } else if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
+      else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol);
+    }
+    // accumulator h of the tile covers tile columns [h*umma_n, (h+1)*umma_n)
+#pragma unroll
+    for (int h = 0; h < n_sub; ++h) {
+      const int rb = row_b + h * p.umma_n;
+      for (int j = 0; j < p.b_boxes; ++j) {
+        const int c0 = p.b_mn_major ? rb + j * kspan : k0;
+        const int c1 = p.b_mn_major ? k0 + kb_off : rb + j * b_rows_per_box;
+        const uint32_t dst = dst_b + h * b_sub_bytes + j * p.b_box_bytes;
+        if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol);
+        else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol);
+      }
+    }
+  };
+  // Operand coordinates of work item t for this CTA.
+  auto operand_rows = [&](int t, int& row_a, int& row_b, int& kb_off) {
+    int tm, tn, grp, row_base, row_limit;
+    tile_coord(t, tm, tn, grp, row_base, row_limit);
+    row_a = row_base + (int)cta_rank * kBlockM;
+    // group g's B is block g of the 2-D view: rows [g*b_group_rows, ...) (K-major) or K offset (N-major)
+    const int b_goff = grp * p.b_group_rows;
+    row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta + (p.b_mn_major ? 0 : b_goff);
+    kb_off = p.b_mn_major ? b_goff : 0;
+  };
+  // Single-CTA kernels: warp 0 (a TMA producer) does not wait at the block-wide set-up barrier.  It initialises the
+  // stage barriers itself, ARRIVES on the set-up barrier and goes straight to its K blocks, while warp 2 is still
+  // allocating tensor memory; the other warps synchronise as before (producers 2 and 3 join the round-robin after the
+  // barrier).  Short problems are a set-up, one or two dozen K blocks and an epilogue, and ~2.2k of their ~12k cycles
+  // went by between kernel entry and the first TMA issue (profiles/r2_notes.md).  With clusters the peer's loads signal
+  // this CTA's barriers, which must not happen before the cluster-wide barrier, so pairs keep the ordinary order.
+  const bool early_producer = kCluster == 1 && warp == 0;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      tma_prefetch_desc(&p.tm_a);
+      tma_prefetch_desc(&p.tm_b);
+      if constexpr (kCluster == 1) {
+        for (int s = 0; s < stages; ++s) {
+          mbar_init(bar_full + 8 * s, 1);
+          mbar_init(bar_empty + 8 * s, 1);
+        }
+        fence_mbar_init();
+      }
+      if (p.epi_tma) {
+        tma_prefetch_desc(&p.tm_c);
+        for (int g = 0; g < p.n_peer; ++g) tma_prefetch_desc(&p.tm_c_peer[g]);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      if constexpr (kCluster > 1) {
+        for (int s = 0; s < stages; ++s) {
+          mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
+          mbar_init(bar_empty + 8 * s, kMc);  // one tcgen05.commit per pair that reads the stage
+        }
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
+        mbar_init(bar_tempty + 8 * a, p.epi_warps * kCta);    // one arrive per epilogue warp (per CTA)
+      }
+      fence_mbar_init();
+    }
+  } else if (warp == 2) {
+    tmem_alloc<kCta>(smem_tptr, tmem_cols);
+  }
+  __syncwarp();
+  tc_fence_before();
+  if constexpr (kCluster > 1) {
+    cluster_sync_all();
+  } else {
+    // named barrier 1 over the whole block: warp 0 only arrives (it needs neither the TMEM address nor the accumulator
+    // barriers), everybody else waits for all arrivals
+    if (early_producer) asm volatile("barrier.cta.arrive 1, %0;" ::"r"(static_cast<uint32_t>(blockDim.x)) : "memory");
+    else asm volatile("barrier.cta.sync 1, %0;" ::"r"(static_cast<uint32_t>(blockDim.x)) : "memory");
+  }
+  tc_fence_after();
+  uint32_t tmem_base = 0;
+  if (!early_producer) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+  // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may
+  // overlap the tail of the previous kernel in the stream; the next kernel may start its own set-up now.  The warps
+  // that read or write global memory wait for the previous grid first (producers before the first TMA load,
+  // epilogue warps before the first store).
+  griddep_launch_dependents();
+  if (warp == 0) TLB_TRACE(0, 14);  // set-up done
+
   if (warp != 1 && warp < kEpiWarp0) {
     // ===================================================== TMA producers (one elected lane of each issues)
     // Three producer warps (0, 2, 3) take the K blocks round-robin, each filling whole stages.  One warp's issue
@@ -623,22 +695,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const bool elected = elect_one();
     // Operands are re-read by other tiles of the raster group: keep them in L2 (evict_last measured +1.5 % bf16,
     // +3 % fp8 sustained over evict_normal; profiles/r1_notes.md).  l2_policy 1 restores evict_normal.
-    const uint64_t pol_a = p.l2_policy == 1 ? policy_evict_normal() : policy_evict_last();
-    const uint64_t pol_b = pol_a;
-    const int kspan = p.k_elems_per_block;
-    const int a_rows_per_box = p.a_box_bytes / kStageRowBytes;
-    const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
+    const uint64_t pol = p.l2_policy == 1 ? policy_evict_normal() : policy_evict_last();
     int s = 0;
     uint32_t ph = 0;
     griddep_wait();
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-      int tm, tn, grp, row_base, row_limit;
-      tile_coord(t, tm, tn, grp, row_base, row_limit);
-      const int row_a = row_base + (int)cta_rank * kBlockM;
-      // group g's B is block g of the 2-D view: rows [g*b_group_rows, ...) (K-major) or K offset (N-major)
-      const int b_goff = grp * p.b_group_rows;
-      const int row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta + (p.b_mn_major ? 0 : b_goff);
-      const int kb_off = p.b_mn_major ? b_goff : 0;
+      int row_a, row_b, kb_off;
+      operand_rows(t, row_a, row_b, kb_off);
       int kb0, kb1;
       k_range(t, kb0, kb1);
       if (warp == 0) TLB_TRACE((t - cluster_id) / num_clusters, 11);
@@ -646,38 +709,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         const bool mine = turn == pidx;
         if (++turn == kProducers) turn = 0;
         if (mine) mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
-        if (mine && elected) {
-          const uint32_t full = bar_full + 8 * s;
-          if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
-          const int k0 = kb * kspan;
-          const uint32_t dst_a = smem_a + s * kABytesPerStage;
-          const uint32_t dst_b = smem_b + s * b_stage_bytes;
-          // K-major operand: box = [rows x 128 B of K], coords {k, row}.
-          // MN-major operand: boxes = [K-block rows x 128 B of M/N], coords {row + j*span, k}.
-          for (int j = 0; j < p.a_boxes; ++j) {
-            const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
-            const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
-            if constexpr (kMc == 2) {
-              // K-major A only (host guarantees it): this CTA fetches rows [64*mc_idx, +64) of its 128-row box
-              // and multicasts them to itself and to the CTA of the other pair with the same pair rank.
-              tma_load_2d_pair_mc(dst_a + mc_idx * (kABytesPerStage / 2), &p.tm_a, full, c0, c1 + (int)mc_idx * (kBlockM / 2),
-                                  static_cast<uint16_t>(0x5u << cta_rank), pol_a);
-            } else if constexpr (kCta == 2) tma_load_2d_pair(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
-            else tma_load_2d(dst_a + j * p.a_box_bytes, &p.tm_a, full, c0, c1, pol_a);
-          }
-          // accumulator h of the tile covers tile columns [h*umma_n, (h+1)*umma_n)
-#pragma unroll
-          for (int h = 0; h < n_sub; ++h) {
-            const int rb = row_b + h * p.umma_n;
-            for (int j = 0; j < p.b_boxes; ++j) {
-              const int c0 = p.b_mn_major ? rb + j * kspan : k0;
-              const int c1 = p.b_mn_major ? k0 + kb_off : rb + j * b_rows_per_box;
-              const uint32_t dst = dst_b + h * b_sub_bytes + j * p.b_box_bytes;
-              if constexpr (kCta == 2) tma_load_2d_pair(dst, &p.tm_b, full, c0, c1, pol_b);
-              else tma_load_2d(dst, &p.tm_b, full, c0, c1, pol_b);
-            }
-          }
-        }
+        if (mine && elected) issue_stage(s, kb, row_a, row_b, kb_off, pol);
         __syncwarp();
         if (++s == stages) { s = 0; ph ^= 1u; }
       }
@@ -711,12 +743,14 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         for (int t = cluster_id; t < num_tiles; t += num_clusters) {
           mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
           tc_fence_after();
+          TLB_TRACE((t - cluster_id) / num_clusters, 0);
           const uint32_t d_tmem = tmem_base + as * p.block_n;
           int kb0, kb1;
           k_range(t, kb0, kb1);
           for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
             tc_fence_after();
+            if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
             if (elected) {
               issue_kblock(s, d_tmem, 0u, kb == kb0);
               umma_commit<kCta>(bar_empty + 8 * s, kMc == 2 ? 0xF : 0x3);  // smem stage reusable once these MMAs retire
@@ -726,6 +760,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
           }
           if (elected) umma_commit<kCta>(bar_tfull + 8 * as, static_cast<uint16_t>(0x3u << leader_rank));  // accumulator complete -> epilogue
           __syncwarp();
+          TLB_TRACE((t - cluster_id) / num_clusters, 2);
           if (++as == acc_stages) { as = 0; aph ^= 1u; }
         }
       } else {
@@ -892,6 +927,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
 
   // ---- teardown: nobody may still be using TMEM / peer smem when it is released
   __syncwarp();  // re-converge the single-lane regions before the .aligned barriers
+  if (warp == kEpiWarp0) TLB_TRACE(0, 15);  // first epilogue warp done with every tile
   tc_fence_before();
   if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();

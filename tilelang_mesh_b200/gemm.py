@@ -19,6 +19,7 @@ from . import _abi, plan_cache
 
 _PLAN_HINTS = {"cta_group", "block_n", "stages", "raster", "split_k", "epi_warps", "epilogue"}
 _sm_counts = {}
+_plan_bypass = False  # plan_cache.tune() sets it while it times explicit plans (the table must not override them)
 
 
 def _sm_count(dev: int) -> int:
@@ -169,12 +170,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: Optional[torch.Tensor] = None, *, 
             bias = _vector(bias, m if bias_per_row else n, "bias", a.device)
             vec_flags |= _abi.VEC_BIAS_M if bias_per_row else _abi.VEC_BIAS_N
     key = (m, n, ka, a.dtype, c.dtype, trans_a, trans_b, lda, ldb, ldc, alpha, relu, vec_flags, tuple(sorted(cfg.items())) if cfg else (),
-           "TLB200_PLAN_CACHE_BYPASS" in os.environ)
+           _plan_bypass)
     hit = _desc_cache.get(key)
     lib = _lib or _load_lib()
     if hit is None:
         plan_cfg = cfg
-        if not (_PLAN_HINTS & cfg.keys()) and "TLB200_PLAN_CACHE_BYPASS" not in os.environ:
+        if not _plan_bypass and not (_PLAN_HINTS & cfg.keys()):
             # no hints from the caller: a measured, persisted plan for this problem wins over the cycle model
             tuned = plan_cache.lookup(_sm_count(dev), m, n, ka, a.dtype, c.dtype, trans_a, trans_b)
             if tuned:

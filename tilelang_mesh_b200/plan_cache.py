@@ -145,7 +145,7 @@ def tune(a, b, c, *, trans_a=False, trans_b=True, reps: int = 9, persist: bool =
     # write-back then competes with the first wave's loads), and the candidates are timed round-robin so that clock
     # and temperature drift hits them all alike.
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
-    os.environ["TLB200_PLAN_CACHE_BYPASS"] = "1"  # time the plan named by cfg, not a cached one
+    G._plan_bypass = True  # time the plan named by cfg, not a cached one
     try:
         legal = []
         for cfg in cands:
@@ -170,7 +170,7 @@ def tune(a, b, c, *, trans_a=False, trans_b=True, reps: int = 9, persist: bool =
                 torch.cuda.synchronize(dev)
                 times[i].append(e0.elapsed_time(e1) * 1e3)
     finally:
-        os.environ.pop("TLB200_PLAN_CACHE_BYPASS", None)
+        G._plan_bypass = False
     results = [(sorted(t)[len(t) // 2], cfg) for t, cfg in zip(times, legal)]
     autos = [us for us, cfg in results if not cfg]
     auto_us = min(autos) if autos else None

@@ -24,6 +24,13 @@ G.gemm(a, b, c, **cfg)
 torch.cuda.synchronize()
 lib.tlb200_debug_set_trace(None)
 t = tr.cpu().view(-1, 16)
+if "small" in sys.argv:
+    r = t[0].tolist(); z = r[13]
+    names = {13: "kernel entry", 14: "set-up done (barriers, TMEM, cluster sync)", 11: "producer issues first K block", 0: "MMA warp holds accumulator",
+             1: "first K block landed", 2: "last commit issued", 3: "epilogue sees accumulator full", 4: "epilogue: accumulator handed back", 15: "epilogue warp done"}
+    for k in sorted(names, key=lambda k: r[k]):
+        print(f"{r[k]-z:8d} cycles  {names[k]}")
+    print("plan", G.plan_for(a, b, c, **cfg)); sys.exit(0)
 print("plan", G.plan_for(a, b, c, **cfg))
 rows = [r for r in t.tolist() if r[2] != 0]
 t0 = rows[0][0]
