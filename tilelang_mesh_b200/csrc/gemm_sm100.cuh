@@ -63,8 +63,6 @@ struct alignas(64) GemmKernelParams {
   int tail_begin, tail_tiles, tail_split, tail_kb;  // tail_tiles == 0: off
   int n_groups;      // 0 = ordinary GEMM
   int b_group_rows;  // rows of one group's B in the 2-D view TMA sees (N if K-major, K if N-major)
-  int group_row[kMaxGroups + 1];
-  int group_tile[kMaxGroups + 1];
   void* c;
   long long ldc;  // elements
   int m, n;
@@ -104,7 +102,17 @@ struct alignas(64) GemmKernelParams {
   const float* col_scale;
   const float* bias;
   int bias_per_row;  // bias is indexed by the output row (else by the column)
+  // ceil(2^64 / d) for the divisors of the work-item decomposition (0 when d <= 1): tiles_mn, raster * tiles_n_c,
+  // raster, tiles_m % raster and tail_tiles.  Divisions by run-time values (~60 dependent instructions each) sat
+  // between the set-up barrier and the first TMA issue of every CTA.
+  unsigned long long magic_tiles_mn, magic_group, magic_raster, magic_last_rows, magic_tail_tiles;
+  int kgroup;        // K blocks per pipeline barrier (1, 2 or 4): `full` / `empty` [g] cover stages [g*kgroup, (g+1)*kgroup)
   long long* trace;  // development builds (-DTLB200_TRACE): per-tile clock64 stamps of CTA 0; null otherwise
+  int debug_mode;    // development builds: 1 = issue no MMAs (stages are handed straight back), 2 = issue no TMA loads
+                     // (the stage barrier is just arrived on), 4 / 8 = one / two producer warps instead of three
+  // Last, so that the scalars every CTA reads before its first TMA issue sit in a few adjacent constant-cache lines.
+  int group_row[kMaxGroups + 1];
+  int group_tile[kMaxGroups + 1];
 };
 
 #ifdef TLB200_TRACE
@@ -512,6 +520,8 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
+  const int kg = (kNSub == 2 || p.kgroup < 2) ? 1 : p.kgroup;  // K blocks (stages) per full / empty barrier pair
+  const int groups = stages / kg;            // ring slots; stages beyond groups * kg stay unused
   constexpr int n_sub = kNSub;  // accumulators per tile (compile-time: a predicated-off tcgen05.mma is not free)
   const int acc_stages = p.acc_stages;
   const uint32_t b_sub_bytes = static_cast<uint32_t>(p.b_sub_bytes);
@@ -528,6 +538,18 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // bytes that land in one stage: the A boxes actually issued (a short problem, M < 128, fetches only its own rows;
   // with A multicast each CTA issues half a box and receives the other half) plus the B rows, per CTA of the pair
   const uint32_t stage_tx_bytes = (static_cast<uint32_t>(p.a_boxes * p.a_box_bytes) * kMc + b_stage_bytes) * kCta;
+  // Kernel parameters are cold in the constant cache at every launch, and the producers' way to their first TMA issue
+  // reads a dozen of them one after another (a miss each time it enters a new line: ~1.2k cycles between the set-up
+  // barrier and the first load).  One word of every line of the scalar block is read here, all at once, while the
+  // set-up is still going on; the sum goes to a spare shared-memory word so that the loads cannot be dropped.
+  if (lane == 0) {
+    const uint32_t h = static_cast<uint32_t>(p.tail_begin) ^ static_cast<uint32_t>(p.n_groups) ^ static_cast<uint32_t>(p.m) ^
+                       static_cast<uint32_t>(p.raster) ^ static_cast<uint32_t>(p.stages) ^ static_cast<uint32_t>(p.a_boxes) ^ p.idesc ^
+                       p.kadv_a ^ static_cast<uint32_t>(p.out_kind) ^ static_cast<uint32_t>(p.l2_policy) ^
+                       static_cast<uint32_t>(p.bias_per_row) ^ static_cast<uint32_t>(p.magic_tiles_mn) ^
+                       static_cast<uint32_t>(p.magic_tail_tiles) ^ static_cast<uint32_t>(p.kgroup);
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_tptr + 8 + 0 * warp), "r"(h) : "memory");
+  }
   const uint32_t acc_cols = static_cast<uint32_t>(p.block_n) * acc_stages;
   const uint32_t tmem_cols = acc_cols <= 32u ? 32u : acc_cols <= 64u ? 64u : acc_cols <= 128u ? 128u
                              : acc_cols <= 256u ? 256u : 512u;
@@ -542,15 +564,23 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
 
   // Work item -> (row tile, column tile); for a grouped GEMM also the group, the first row of the tile
   // and the end of the group's rows (the tile's row limit).
+  // x / d through the host's reciprocal ceil(2^64 / d): the high half of x * magic is exact for every 32-bit x and
+  // d >= 2 (magic 0 stands for d == 1).  No run-time division is left on the way to the first TMA issue.
+  auto fdiv = [](int x, unsigned long long magic) -> int {
+    return magic ? static_cast<int>(__umul64hi(static_cast<unsigned long long>(static_cast<unsigned>(x)), magic)) : x;
+  };
   auto tile_coord = [&](int w, int& tm, int& tn, int& grp, int& row_base, int& row_limit) {
-    const int t = !tail_mode ? w % tiles_mn : (w < p.tail_begin ? w : p.tail_begin + (w - p.tail_begin) % p.tail_tiles);
+    int t;
+    if (!tail_mode) t = w - fdiv(w, p.magic_tiles_mn) * tiles_mn;
+    else t = w < p.tail_begin ? w : p.tail_begin + (w - p.tail_begin) - fdiv(w - p.tail_begin, p.magic_tail_tiles) * p.tail_tiles;
     const int group = p.raster * tiles_n_c;
-    const int g = t / group;
+    const int g = fdiv(t, p.magic_group);
     const int first = g * p.raster;
     const int rows = min(p.raster, p.tiles_m - first);
     const int within = t - g * group;
-    tm = first + within % rows;
-    tn = (within / rows) * kMc + (int)mc_idx;  // may equal tiles_n for the last odd tile: that pair computes zeros
+    const int wq = fdiv(within, rows == p.raster ? p.magic_raster : p.magic_last_rows);
+    tm = first + within - wq * rows;
+    tn = wq * kMc + (int)mc_idx;  // may equal tiles_n for the last odd tile: that pair computes zeros
     if (p.n_groups == 0) {
       grp = 0;
       row_base = tm * kCta * kBlockM;
@@ -566,26 +596,52 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // K-block range [kb0, kb1) of work item w
   auto k_range = [&](int w, int& kb0, int& kb1) {
     if (tail_mode) {
-      kb0 = w < p.tail_begin ? 0 : ((w - p.tail_begin) / p.tail_tiles) * p.tail_kb;
+      kb0 = w < p.tail_begin ? 0 : fdiv(w - p.tail_begin, p.magic_tail_tiles) * p.tail_kb;
       kb1 = w < p.tail_begin ? nkb : min(nkb, kb0 + p.tail_kb);
     } else {
-      kb0 = (w / tiles_mn) * p.kb_per_split;
+      kb0 = fdiv(w, p.magic_tiles_mn) * p.kb_per_split;
       kb1 = min(nkb, kb0 + p.kb_per_split);
     }
   };
 
-  // One pipeline stage: arm `full[s]` with the bytes that will land and issue the A and B boxes of K block `kb`.
+  // One pipeline stage: issue the A and B boxes of K block `kb` into stage `s`; their bytes are counted on `full`
+  // (armed by the caller for all the K blocks of a group).
   // K-major operand: box = [rows x 128 B of K], coords {k, row}; MN-major: boxes = [K-block rows x 128 B of M/N],
   // coords {row + j*span, k}.  Called by one elected lane.
-  auto issue_stage = [&](int s, int kb, int row_a, int row_b, int kb_off, uint64_t pol) {
+  const bool kmajor_single_box = p.a_boxes == 1 && p.b_boxes == 1 && !p.a_mn_major && !p.b_mn_major;
+  auto issue_stage = [&](int s, uint32_t full, int kb, int row_a, int row_b, int kb_off, uint64_t pol) {
     const int kspan = p.k_elems_per_block;
     const int a_rows_per_box = p.a_box_bytes / kStageRowBytes;
     const int b_rows_per_box = p.b_box_bytes / kStageRowBytes;
-    const uint32_t full = bar_full + 8 * s;
-    if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes);
+#ifdef TLB200_TRACE_KB
+    const bool tri = p.trace && blockIdx.x == 0 && kb < 64;  // CTA 0's producers, first 64 K blocks, step by step
+#define TLB_TRI(j) do { if (tri) p.trace[(64 + kb) * 16 + (j)] = clock64(); } while (0)
+#else
+#define TLB_TRI(j) do { } while (0)
+#endif
+    TLB_TRI(1);
     const int k0 = kb * kspan;
     const uint32_t dst_a = smem_a + s * kABytesPerStage;
     const uint32_t dst_b = smem_b + s * b_stage_bytes;
+    if (kmajor_single_box) {
+      // Both operands K-contiguous, one box each (the benchmark layout): straight-line issue.  The general loops below
+      // (several boxes per operand, either major-ness chosen per box) compile to ~150 dependent instructions per K
+      // block - 840 cycles per issue, which capped every tile narrower than 256 columns at ~330 cycles per K block
+      // (profiles/r2_notes.md); this path is ~20.
+      if constexpr (kMc == 2) {
+        tma_load_2d_pair_mc(dst_a + mc_idx * (kABytesPerStage / 2), &p.tm_a, full, k0, row_a + (int)mc_idx * (kBlockM / 2),
+                            static_cast<uint16_t>(0x5u << cta_rank), pol);
+      } else if constexpr (kCta == 2) tma_load_2d_pair(dst_a, &p.tm_a, full, k0, row_a, pol);
+      else tma_load_2d(dst_a, &p.tm_a, full, k0, row_a, pol);
+      TLB_TRI(2);
+#pragma unroll
+      for (int h = 0; h < n_sub; ++h) {
+        if constexpr (kCta == 2) tma_load_2d_pair(dst_b + h * b_sub_bytes, &p.tm_b, full, k0, row_b + h * p.umma_n, pol);
+        else tma_load_2d(dst_b + h * b_sub_bytes, &p.tm_b, full, k0, row_b + h * p.umma_n, pol);
+      }
+      TLB_TRI(3);
+      return;
+    }
     for (int j = 0; j < p.a_boxes; ++j) {
       const int c0 = p.a_mn_major ? row_a + j * kspan : k0;
       const int c1 = p.a_mn_major ? k0 : row_a + j * a_rows_per_box;
@@ -687,31 +743,61 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     // path (try_wait on `empty`, arrive.expect_tx, two TMA issues) costs ~280 ns per K block, which starved every
     // tile narrower than 256 columns (282 ns per block whatever the tile, stage count or cluster shape;
     // profiles/r1_notes.md); three interleaved streams bring the issue cost under the MMA time of a 64-wide tile.
-    // Parity waits only tell adjacent phases apart: a producer that skips P K blocks between its visits must not
-    // be able to see a stage's `empty` barrier two phases behind, which holds for P <= stages.
-    const int kProducers = stages < 3 ? stages : 3;
+    // Parity waits only tell adjacent phases apart: a producer that skips P groups between its visits must not
+    // be able to see a group's `empty` barrier two phases behind, which holds for P <= groups.
+    // A barrier pair covers `kg` consecutive stages (GemmKernelParams::kgroup): one wait, one expect_tx and, on the
+    // other side, one wait and one commit per kg K blocks - the hand-shake, not the loads or the MMAs, is what a
+    // narrow tile's K block costs (see the MMA issuer below).
+#ifdef TLB200_TRACE
+    const int kProducers = (p.debug_mode & 4) ? 1 : (p.debug_mode & 8) ? 2 : groups < 3 ? groups : 3;
+#else
+    const int kProducers = groups < 3 ? groups : 3;
+#endif
     const int pidx = warp == 0 ? 0 : warp - 1;  // warps 0, 2, 3 -> 0, 1, 2 (a warp with pidx >= kProducers idles)
     int turn = 0;                               // whose K block the next one is
     const bool elected = elect_one();
     // Operands are re-read by other tiles of the raster group: keep them in L2 (evict_last measured +1.5 % bf16,
     // +3 % fp8 sustained over evict_normal; profiles/r1_notes.md).  l2_policy 1 restores evict_normal.
+    if (warp == 0) TLB_TRACE(200, 0);
     const uint64_t pol = p.l2_policy == 1 ? policy_evict_normal() : policy_evict_last();
-    int s = 0;
+    int gs = 0;  // ring slot: a GROUP of kg consecutive stages behind one full / empty barrier pair
     uint32_t ph = 0;
+    if (warp == 0) TLB_TRACE(200, 1);
     griddep_wait();
+    if (warp == 0) TLB_TRACE(200, 2);
     for (int t = cluster_id; t < num_tiles; t += num_clusters) {
       int row_a, row_b, kb_off;
       operand_rows(t, row_a, row_b, kb_off);
+      if (warp == 0 && t == cluster_id) TLB_TRACE(200, 3);
       int kb0, kb1;
       k_range(t, kb0, kb1);
       if (warp == 0) TLB_TRACE((t - cluster_id) / num_clusters, 11);
-      for (int kb = kb0; kb < kb1; ++kb) {
+      for (int kb = kb0; kb < kb1; kb += kg) {
         const bool mine = turn == pidx;
         if (++turn == kProducers) turn = 0;
-        if (mine) mbar_wait(bar_empty + 8 * s, ph ^ 1u, 0);
-        if (mine && elected) issue_stage(s, kb, row_a, row_b, kb_off, pol);
+#ifdef TLB200_TRACE_KB
+        if (mine && elected && kb < 64 && p.trace && blockIdx.x == 0 && t == cluster_id) p.trace[(64 + kb) * 16 + 4] = clock64();
+#endif
+        if (mine) mbar_wait(bar_empty + 8 * gs, ph ^ 1u, 0);
+        if (mine && elected) {
+          const int nk = kb1 - kb < kg ? kb1 - kb : kg;
+          const uint32_t full = bar_full + 8 * gs;
+#ifdef TLB200_TRACE_KB
+          if (kb < 64 && p.trace && blockIdx.x == 0 && t == cluster_id) p.trace[(64 + kb) * 16 + 0] = clock64();
+#endif
+#ifdef TLB200_TRACE
+          if (p.debug_mode & 2) { if (leader) mbar_arrive(full); } else
+#endif
+          {
+            if (leader) mbar_arrive_expect_tx(full, stage_tx_bytes * nk);
+            for (int j = 0; j < nk; ++j) issue_stage(gs * kg + j, full, kb + j, row_a, row_b, kb_off, pol);
+          }
+        }
         __syncwarp();
-        if (++s == stages) { s = 0; ph ^= 1u; }
+#ifdef TLB200_TRACE
+        if (warp == 0 && t == cluster_id && kb - kb0 == 6 * kg) TLB_TRACE(0, 12);  // warp 0 has issued its third group
+#endif
+        if (++gs == groups) { gs = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
@@ -740,29 +826,62 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         }
       };
       if constexpr (kNSub == 1) {
-        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-          mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
-          tc_fence_after();
-          TLB_TRACE((t - cluster_id) / num_clusters, 0);
-          const uint32_t d_tmem = tmem_base + as * p.block_n;
-          int kb0, kb1;
-          k_range(t, kb0, kb1);
-          for (int kb = kb0; kb < kb1; ++kb) {
-            mbar_wait(bar_full + 8 * s, ph, 2);  // TMA bytes of this stage have landed
+        // Narrow tiles are bound by THIS loop, not by the tensor pipe or the loads.  tools/ubench/umma_pace.cu: a
+        // 256x64 MMA runs every 43 cycles when issued back to back (172 per K block), but the pipe holds next to no
+        // queue - whatever the issuing thread does between two K blocks is added to them, and a barrier wait alone is
+        // 100-200 cycles (the loop that waited, then issued, ran at ~320 per K block with operands already resident).
+        // So: ONE elected thread runs the whole loop (ptxas then keeps descriptors and barrier addresses in uniform
+        // registers: no R2UR in front of every MMA), the barrier of the NEXT K block is probed before this block's
+        // MMAs are issued and only waited on if that probe failed, the stage state advances by additions, and the four
+        // MMAs of a K block are one asm block.  Even so one pass (probe, commit, bookkeeping, with the producers'
+        // hand-shake on the other side) is ~250-320 cycles (tools/ubench/umma_ring.cu), above the 172 of a 64-wide K
+        // block, so narrow tiles put `kgroup` K blocks behind each barrier pair: one pass then issues 4 * kgroup MMAs.
+        static_assert(kStageRowBytes / kUmmaKBytes == 4, "umma_ss_x4 issues four MMAs per K block");
+        const uint16_t empty_mask = kMc == 2 ? 0xF : 0x3;
+        if (elected) {
+          const uint32_t a_w0 = static_cast<uint32_t>(hi_a) | a_lo0, b_w0 = static_cast<uint32_t>(hi_b) | b_lo0;
+          const uint32_t a_hi = static_cast<uint32_t>(hi_a >> 32), b_hi = static_cast<uint32_t>(hi_b >> 32);
+          const uint32_t a_gstep = a_step * kg, b_gstep = b_step * kg;
+          uint32_t a_w = a_w0, b_w = b_w0, bar_e = bar_empty, bar_f = bar_full;  // of the coming group
+          int gs = 0;
+          bool ready = false;  // the probe of the coming group's barrier succeeded
+          for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+            mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
             tc_fence_after();
-            if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
-            if (elected) {
-              issue_kblock(s, d_tmem, 0u, kb == kb0);
-              umma_commit<kCta>(bar_empty + 8 * s, kMc == 2 ? 0xF : 0x3);  // smem stage reusable once these MMAs retire
+            TLB_TRACE((t - cluster_id) / num_clusters, 0);
+            const uint32_t d_tmem = tmem_base + as * p.block_n;
+            int kb0, kb1;
+            k_range(t, kb0, kb1);
+            const bool more_tiles = t + num_clusters < num_tiles;
+            for (int kb = kb0; kb < kb1; kb += kg) {
+              if (!ready) mbar_wait(bar_f, ph, 2);  // TMA bytes of this group's stages have landed
+              tc_fence_after();
+              if (kb == kb0) TLB_TRACE((t - cluster_id) / num_clusters, 1);
+#ifdef TLB200_TRACE_KB
+              if (p.trace && blockIdx.x == 0 && t == cluster_id && kb < 64) p.trace[(64 + kb) * 16 + 8] = clock64();  // this group's operands seen
+#endif
+              uint32_t a_cur = a_w, b_cur = b_w;
+              const uint32_t e_cur = bar_e;
+              a_w += a_gstep; b_w += b_gstep; bar_e += 8; bar_f += 8;
+              if (++gs == groups) { gs = 0; ph ^= 1u; a_w = a_w0; b_w = b_w0; bar_e = bar_empty; bar_f = bar_full; }
+              // non-blocking probe (try_wait may suspend the thread, which would hold back the MMAs below)
+              ready = (kb + kg < kb1 || more_tiles) && mbar_test_wait(bar_f, ph);
+              const int nk = kb1 - kb < kg ? kb1 - kb : kg;
+#ifdef TLB200_TRACE
+              if (!(p.debug_mode & 1))
+#endif
+              for (int j = 0; j < nk; ++j) {
+                umma_ss_x4<kCta, kKind>(d_tmem, a_cur, a_hi, b_cur, b_hi, kadv_a, kadv_b, idesc, (kb == kb0 && j == 0) ? 0u : 1u);
+                a_cur += a_step; b_cur += b_step;
+              }
+              umma_commit<kCta>(e_cur, empty_mask);  // the group's stages are reusable once these MMAs retire
             }
-            __syncwarp();
-            if (++s == stages) { s = 0; ph ^= 1u; }
+            umma_commit<kCta>(bar_tfull + 8 * as, static_cast<uint16_t>(0x3u << leader_rank));  // accumulator complete -> epilogue
+            TLB_TRACE((t - cluster_id) / num_clusters, 2);
+            if (++as == acc_stages) { as = 0; aph ^= 1u; }
           }
-          if (elected) umma_commit<kCta>(bar_tfull + 8 * as, static_cast<uint16_t>(0x3u << leader_rank));  // accumulator complete -> epilogue
-          __syncwarp();
-          TLB_TRACE((t - cluster_id) / num_clusters, 2);
-          if (++as == acc_stages) { as = 0; aph ^= 1u; }
         }
+        __syncwarp();
       } else {
         // Two accumulators per tile sharing every A stage (they fill TMEM, so there is no second buffer: what the
         // epilogue cannot hide is exposed).  tmem_full/empty[h] belong to accumulator h.  The K blocks are issued
@@ -860,7 +979,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       // a tail slice writes tile (t - tail_begin) of the workspace matrix, whole (the reduction clips to M x N)
       const int row0 = (tail_item ? (t - p.tail_begin) * kCta * kBlockM : row_base) + (int)cta_rank * kBlockM;
       const int col0 = tail_item ? 0 : tn * p.block_n;
-      const int row_off = (tail_mode ? 0 : t / tiles_mn) * p.split_row_pitch;
+      const int row_off = (tail_mode ? 0 : fdiv(t, p.magic_tiles_mn)) * p.split_row_pitch;
       if (tail_item) row_limit = 0x7fffffff;
       // partial sums of a tail slice go to the workspace raw; everything else is the final C
       EpiOut o{tail_item ? &p.tm_ws : &p.tm_c, tail_item ? p.ws : p.c, tail_item ? (long long)p.block_n : p.ldc,

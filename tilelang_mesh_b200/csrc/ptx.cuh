@@ -121,6 +121,26 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag
   }
 }
 
+// The same wait for a CONVERGED warp, with a warp-uniform exit: every lane polls and the loop ends on a vote.  After
+// mbar_wait() ptxas treats what follows as possibly divergent and keeps it out of the uniform datapath (every
+// tcgen05.mma operand then goes through an R2UR); the vote's result is uniform by construction, so the code after
+// this wait stays in uniform registers.  All 32 lanes must call it.
+__device__ __forceinline__ void mbar_wait_uniform(uint32_t bar, uint32_t parity, int tag) {
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+    if ((++spins & 0x3ffu) == 0) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > TLB200_WATCHDOG_NS) {
+        printf("tlb200 watchdog: block %d thread %d tag %d bar 0x%x parity %u\n", (int)blockIdx.x,
+               (int)threadIdx.x, tag, bar, parity);
+        __trap();
+      }
+    }
+  }
+}
+
 // ----------------------------------------------------------------------------- fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -284,6 +304,42 @@ __device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t desc_a, uint64
   }
 }
 #undef TLB200_UMMA
+
+// The four MMAs of one 128-byte K block as ONE asm statement: the descriptors' low words advance by `kadv` (16-byte
+// units) per MMA, their high words and the instruction descriptor stay.  Written as a block so that nothing is scheduled
+// between the four issues and the descriptor arithmetic is four additions (the issue loop of a narrow tile is bound by
+// this thread's own instruction latency, not by the tensor pipe: profiles/r2_notes.md section 12).  The low word must
+// not carry out of its 14-bit address field: a K block never leaves its stage, and shared memory ends below 2^18.
+#define TLB200_UMMA4(GROUP, KIND)                                                                                   \
+  asm volatile(                                                                                                     \
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 da, db;\n\t.reg .b32 aw, bw;\n\t"                                          \
+      "setp.ne.b32 p, %8, 0;\n\tsetp.eq.b32 t, %7, %7;\n\t"                                                         \
+      "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"                                                          \
+      "tcgen05.mma.cta_group::" GROUP ".kind::" KIND " [%0], da, db, %7, p;\n\t"                                     \
+      "add.u32 aw, %1, %5;\n\tadd.u32 bw, %3, %6;\n\tmov.b64 da, {aw, %2};\n\tmov.b64 db, {bw, %4};\n\t"             \
+      "tcgen05.mma.cta_group::" GROUP ".kind::" KIND " [%0], da, db, %7, t;\n\t"                                     \
+      "add.u32 aw, aw, %5;\n\tadd.u32 bw, bw, %6;\n\tmov.b64 da, {aw, %2};\n\tmov.b64 db, {bw, %4};\n\t"             \
+      "tcgen05.mma.cta_group::" GROUP ".kind::" KIND " [%0], da, db, %7, t;\n\t"                                     \
+      "add.u32 aw, aw, %5;\n\tadd.u32 bw, bw, %6;\n\tmov.b64 da, {aw, %2};\n\tmov.b64 db, {bw, %4};\n\t"             \
+      "tcgen05.mma.cta_group::" GROUP ".kind::" KIND " [%0], da, db, %7, t;\n\t}" ::"r"(tmem_d),                     \
+      "r"(a_w), "r"(a_hi), "r"(b_w), "r"(b_hi), "r"(kadv_a), "r"(kadv_b), "r"(idesc), "r"(accumulate)               \
+      : "memory")
+template <int kCta, int kKind>
+__device__ __forceinline__ void umma_ss_x4(uint32_t tmem_d, uint32_t a_w, uint32_t a_hi, uint32_t b_w, uint32_t b_hi,
+                                           uint32_t kadv_a, uint32_t kadv_b, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (kCta == 1) {
+    if constexpr (kKind == kKindF8) TLB200_UMMA4("1", "f8f6f4");
+    else if constexpr (kKind == kKindTF32) TLB200_UMMA4("1", "tf32");
+    else if constexpr (kKind == kKindI8) TLB200_UMMA4("1", "i8");
+    else TLB200_UMMA4("1", "f16");
+  } else {
+    if constexpr (kKind == kKindF8) TLB200_UMMA4("2", "f8f6f4");
+    else if constexpr (kKind == kKindTF32) TLB200_UMMA4("2", "tf32");
+    else if constexpr (kKind == kKindI8) TLB200_UMMA4("2", "i8");
+    else TLB200_UMMA4("2", "f16");
+  }
+}
+#undef TLB200_UMMA4
 
 // Make `bar` observe completion of every tcgen05.mma this thread issued so far.
 // (implies tcgen05.fence::before_thread_sync).  For a pair the arrive is multicast to the

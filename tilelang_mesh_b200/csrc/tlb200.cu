@@ -47,6 +47,7 @@ AddrRangeFn g_addr_range = nullptr;
 RetainHandleFn g_retain_handle = nullptr;
 ReleaseHandleFn g_release_handle = nullptr;
 bool g_no_multicast = false;  // TLB200_NO_MULTICAST=1 in the environment: the A-multicast plan is never used
+int g_kgroup = 0;             // TLB200_KGROUP=1|2|4 in the environment: K blocks per stage barrier of narrow tiles (0 = automatic)
 std::mutex g_init_mu;
 constexpr int kMaxDevices = 64;
 std::atomic<int> g_sm_count[kMaxDevices];   // zero-initialised (static storage)
@@ -939,6 +940,8 @@ int tlb200_init(int device) {
       g_release_handle = reinterpret_cast<ReleaseHandleFn>(bind("cuMemRelease"));
       const char* nm = getenv("TLB200_NO_MULTICAST");
       g_no_multicast = nm && nm[0] && nm[0] != '0';
+      const char* kgs = getenv("TLB200_KGROUP");
+      if (kgs && (kgs[0] == '1' || kgs[0] == '2' || kgs[0] == '4') && !kgs[1]) g_kgroup = kgs[0] - '0';
     }
     // Same step as the generated init(): raise the dynamic shared memory limit (wrapper.py:15-21).
     e = cudaSuccess;
@@ -993,6 +996,8 @@ int tlb200_init(int device) {
 #ifdef TLB200_TRACE
 static long long* g_trace = nullptr;
 extern "C" void tlb200_debug_set_trace(long long* p) { g_trace = p; }
+static int g_debug_mode = 0;
+extern "C" void tlb200_debug_set_mode(int mode) { g_debug_mode = mode; }
 #endif
 
 static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, void* c, void* ws, int64_t ws_bytes,
@@ -1132,6 +1137,21 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     grid = static_cast<int>(clusters < 1 ? 1 : clusters) * pl.cta_group;
   }
   kp.raster = pl.raster;
+  {
+    // Reciprocals of the work-item decomposition's divisors (GemmKernelParams::magic_*): the high 64 bits of
+    // x * ceil(2^64 / d) are x / d for every 32-bit x when d >= 2; 0 stands for d <= 1.
+    const int mcf = r.mc == 2 ? 2 : 1;
+    const long long tiles_n_c = (kp.tiles_n + mcf - 1) / mcf;
+    const long long tiles_mn = kp.tiles_m * tiles_n_c;
+    auto magic = [](long long dv) -> unsigned long long {
+      return dv <= 1 ? 0ull : ~0ull / static_cast<unsigned long long>(dv) + 1ull;
+    };
+    kp.magic_tiles_mn = magic(tiles_mn);
+    kp.magic_group = magic(kp.raster * tiles_n_c);
+    kp.magic_raster = magic(kp.raster);
+    kp.magic_last_rows = magic(kp.raster > 0 ? kp.tiles_m % kp.raster : 0);
+    kp.magic_tail_tiles = magic(tail ? r.tail_tiles : 0);
+  }
   kp.block_n = pl.block_n;
   kp.umma_n = r.umma_n;
   kp.n_sub = r.n_sub;
@@ -1167,8 +1187,18 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   if (!split) {  // with split-K the reduction kernel applies them to the summed slices
     kp.row_scale = rv.row_scale; kp.col_scale = rv.col_scale; kp.bias = rv.bias; kp.bias_per_row = rv.bias_per_row;
   }
+  // Narrow tiles (one accumulator, <= 128 columns) are bound by the per-barrier hand-shake of the stage ring, not by
+  // the tensor pipe: two K blocks share a barrier pair (four for <= 32 columns) when the ring keeps >= 3 groups.
+  kp.kgroup = 1;
+  if (pl.block_n <= 128 && r.n_sub == 1) {
+    int kgw = pl.block_n <= 32 ? 4 : 2;
+    if (g_kgroup > 0) kgw = g_kgroup;
+    while (kgw > 1 && pl.stages / kgw < 3) kgw >>= 1;
+    kp.kgroup = kgw;
+  }
 #ifdef TLB200_TRACE
   kp.trace = g_trace;
+  kp.debug_mode = g_debug_mode;
 #endif
 
   cudaLaunchConfig_t cfg;

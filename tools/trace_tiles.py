@@ -12,6 +12,7 @@ cfg = {}
 for a in sys.argv[1:]:
     if "=" in a:
         kk, v = a.split("="); cfg[kk] = int(v)
+debug_mode = cfg.pop("debug", 0)  # development knobs of the traced build (GemmKernelParams::debug_mode); the product is garbage
 lib = _abi.load()
 lib.tlb200_debug_set_trace.argtypes = [ctypes.c_void_p]
 a = torch.randn(m, k, device="cuda").to(dt); b = torch.randn(n, k, device="cuda").to(dt)
@@ -19,17 +20,34 @@ c = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
 tr = torch.zeros(256 * 16, dtype=torch.int64, device="cuda")
 for _ in range(3): G.gemm(a, b, c, **cfg)
 torch.cuda.synchronize()
+if "cold" in sys.argv:  # read 512 MB first: the traced call finds nothing of its operands in L2
+    torch.empty(512 << 20, dtype=torch.uint8, device="cuda").view(torch.int64).sum().item()
 lib.tlb200_debug_set_trace(tr.data_ptr())
+lib.tlb200_debug_set_mode(debug_mode)
 G.gemm(a, b, c, **cfg)
 torch.cuda.synchronize()
 lib.tlb200_debug_set_trace(None)
+lib.tlb200_debug_set_mode(0)
 t = tr.cpu().view(-1, 16)
 if "small" in sys.argv:
     r = t[0].tolist(); z = r[13]
     names = {13: "kernel entry", 14: "set-up done (barriers, TMEM, cluster sync)", 11: "producer issues first K block", 0: "MMA warp holds accumulator",
-             1: "first K block landed", 2: "last commit issued", 3: "epilogue sees accumulator full", 4: "epilogue: accumulator handed back", 15: "epilogue warp done"}
+             12: "producer warp 0 has issued its 3rd K block (blocks 0, 3, 6; no stage was waited for)", 1: "first K block landed", 2: "last commit issued", 3: "epilogue sees accumulator full", 4: "epilogue: accumulator handed back", 15: "epilogue warp done"}
     for k in sorted(names, key=lambda k: r[k]):
         print(f"{r[k]-z:8d} cycles  {names[k]}")
+    if r[9]:  # -DTLB200_TRACE_WAIT builds only (two clock reads per K block perturb the loop they measure)
+        print(f"MMA warp waited for operand data {r[9]} cycles of the {r[2]-r[1]} between the first K block and the last commit")
+    else:
+        print(f"main loop: {r[2]-r[1]} cycles between the first K block landing and the last commit")
+    q = t[200].tolist()
+    if q[0]:
+        print(f"producer warp 0 after set-up: +{q[0]-r[14]} role dispatch, +{q[1]-q[0]} L2 policy, +{q[2]-q[1]} griddepcontrol.wait, +{q[3]-q[2]} tile coordinates, +{r[11]-q[3]} K range -> first issue")
+    print("K block | producer: starts waiting for the stage, +wait, +expect_tx, +A issue, +B issue | MMA thread sees the operands (after the B issue)")
+    for kb in range(64):
+        q = t[64 + kb].tolist()
+        if not q[0]:
+            continue
+        print(f"    {kb:2d} | {q[4]-z:7d} {q[0]-q[4]:6d} {q[1]-q[0]:5d} {q[2]-q[1]:5d} {q[3]-q[2]:5d} | {q[8]-z:7d} ({q[8]-q[3]:6d})")
     print("plan", G.plan_for(a, b, c, **cfg)); sys.exit(0)
 print("plan", G.plan_for(a, b, c, **cfg))
 rows = [r for r in t.tolist() if r[2] != 0]
