@@ -98,7 +98,11 @@ typedef struct tlb200_gemm_desc {
   /* ABI 2: which epilogue vectors tlb200_gemm_fused is given (ignored by every other entry point, which treat
    * them as absent).  All vectors are float32. */
   uint32_t vec_flags;    /* TLB200_VEC_* */
-  int32_t reserved2[3];  /* must be 0 */
+  int32_t reserved2[3];  /* [0] = cfg_kgroup: K blocks (pipeline stages) that share one full / empty barrier pair in
+                          *       tiles of at most 128 columns - 0 auto (2; 4 for tiles of <= 32 columns), else 1, 2 or 4
+                          *       (lowered when the stage ring would keep fewer than 3 groups; wider tiles always use 1;
+                          *       TLB200_KGROUP in the environment at tlb200_init sets the automatic value);
+                          * [1], [2] must be 0 */
 } tlb200_gemm_desc;
 
 /* Epilogue vectors ("bias / per-row scales"; the per-row form is the scales_a[m, kb] of

@@ -254,6 +254,18 @@ def test_tuning_knobs_do_not_change_results(cfg):
     assert bit_equal(G.gemm(a, b, **cfg), base)  # same K order per element => identical bits
 
 
+@pytest.mark.parametrize("kgroup", [1, 2, 4])
+@pytest.mark.parametrize("cfg", [dict(cta_group=1, block_n=64), dict(cta_group=2, block_n=64), dict(cta_group=2, block_n=128),
+                                 dict(cta_group=1, block_n=32, stages=5), dict(cta_group=4, block_n=64), dict(cta_group=2, block_n=96)])
+@pytest.mark.parametrize("k", [64, 192, 448, 1160])  # 1, 3, 7 and 19 K blocks (the last one partial): groups end ragged
+def test_stage_groups_do_not_change_results(kgroup, cfg, k):
+    """K blocks that share a barrier pair (cfg_kgroup) change the hand-shake, not the arithmetic: same bits as one K
+    block per barrier, for K-block counts that are not multiples of the group and more tiles than CTAs."""
+    a, b = operands(700, 8200 if cfg["block_n"] <= 64 else 9300, k, torch.bfloat16)
+    base = G.gemm(a, b, cta_group=1, block_n=256, epilogue=1)
+    assert bit_equal(G.gemm(a, b, kgroup=kgroup, **cfg), base)
+
+
 # ------------------------------------------------------------------ tf32 and int8 operands
 # testing/python/kernel/test_tilelang_kernel_gemm.py:156-247: f32f32f32 nn/nt/tn and i8i8i32 nt/tn at 512x1024x768
 @pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)], ids=["nn", "nt", "tn", "tt"])

@@ -177,7 +177,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
                 TLB200_ABI_VERSION);
   if (d->m < 0 || d->n < 0 || d->k < 0) return fail("tlb200: negative extent (m=%d n=%d k=%d)", d->m, d->n, d->k);
-  if (d->reserved2[0] || d->reserved2[1] || d->reserved2[2]) return fail("tlb200: descriptor field reserved2 must be zero");
+  if (d->reserved2[1] || d->reserved2[2]) return fail("tlb200: descriptor fields reserved2[1..2] must be zero");
+  if (d->reserved2[0] != 0 && d->reserved2[0] != 1 && d->reserved2[0] != 2 && d->reserved2[0] != 4)
+    return fail("tlb200: cfg_kgroup must be 0 (automatic), 1, 2 or 4 (got %d)", d->reserved2[0]);
   if (d->vec_flags & ~(TLB200_VEC_ROW_SCALE | TLB200_VEC_COL_SCALE | TLB200_VEC_BIAS_N | TLB200_VEC_BIAS_M))
     return fail("tlb200: unknown bits in vec_flags (0x%x)", d->vec_flags);
   if (!is_ab_dtype(d->ab_dtype))
@@ -1193,6 +1195,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   if (pl.block_n <= 128 && r.n_sub == 1) {
     int kgw = pl.block_n <= 32 ? 4 : 2;
     if (g_kgroup > 0) kgw = g_kgroup;
+    if (d->reserved2[0] > 0) kgw = d->reserved2[0];  // cfg_kgroup
     while (kgw > 1 && pl.stages / kgw < 3) kgw >>= 1;
     kp.kgroup = kgw;
   }

@@ -84,7 +84,7 @@ def _row_pitch(t: torch.Tensor, name: str) -> int:
 
 def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha=1.0, relu=False,
               cta_group=0, block_n=0, stages=0, raster=0, epilogue=0, epi_warps=0, split_k=0, l2_policy=0,
-              accumulate=False, vec_flags=0) -> _abi.GemmDesc:
+              accumulate=False, vec_flags=0, kgroup=0) -> _abi.GemmDesc:
     d = _abi.GemmDesc()
     d.abi_version = _abi.ABI_VERSION
     d.m, d.n, d.k = int(m), int(n), int(k)
@@ -99,6 +99,7 @@ def make_desc(m, n, k, ab_dtype, c_dtype, trans_a, trans_b, lda, ldb, ldc, alpha
     d.reserved[1] = int(split_k)
     d.reserved[2] = int(l2_policy)
     d.vec_flags = int(vec_flags)
+    d.reserved2[0] = int(kgroup)
     return d
 
 
