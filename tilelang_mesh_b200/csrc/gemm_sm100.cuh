@@ -409,7 +409,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
   auto release_accumulator = [&]() {
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) {
+    if (lane == 0 && tempty_bar != 0) {  // 0: no later tile waits for this accumulator (see the call site)
       if (tempty_remote) mbar_arrive_cluster(tempty_bar);
       else mbar_arrive(tempty_bar);
     }
@@ -1003,10 +1003,15 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         // Nothing to read (a fully out-of-range half-tile, or an output type this instantiation cannot produce - the
         // host rejects those): hand the accumulator straight back.  Otherwise epilogue_tile does so itself, as soon as
         // its last tcgen05.ld has completed.
+        // The hand-back of an accumulator that no later tile of this cluster will use is left out: nobody would wait
+        // for it, and as an arrive on the LEADER's barrier from the other CTA of a pair it would be the one remote
+        // operation of this kernel that is never observed by its target - which lets the teardown below do without a
+        // cluster-scope release (it compiles to MEMBAR.ALL.GPU and waits for every thread's stores to be acknowledged).
+        const bool acc_reused = t + (kNSub == 2 ? 1 : acc_stages) * num_clusters < num_tiles;
         auto release_unread = [&]() {
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) {
+          if (lane == 0 && acc_reused) {
             if constexpr (kCta == 2) mbar_arrive_cluster(tempty_leader + 8 * bi);
             else mbar_arrive(bar_tempty + 8 * bi);
           }
@@ -1014,7 +1019,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         if (rows_in_range) {  // warp-uniform
           constexpr bool kAccInt = kKind == kKindI8;  // int8 operands accumulate in int32
 #define TLB_EPI(K) epilogue_tile<K, kAccInt>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter, \
-                                             (kCta == 2 ? tempty_leader : bar_tempty) + 8 * bi, kCta == 2)
+                                             acc_reused ? (kCta == 2 ? tempty_leader : bar_tempty) + 8 * bi : 0u, kCta == 2)
           switch (out_kind) {
             case kOutBF16: TLB_EPI(kOutBF16); break;
             case kOutF16: TLB_EPI(kOutF16); break;
@@ -1048,7 +1053,16 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   __syncwarp();  // re-converge the single-lane regions before the .aligned barriers
   if (warp == kEpiWarp0) TLB_TRACE(0, 15);  // first epilogue warp done with every tile
   tc_fence_before();
-  if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
+  // Execution order is all this barrier has to give: every remote operation on a CTA's shared memory (the pair's TMA
+  // loads crediting the leader's `full` barriers, the MMA thread's multicast commits, the hand-backs of accumulators
+  // that a later tile uses) has been OBSERVED by a thread of that CTA through an mbarrier wait before that thread can
+  // get here, and the staging slabs have been read by the stores (wait_group.read above).  A release arrive would
+  // add MEMBAR.ALL.GPU + ERRBAR per thread - the CTA then holds its SM until its global stores are acknowledged,
+  // ~0.6 us that the next kernel's set-up (programmatic dependent launch) can use.
+  if constexpr (kCluster > 1) {
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+  } else __syncthreads();
   tc_fence_after();
   if (warp == 2) tmem_dealloc<kCta>(tmem_base, tmem_cols);
 }
