@@ -80,7 +80,9 @@ typedef struct tlb200_gemm_desc {
   int64_t lda, ldb, ldc;
   float alpha;        /* scale_a*scale_b for per-tensor-scaled fp8; 1.0f otherwise */
   uint32_t epilogue;  /* TLB200_EPI_* */
-  int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles, 2 = 2-CTA cluster tiles, 4 = two such pairs per cluster
+  int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles (128 rows), 2 = 2-CTA cluster tiles (256 rows),
+                            3 = 2-CTA cluster tiles of 128 rows (64 per CTA; block_n a multiple of 64, K-contiguous A,
+                            not for tlb200_gemm_grouped or several destinations), 4 = two pairs of 2 per cluster
                             on neighbouring column tiles, every A box fetched once and TMA-multicast to both
                             (only when all of A is proven to lie in the current device's own memory, see
                             tlb200_is_own_device_memory - an error otherwise; chosen automatically under the

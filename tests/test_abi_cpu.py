@@ -133,7 +133,11 @@ def test_plan_rejects_bad_arguments(built_lib):
         G.plan(128, 128, 128, torch.float8_e4m3fn, torch.float8_e4m3fn, block_n=64, epilogue=2)
     assert G.plan(128, 64, 128, torch.float8_e4m3fn, torch.float8_e4m3fn)["epilogue"] == 1
     with pytest.raises(RuntimeError, match="cfg_cta_group"):
-        G.plan(128, 128, 128, cta_group=3)
+        G.plan(128, 128, 128, cta_group=5)
+    with pytest.raises(RuntimeError, match="cfg_cta_group=3"):
+        G.plan(64, 128, 128, cta_group=3)  # pairs of 64-row CTAs need more than 64 rows
+    h = G.plan(512, 2048, 4096, cta_group=3, block_n=128)
+    assert (h["cta_group"], h["block_m"], h["block_n"], h["tmem_cols"]) == (2, 128, 128, 128)
     with pytest.raises(RuntimeError, match="cfg_stages"):
         G.plan(128, 128, 128, stages=40)
     d = G.make_desc(8, 8, 8, _abi.BFLOAT16, _abi.BFLOAT16, 0, 1, 8, 8, 8)

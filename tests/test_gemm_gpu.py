@@ -266,6 +266,33 @@ def test_stage_groups_do_not_change_results(kgroup, cfg, k):
     assert bit_equal(G.gemm(a, b, kgroup=kgroup, **cfg), base)
 
 
+@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("dt,out", [(torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.float32), (torch.float16, torch.float16),
+                                    (torch.int8, torch.int32)])
+@pytest.mark.parametrize("m,n,k", [(65, 128, 64), (128, 256, 128), (300, 200, 136), (1000, 1200, 520), (512, 2048, 1160)])
+def test_pair_tiles_of_128_rows_bit_exact(bn, dt, out, m, n, k):
+    """cfg_cta_group = 3: cta_group::2 MMAs with M = 128, 64 rows per CTA, the accumulator laid out as two column halves
+    over the 128 TMEM lanes.  Integer-valued operands: every plan must give the oracle's bits."""
+    a, b = operands(m, n, k, dt, kind="int")
+    c = G.gemm(a, b, out_dtype=out, cta_group=3, block_n=bn)
+    assert bit_equal(c, G.gemm(a, b, out_dtype=out, cta_group=1, block_n=256, epilogue=1))
+    for extra in (dict(epilogue=1), dict(epi_warps=8) if bn >= 128 else dict(stages=3), dict(split_k=2), dict(kgroup=1)):
+        if "split_k" in extra and dt == torch.int8:
+            continue
+        assert bit_equal(G.gemm(a, b, out_dtype=out, cta_group=3, block_n=bn, **extra), c), extra
+
+
+def test_pair_tiles_of_128_rows_argument_errors():
+    a, b = operands(64, 128, 64, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="cfg_cta_group=3"):
+        G.gemm(a, b, cta_group=3, block_n=128)  # needs more than 64 rows
+    a, b = operands(256, 256, 64, torch.bfloat16)
+    with pytest.raises(RuntimeError, match="multiple of 64"):
+        G.gemm(a, b, cta_group=3, block_n=96)
+    with pytest.raises(RuntimeError, match="K-contiguous A"):
+        G.gemm(a.t().contiguous(), b, trans_a=True, cta_group=3, block_n=128)
+
+
 # ------------------------------------------------------------------ tf32 and int8 operands
 # testing/python/kernel/test_tilelang_kernel_gemm.py:156-247: f32f32f32 nn/nt/tn and i8i8i32 nt/tn at 512x1024x768
 @pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)], ids=["nn", "nt", "tn", "tt"])

@@ -106,6 +106,9 @@ struct alignas(64) GemmKernelParams {
   // raster, tiles_m % raster and tail_tiles.  Divisions by run-time values (~60 dependent instructions each) sat
   // between the set-up barrier and the first TMA issue of every CTA.
   unsigned long long magic_tiles_mn, magic_group, magic_raster, magic_last_rows, magic_tail_tiles;
+  int half_m;        // pair tiles of 128 rows: 64 rows per CTA (cta_group::2 MMAs with M = 128).  An accumulator then is
+                     // block_n / 2 TMEM columns over all 128 lanes: lanes [0, 64) hold rows 0-63 of the tile columns
+                     // [0, block_n / 2), lanes [64, 128) the same rows of columns [block_n / 2, block_n)
   int kgroup;        // K blocks per pipeline barrier (1, 2 or 4): `full` / `empty` [g] cover stages [g*kgroup, (g+1)*kgroup)
   long long* trace;  // development builds (-DTLB200_TRACE): per-tile clock64 stamps of CTA 0; null otherwise
   int debug_mode;    // development builds: 1 = issue no MMAs (stages are handed straight back), 2 = issue no TMA loads
@@ -291,7 +294,7 @@ struct EpiCtx {
   const GemmKernelParams& p;
   const EpiOut& o;
   uint32_t lane_taddr;  // TMEM address of this warp's lane quarter, column 0 of the accumulator
-  int q, lane, row0, row_limit, row_off, col0;
+  int q, lane, row0, row_limit, row_off, col0;  // q: which 32 rows of the CTA's part of the tile
   uint32_t stage_smem;
   int nslabs;
 };
@@ -384,8 +387,8 @@ __device__ __forceinline__ void epi_stage(const EpiCtx& e, int cs, const uint4 (
   ++slab_iter;
 }
 
-// Executed by the epilogue warps.  Warp `q` owns TMEM lanes / tile rows [32q, 32q+32) and the accumulator
-// columns [cbeg, cend).  tmem_acc = TMEM address of the accumulator (lane 0, first column).
+// Executed by the epilogue warps.  The warp owns TMEM lanes [32q, 32q+32), tile rows [32rq, 32rq+32) (rq == q except
+// for pair tiles of 128 rows) and the tile columns [cbeg, cend).  tmem_acc = TMEM address of tile column 0 in those lanes.
 //
 // The accumulator goes back to the MMA warp the moment this warp's LAST tcgen05.ld of it has completed: what
 // follows for that last slab (cast, wait for the TMA engine to have read the staging slab, st.shared, proxy fence,
@@ -393,7 +396,7 @@ __device__ __forceinline__ void epi_stage(const EpiCtx& e, int cs, const uint4 (
 // was held until the last store had been issued - 4.5k cycles per 128 x 256 accumulator, all of them exposed for a
 // tile that fills TMEM (profiles/r2_notes.md).
 template <int kOut, bool kAccInt>
-__device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const EpiOut& o, uint32_t tmem_acc, int q,
+__device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const EpiOut& o, uint32_t tmem_acc, int q, int rq,
                                               int lane, int row0, int row_limit, int row_off, int col0, int cbeg, int cend,
                                               uint32_t stage_smem, int nslabs, int& slab_iter, uint32_t tempty_bar,
                                               bool tempty_remote) {
@@ -401,7 +404,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
   constexpr int kColsPerSlab = 128 / kOB;   // fp32 columns that fill one 128 B staging row
   constexpr int kPacketsPerLd = 32 * kOB / 16;  // 16 B packets produced by one x32 load
   constexpr int kValsPerPacket = 16 / kOB;
-  const int grow = row0 + q * 32 + lane;  // global row of this thread
+  const int grow = row0 + rq * 32 + lane;  // global row of this thread (rq: which 32 rows; q: which 32 TMEM lanes)
   const uint32_t lane_taddr = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
   const float alpha = o.alpha;
   const bool relu = o.relu != 0;
@@ -418,9 +421,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmKernelParams& p, const E
   // A TMA store writes the warp's whole 32-row slab: use it only when all 32 rows belong to this tile's
   // row range (always true for an ordinary GEMM, where the tensor map clips at M; a grouped GEMM's last
   // row tile of a group falls back to predicated stores).
-  const bool slab_rows_ok = p.n_groups == 0 || row0 + q * 32 + 32 <= row_limit;
+  const bool slab_rows_ok = p.n_groups == 0 || row0 + rq * 32 + 32 <= row_limit;
   if (o.tma && slab_rows_ok) {
-    const EpiCtx e{p, o, lane_taddr, q, lane, row0, row_limit, row_off, col0, stage_smem, nslabs};
+    const EpiCtx e{p, o, lane_taddr, rq, lane, row0, row_limit, row_off, col0, stage_smem, nslabs};
     // slabs of this warp that hold at least one column of C (warp-uniform)
     int nsl = 0;
     for (int cs = cbeg; cs < cend && col0 + cs < o.n; cs += kColsPerSlab) ++nsl;
@@ -520,6 +523,10 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // ---- shared memory carve-up (1024 B aligned for the 128B swizzle pattern)
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int stages = p.stages;
+  const bool half_m = kCta == 2 && kNSub == 1 && kMc == 1 && p.half_m != 0;
+  const int rows_cta = half_m ? kBlockM / 2 : kBlockM;                       // tile rows of one CTA
+  const uint32_t a_stage_bytes = half_m ? kABytesPerStage / 2 : kABytesPerStage;
+  const int acc_w = half_m ? p.block_n / 2 : p.block_n;                      // TMEM columns of one accumulator
   const int kg = (kNSub == 2 || p.kgroup < 2) ? 1 : p.kgroup;  // K blocks (stages) per full / empty barrier pair
   const int groups = stages / kg;            // ring slots; stages beyond groups * kg stay unused
   constexpr int n_sub = kNSub;  // accumulators per tile (compile-time: a predicated-off tcgen05.mma is not free)
@@ -527,7 +534,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t b_sub_bytes = static_cast<uint32_t>(p.b_sub_bytes);
   const uint32_t b_stage_bytes = b_sub_bytes * n_sub;
   const uint32_t smem_a = smem_base;
-  const uint32_t smem_b = smem_a + stages * kABytesPerStage;
+  const uint32_t smem_b = smem_a + stages * a_stage_bytes;
   const uint32_t smem_epi = smem_b + stages * b_stage_bytes;
   const uint32_t smem_bar = smem_epi + p.epi_slabs * kEpiBufBytes;
   const uint32_t bar_full = smem_bar;                    // [stages]
@@ -550,7 +557,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
                        static_cast<uint32_t>(p.magic_tail_tiles) ^ static_cast<uint32_t>(p.kgroup);
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_tptr + 8 + 0 * warp), "r"(h) : "memory");
   }
-  const uint32_t acc_cols = static_cast<uint32_t>(p.block_n) * acc_stages;
+  const uint32_t acc_cols = static_cast<uint32_t>(acc_w) * acc_stages;
   const uint32_t tmem_cols = acc_cols <= 32u ? 32u : acc_cols <= 64u ? 64u : acc_cols <= 128u ? 128u
                              : acc_cols <= 256u ? 256u : 512u;
 
@@ -583,13 +590,13 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     tn = wq * kMc + (int)mc_idx;  // may equal tiles_n for the last odd tile: that pair computes zeros
     if (p.n_groups == 0) {
       grp = 0;
-      row_base = tm * kCta * kBlockM;
+      row_base = tm * kCta * rows_cta;
       row_limit = p.m;
     } else {
       int gi = 0;
       while (gi + 1 < p.n_groups && p.group_tile[gi + 1] <= tm) ++gi;
       grp = gi;
-      row_base = p.group_row[gi] + (tm - p.group_tile[gi]) * kCta * kBlockM;
+      row_base = p.group_row[gi] + (tm - p.group_tile[gi]) * kCta * rows_cta;
       row_limit = p.group_row[gi + 1];
     }
   };
@@ -621,7 +628,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
 #endif
     TLB_TRI(1);
     const int k0 = kb * kspan;
-    const uint32_t dst_a = smem_a + s * kABytesPerStage;
+    const uint32_t dst_a = smem_a + s * a_stage_bytes;
     const uint32_t dst_b = smem_b + s * b_stage_bytes;
     if (kmajor_single_box) {
       // Both operands K-contiguous, one box each (the benchmark layout): straight-line issue.  The general loops below
@@ -670,7 +677,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   auto operand_rows = [&](int t, int& row_a, int& row_b, int& kb_off) {
     int tm, tn, grp, row_base, row_limit;
     tile_coord(t, tm, tn, grp, row_base, row_limit);
-    row_a = row_base + (int)cta_rank * kBlockM;
+    row_a = row_base + (int)cta_rank * rows_cta;
     // group g's B is block g of the 2-D view: rows [g*b_group_rows, ...) (K-major) or K offset (N-major)
     const int b_goff = grp * p.b_group_rows;
     row_b = tn * p.block_n + (int)cta_rank * p.b_rows_per_cta + (p.b_mn_major ? 0 : b_goff);
@@ -809,7 +816,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       const uint64_t hi_b = static_cast<uint64_t>(p.desc_hi_b) << 32 | p.desc_lbo_b;
       const uint32_t kadv_a = p.kadv_a, kadv_b = p.kadv_b;
       const uint32_t a_lo0 = (smem_a & 0x3FFFFu) >> 4, b_lo0 = (smem_b & 0x3FFFFu) >> 4;
-      const uint32_t a_step = kABytesPerStage >> 4, b_step = b_stage_bytes >> 4, b_sub = b_sub_bytes >> 4;
+      const uint32_t a_step = a_stage_bytes >> 4, b_step = b_stage_bytes >> 4, b_sub = b_sub_bytes >> 4;
       const uint32_t umma_n = p.umma_n;
       int s = 0;
       uint32_t ph = 0;
@@ -849,7 +856,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
             mbar_wait(bar_tempty + 8 * as, aph ^ 1u, 1);  // epilogue has drained this accumulator
             tc_fence_after();
             TLB_TRACE((t - cluster_id) / num_clusters, 0);
-            const uint32_t d_tmem = tmem_base + as * p.block_n;
+            const uint32_t d_tmem = tmem_base + as * acc_w;
             int kb0, kb1;
             k_range(t, kb0, kb1);
             const bool more_tiles = t + num_clusters < num_tiles;
@@ -966,7 +973,12 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
     const uint32_t tempty_leader = (kCta == 2) ? mapa(bar_tempty, leader_rank) : bar_tempty;
     // Column range of this warp inside ONE accumulator (all warps drain accumulator 0, then 1).
     const int acc_width = (kNSub == 2) ? p.umma_n : p.block_n;
-    const int ccols = acc_width / (p.epi_warps >> 2);
+    // Pair tiles of 128 rows (half_m): this warp's lane quarter q holds tile rows [32 * (q & 1), +32) of the column half
+    // q >> 1, at TMEM columns [0, block_n / 2) - so the warp's columns start at col_half and its TMEM address is
+    // shifted back by as much (the epilogue adds the tile column to it).
+    const int rq = half_m ? (q & 1) : q;                           // which 32 rows of the CTA's part of the tile
+    const int col_half = half_m ? (q >> 1) * (p.block_n / 2) : 0;  // first tile column this warp can reach
+    const int ccols = (half_m ? acc_width / 2 : acc_width) / (p.epi_warps >> 2);
     int as = 0;
     uint32_t aph = 0;
     int slab_iter = 0;
@@ -975,9 +987,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       int tm, tn, grp, row_base, row_limit;
       tile_coord(t, tm, tn, grp, row_base, row_limit);
       const bool tail_item = tail_mode && t >= p.tail_begin;
-      const bool rows_in_range = row_base + (int)cta_rank * kBlockM < row_limit;
+      const bool rows_in_range = row_base + (int)cta_rank * rows_cta < row_limit;
       // a tail slice writes tile (t - tail_begin) of the workspace matrix, whole (the reduction clips to M x N)
-      const int row0 = (tail_item ? (t - p.tail_begin) * kCta * kBlockM : row_base) + (int)cta_rank * kBlockM;
+      const int row0 = (tail_item ? (t - p.tail_begin) * kCta * rows_cta : row_base) + (int)cta_rank * rows_cta;
       const int col0 = tail_item ? 0 : tn * p.block_n;
       const int row_off = (tail_mode ? 0 : fdiv(t, p.magic_tiles_mn)) * p.split_row_pitch;
       if (tail_item) row_limit = 0x7fffffff;
@@ -995,11 +1007,11 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         mbar_wait(bar_tfull + 8 * bi, aph, 3);
         tc_fence_after();
         if ((ew & 3) == 0) TLB_TRACE((t - cluster_id) / num_clusters, 3 + 2 * h + (ew >> 2) * 4);
-        const uint32_t acc = (kNSub == 2) ? tmem_base : tmem_base + as * p.block_n;  // column 0 of the tile
+        const uint32_t acc = ((kNSub == 2) ? tmem_base : tmem_base + as * acc_w) - col_half;  // column 0 of the tile
 #ifdef TLB200_TRACE
         o.trace_seq = (ew == 0 && h == 0) ? (t - cluster_id) / num_clusters : -1;
 #endif
-        const int cbeg = h * acc_width + chalf * ccols, cend = cbeg + ccols;
+        const int cbeg = h * acc_width + col_half + chalf * ccols, cend = cbeg + ccols;
         // Nothing to read (a fully out-of-range half-tile, or an output type this instantiation cannot produce - the
         // host rejects those): hand the accumulator straight back.  Otherwise epilogue_tile does so itself, as soon as
         // its last tcgen05.ld has completed.
@@ -1018,7 +1030,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         };
         if (rows_in_range) {  // warp-uniform
           constexpr bool kAccInt = kKind == kKindI8;  // int8 operands accumulate in int32
-#define TLB_EPI(K) epilogue_tile<K, kAccInt>(p, o, acc, q, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter, \
+#define TLB_EPI(K) epilogue_tile<K, kAccInt>(p, o, acc, q, rq, lane, row0, row_limit, row_off, col0, cbeg, cend, my_stage, nslabs, slab_iter, \
                                              acc_reused ? (kCta == 2 ? tempty_leader : bar_tempty) + 8 * bi : 0u, kCta == 2)
           switch (out_kind) {
             case kOutBF16: TLB_EPI(kOutBF16); break;

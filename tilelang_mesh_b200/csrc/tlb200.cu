@@ -146,6 +146,7 @@ struct Resolved {
   bool a_mn, b_mn;
   int n_sub, umma_n, acc_stages, epi_warps, epi_slabs;
   int mc;                 // 2 = clusters of two pairs sharing every A box by TMA multicast, else 1
+  int half;               // 1 = pair tiles of 128 rows (64 per CTA, cta_group::2 MMAs with M = 128)
   int b_rows_per_cta;
   int num_k_blocks;
   bool epi_tma, epi_lsu;
@@ -171,7 +172,8 @@ constexpr bool kAutoMc = true;  // multicast plans are chosen automatically
 int mc_clusters_of(int sms) { return (g_mc_clusters > 0 && sms == g_mc_clusters_sms) ? g_mc_clusters : sms * 33 / 148; }
 
 int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved* r, bool allow_split = false,
-            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = false, bool allow_tail = true) {
+            const void* a_ptr = nullptr, const void* b_ptr = nullptr, bool allow_mc = false, bool allow_tail = true,
+            bool allow_half = true) {
   if (!d) return fail("tlb200: null descriptor");
   if (d->abi_version != TLB200_ABI_VERSION)
     return fail("tlb200: descriptor abi_version %d, library speaks %d", d->abi_version,
@@ -227,8 +229,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
 
   tlb200_gemm_plan& p = r->plan;
   memset(&p, 0, sizeof(p));
-  if (d->cfg_cta_group < 0 || d->cfg_cta_group == 3 || d->cfg_cta_group > 4)
-    return fail("tlb200: cfg_cta_group must be 0, 1, 2 or 4 (got %d)", d->cfg_cta_group);
+  if (d->cfg_cta_group < 0 || d->cfg_cta_group > 4)
+    return fail("tlb200: cfg_cta_group must be 0, 1, 2, 3 or 4 (got %d)", d->cfg_cta_group);
   if (d->reserved[1] < -1 || d->reserved[1] > 64)
     return fail("tlb200: cfg_split_k must be in [0,64], or -1 to force the tail split (got %d)", d->reserved[1]);
   if (d->reserved[1] > 1 && d->ab_dtype == TLB200_INT8) return fail("tlb200: split-K is not offered for int8 (partial sums are kept in fp32)");
@@ -237,7 +239,14 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   // spans per CTA.  Tiles wider than 256 columns (two accumulators sharing one A stage: 25 % less
   // L2->SM traffic) fill the 512 TMEM columns, so their accumulator is single-buffered.
   // cfg_cta_group = 4: pairs (cta_group::2 MMAs) in clusters of two pairs that share A by multicast
-  const int cfg_cg = d->cfg_cta_group == 4 ? 2 : d->cfg_cta_group;
+  // cfg_cta_group = 3: pairs whose tile is 128 rows (64 per CTA): for the same tile area a CTA stages fewer operand
+  // bytes per K block than with 128 rows and half the columns, and narrow tiles are bound by exactly those bytes
+  bool half = d->cfg_cta_group == 3;
+  const bool half_possible = allow_half && !r->a_mn && d->m > kBlockM / 2;
+  if (half && !half_possible)
+    return fail("tlb200: cfg_cta_group=3 (pairs of 64-row CTAs) needs a K-contiguous A, m > %d and an ordinary (not grouped, "
+                "single-destination) contraction", kBlockM / 2);
+  const int cfg_cg = (d->cfg_cta_group == 4 || half) ? 2 : d->cfg_cta_group;
   int cg = cfg_cg, bn = d->cfg_block_n, auto_split = 1, mc = d->cfg_cta_group == 4 ? 2 : 1;
   const int sms_all = sm_count > 0 ? sm_count : 148;
   const int mc_clusters = mc_clusters_of(sms_all);
@@ -252,26 +261,36 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     //   K-block cycles per CTA = 2*block_n / eff(cta_group, block_n)   (512 for a 256-wide tile)
     //   eff: how well the operand feed keeps the tensor pipe busy for that tile shape (measured at
     //   4096^3); wide tiles get a bonus for their lower power per flop but expose one epilogue per tile.
+    // mc = 3 marks the pair tiles of 128 rows (64 per CTA): a CTA then stages 8 KB of A and block_n / 2 rows of B per
+    // K block, and a narrow tile's K block costs its bytes at ~82 B/clk (profiles/r2_notes.md section 12)
     struct Cand { int cg, bn, mc; double eff; };
     const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.89}, {2, 128, 1, 0.90}, {1, 128, 1, 0.75},
                           {1, 64, 1, 0.45}, {2, 64, 1, 0.58}, {1, 32, 1, 0.31},
-                          {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64}};
+                          {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64},
+                          {2, 128, 3, 1.28}, {2, 256, 3, 1.70}};
     const int nkb = (d->k + r->span - 1) / r->span;
     double best = 1e300;
     int best_cg = 0, best_bn = 0, best_split = 1, best_mc = 1;
-    for (const Cand& c : cands) {
+    for (const Cand& c0 : cands) {
+      Cand c = c0;
+      const bool c_half = c.mc == 3;
+      if (c_half) {
+        c.mc = 1;
+        if (!half_possible || (d->cfg_cta_group != 0 && d->cfg_cta_group != 3) || d->cfg_epilogue >= 2 && (c.bn / 2) % (128 / r->ob)) continue;
+      } else if (half) continue;
       if (c.mc == 2 && d->cfg_cta_group != 4 && (!kAutoMc || c.bn != 256)) continue;  // measured: only 256-wide tiles gain
       if (cfg_cg && c.cg != cfg_cg) continue;
       if (c.mc == 2 && (!mc_possible || d->cfg_cta_group == 2 || d->n <= c.bn)) continue;
       if (c.mc == 1 && d->cfg_cta_group == 4) continue;
       if (d->cfg_block_n && c.bn != d->cfg_block_n) continue;
-      if (c.cg == 2 && (d->m <= kBlockM || sms_all < 2)) continue;
+      if (c.cg == 2 && ((d->m <= kBlockM && !c_half) || sms_all < 2)) continue;
       if (c.bn == 512 && (r->es != 2 || d->n < 512)) continue;  // 8-bit operands: double-buffered tiles measure faster
       if (c.bn > 32 && c.bn / 2 >= d->n && c.bn != d->cfg_block_n) continue;  // tile twice wider than the matrix
       const int step = r->b_mn ? r->span * c.cg : 32;
       if ((c.bn > 256 ? c.bn / 2 : c.bn) % step) continue;
       if (d->cfg_epilogue >= 2 && (c.bn > 256 ? c.bn / 2 : c.bn) % (128 / r->ob)) continue;  // staging slabs are 128 B wide
-      const long long tiles = static_cast<long long>((d->m + kBlockM * c.cg - 1) / (kBlockM * c.cg)) *
+      const int c_rows = c_half ? kBlockM : kBlockM * c.cg;
+      const long long tiles = static_cast<long long>((d->m + c_rows - 1) / c_rows) *
                               (((d->n + c.bn - 1) / c.bn + c.mc - 1) / c.mc);  // work items: c.mc column tiles each
       const long long clusters = c.mc == 2 ? mc_clusters : sms_all / c.cg;
       for (int split = 1; split <= 32; split *= 2) {
@@ -296,7 +315,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
           }
         }
         if (split > 1) total += 3000.0 + (static_cast<double>(split) * 4.0 + 2.0) * d->m * d->n / 2500.0;
-        if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; best_mc = c.mc; }
+        if (total < best) { best = total; best_cg = c.cg; best_bn = c.bn; best_split = split; best_mc = c_half ? 3 : c.mc; }
       }
     }
     if (best_cg == 0) {  // nothing matched the constraints: fall back to the smallest legal tile
@@ -305,7 +324,9 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
       best_bn = d->cfg_block_n ? d->cfg_block_n : (r->b_mn ? r->span * best_cg : 32);
     }
     cg = best_cg; bn = best_bn; auto_split = best_split; mc = best_mc;
+    if (mc == 3) { mc = 1; half = true; }
   }
+  r->half = half ? 1 : 0;
   if (sms_all < 2) cg = 1;
   const int n_step = r->b_mn ? r->span * cg : 32;
   r->n_sub = bn > 256 ? 2 : 1;
@@ -315,6 +336,8 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
                 bn, cg, r->b_mn ? ", N-major B" : "", n_step, n_step, 2 * n_step);
   if (mc == 2 && (r->n_sub != 1 || cg != 2))
     return fail("tlb200: cfg_cta_group=4 needs block_n <= 256");
+  if (half && (r->n_sub != 1 || cg != 2 || mc != 1 || bn % 64))
+    return fail("tlb200: cfg_cta_group=3 needs block_n a multiple of 64, at most 256");
   r->mc = mc;
   r->acc_stages = (2 * bn <= 512) ? 2 : 1;
   int ew = d->reserved[0];  // cfg_epi_warps
@@ -323,10 +346,10 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     ew = (bn > 256 && half % 32 == 0 && half % (128 / r->ob) == 0) ? 8 : 4;
   }
   if (ew != 4 && ew != 8) return fail("tlb200: cfg_epi_warps must be 0, 4 or 8 (got %d)", ew);
-  if ((r->umma_n / (ew / 4)) % 32) return fail("tlb200: block_n=%d cannot be split over %d epilogue warps", bn, ew);
+  if (((half ? r->umma_n / 2 : r->umma_n) / (ew / 4)) % 32) return fail("tlb200: block_n=%d cannot be split over %d epilogue warps", bn, ew);
   r->epi_warps = ew;
   r->b_rows_per_cta = r->umma_n / cg;
-  const int per_stage = kABytesPerStage + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
+  const int per_stage = (half ? kABytesPerStage / 2 : kABytesPerStage) + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
   int stages = d->cfg_stages;
   // Eight epilogue warps get two staging slabs each (so a slab can be refilled while the TMA store of the previous
   // one is still reading it) whenever at least three pipeline stages still fit, or the stage count the caller asked for.
@@ -340,7 +363,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (stages < 2 || stages > kMaxStages || stages > max_stages)
     return fail("tlb200: cfg_stages=%d out of range [2,%d]", stages, max_stages < kMaxStages ? max_stages : kMaxStages);
   p.cta_group = cg;
-  p.block_m = kBlockM * cg;
+  p.block_m = half ? kBlockM : kBlockM * cg;
   p.block_n = bn;
   p.block_k = r->span;
   p.stages = stages;
@@ -422,7 +445,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   const bool tma_ok = ((d->ldc * r->ob) % 16 == 0) && ((reinterpret_cast<uintptr_t>(c_ptr) % 16) == 0) &&
                       ((static_cast<long long>(d->n) * r->ob) % 16 == 0);
   // The TMA-store epilogue writes whole 128-byte-wide slabs: the tile must be a whole number of them.
-  const bool slab_ok = (r->umma_n / (r->epi_warps / 4)) % (128 / r->ob) == 0;
+  const bool slab_ok = ((half ? r->umma_n / 2 : r->umma_n) / (r->epi_warps / 4)) % (128 / r->ob) == 0;
   if (epi == 0) epi = (tma_ok && slab_ok) ? 2 : 1;
   if (epi >= 2 && !tma_ok) return fail("tlb200: the staged epilogues (cfg_epilogue 2, 3) need a 16-byte aligned C, row pitch and row length (n * element size)");
   if (epi >= 2 && !slab_ok)
@@ -431,11 +454,11 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   p.epilogue = epi;
   r->epi_tma = epi >= 2;
   r->epi_lsu = epi == 3;
-  const int acc_cols = bn * r->acc_stages;
+  const int acc_cols = (half ? bn / 2 : bn) * r->acc_stages;
   p.tmem_cols = acc_cols <= 32 ? 32 : acc_cols <= 64 ? 64 : acc_cols <= 128 ? 128 : acc_cols <= 256 ? 256 : 512;
   p.umma_n = r->umma_n;
   p.epi_warps = r->epi_warps;
-  p.instr_desc = instr_desc_impl(kBlockM * cg, r->umma_n, 32 / r->es, d->ab_dtype, d->ab_dtype == TLB200_INT8 ? TLB200_INT32 : TLB200_FLOAT32,
+  p.instr_desc = instr_desc_impl(p.block_m, r->umma_n, 32 / r->es, d->ab_dtype, d->ab_dtype == TLB200_INT8 ? TLB200_INT32 : TLB200_FLOAT32,
                                  !r->a_mn, !r->b_mn, 1, 1);
   if (p.instr_desc == 0) return fail("tlb200: cannot encode instruction descriptor");
   return 0;
@@ -766,17 +789,18 @@ int current_device_ready(int* dev_out) {
 int plan_call(const tlb200_gemm_desc* d, int dev, const void* a, const void* b, const void* c, const void* ws,
               int64_t ws_bytes, int n_peer, int n_groups, Resolved* r) {
   // never with grouped row tiles (not paired across column tiles) nor on the multi-GPU entry point
-  bool allow_mc = n_groups == 0 && n_peer == 0 && !g_no_multicast;
+  const bool plain = n_groups == 0 && n_peer == 0;  // the pair tiles of 128 rows are offered to ordinary contractions only
+  bool allow_mc = plain && !g_no_multicast;
   const int sms = g_sm_count[dev].load();
   for (int attempt = 0; attempt < 2; ++attempt) {
-    if (int rc = resolve(d, sms, c, r, ws != nullptr, a, b, allow_mc)) return rc;
+    if (int rc = resolve(d, sms, c, r, ws != nullptr, a, b, allow_mc, true, plain)) return rc;
     if (r->split_k > 1 && !ws) return fail("tlb200_gemm: cfg_split_k=%d needs a workspace: call tlb200_gemm_ex", d->reserved[1]);
     if (r->ws_bytes > 0) {
       if (reinterpret_cast<uintptr_t>(ws) % 256) return fail("tlb200_gemm_ex: workspace must be 256-byte aligned");
       if (ws_bytes < r->ws_bytes && r->split_k > 1 && d->reserved[1] <= 1) {
         tlb200_gemm_desc d1 = *d;  // automatic split does not fit the workspace: run unsplit
         d1.reserved[1] = 1;
-        if (int rc = resolve(&d1, sms, c, r, true, a, b, allow_mc)) return rc;
+        if (int rc = resolve(&d1, sms, c, r, true, a, b, allow_mc, true, plain)) return rc;
       }
       if (ws_bytes < r->ws_bytes)
         return fail("tlb200_gemm_ex: this call needs a %lld-byte workspace (%lld for re-pitched operands, %lld for split-K x%d), got %lld",
@@ -1073,7 +1097,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     // A problem shorter than one tile (decode-time shapes) fetches only the rows it has, rounded up to the 8-row
     // swizzle atom: the other rows of the stage feed accumulator rows that are never stored, and filling them
     // with zeros would still cost the SM's TMA write bandwidth (the bound for such shapes).
-    int a_box_rows = kBlockM / r.mc;
+    int a_box_rows = r.half ? kBlockM / 2 : kBlockM / r.mc;
     if (pl.cta_group == 1 && n_groups == 0 && d->m < kBlockM) a_box_rows = (d->m + 7) / 8 * 8;
     if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, a_box_rows, "A[M,K]")) return rc;
     kp.a_boxes = 1; kp.a_box_bytes = a_box_rows * kStageRowBytes;
@@ -1191,6 +1215,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   }
   // Narrow tiles (one accumulator, <= 128 columns) are bound by the per-barrier hand-shake of the stage ring, not by
   // the tensor pipe: two K blocks share a barrier pair (four for <= 32 columns) when the ring keeps >= 3 groups.
+  kp.half_m = r.half;
   kp.kgroup = 1;
   if (pl.block_n <= 128 && r.n_sub == 1) {
     int kgw = pl.block_n <= 32 ? 4 : 2;
@@ -1276,6 +1301,7 @@ int tlb200_gemm_grouped(const tlb200_gemm_desc* d, const void* a, const void* b,
   if (total != d->m) return fail("tlb200_gemm_grouped: group rows sum to %lld but desc.m = %d", total, d->m);
   if (d->trans_a) return fail("tlb200_gemm_grouped: A must be [sum_rows, K] (transpose_A = 0)");
   if (d->reserved[1] > 1) return fail("tlb200_gemm_grouped: split-K is not offered for grouped contractions");
+  if (d->cfg_cta_group == 3) return fail("tlb200_gemm_grouped: cfg_cta_group=3 is not offered for grouped contractions");
   tlb200_gemm_desc d1 = *d;
   d1.reserved[1] = 1;
   if (d1.cfg_block_n == 0 && d1.cfg_cta_group == 0) {  // tiles must not waste rows on small groups
@@ -1295,6 +1321,7 @@ int tlb200_gemm_bcast(const tlb200_gemm_desc* d, const void* a, const void* b, v
       return fail("tlb200_gemm_bcast: destination %d is aligned differently from destination 0", g);
   }
   if (d && d->reserved[1] > 1) return fail("tlb200_gemm_bcast: split-K cannot be combined with multiple destinations");
+  if (d && d->cfg_cta_group == 3 && n_c > 1) return fail("tlb200_gemm_bcast: cfg_cta_group=3 is not offered with multiple destinations");
   if (d && (d->epilogue & TLB200_EPI_ACCUMULATE)) return fail("tlb200_gemm_bcast: TLB200_EPI_ACCUMULATE is not offered with multiple destinations");
   // Stores into peer memory drain at NVLink speed, so a tile's epilogue takes several times longer than on one GPU.
   // A 512-wide tile fills TMEM (single-buffered accumulator) and would expose all of that to the tensor pipe: the
