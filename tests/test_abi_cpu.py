@@ -113,7 +113,7 @@ def test_plan_split_k(built_lib):
     # decode-like skinny shape: 16 tiles for 148 SMs and K = 14336 -> K is cut into slices
     p = G.plan(128, 4096, 14336)
     assert p["split_k"] >= 4 and p["workspace_bytes"] == p["split_k"] * 128 * 4096 * 4
-    assert p["grid"] == min(148, p["tiles_m"] * p["tiles_n"] * p["split_k"])
+    assert p["grid"] == min(148 // p["cta_group"], p["tiles_m"] * p["tiles_n"] * p["split_k"]) * p["cta_group"]
     assert G.plan(128, 4096, 14336, split_k=1)["split_k"] == 1
     assert G.plan(256, 256, 16384)["split_k"] > 1
     assert G.plan(8192, 8192, 8192)["split_k"] == 1 and G.plan(8192, 8192, 8192)["workspace_bytes"] == 0

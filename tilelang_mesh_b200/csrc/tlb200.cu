@@ -264,10 +264,13 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     // mc = 3 marks the pair tiles of 128 rows (64 per CTA): a CTA then stages 8 KB of A and block_n / 2 rows of B per
     // K block, and a narrow tile's K block costs its bytes at ~82 B/clk (profiles/r2_notes.md section 12)
     struct Cand { int cg, bn, mc; double eff; };
-    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.89}, {2, 128, 1, 0.90}, {1, 128, 1, 0.75},
-                          {1, 64, 1, 0.45}, {2, 64, 1, 0.58}, {1, 32, 1, 0.31},
+    // Tiles narrower than 256 columns: eff = 2 * block_n / (bytes one CTA stages per K block / 82 B per clock), the
+    // measured main-loop pace since the stage barriers are grouped (245 / 269 / 319 / 406 cycles for 256x64, 256x128,
+    // 128x64, 128x128; tools/tune_b2b.py is the check: which shapes still have a better explicit plan, and by how much).
+    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.89}, {2, 128, 1, 0.95}, {1, 128, 1, 0.63},
+                          {1, 64, 1, 0.40}, {2, 64, 1, 0.52}, {1, 32, 1, 0.26},
                           {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64},
-                          {2, 128, 3, 1.28}, {2, 256, 3, 1.70}};
+                          {2, 64, 3, 0.85}, {2, 128, 3, 1.28}, {2, 256, 3, 1.70}};
     const int nkb = (d->k + r->span - 1) / r->span;
     double best = 1e300;
     int best_cg = 0, best_bn = 0, best_split = 1, best_mc = 1;
@@ -299,8 +302,23 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
         const long long items = tiles * split;
         const long long waves = (items + clusters - 1) / clusters;
         const double kb = static_cast<double>((nkb + split - 1) / split);
-        double tile = kb * 2.0 * c.bn / c.eff + (c.bn > 256 ? 8000.0 : 0.0);
-        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? 3000.0 : 0.0);  // pairs start ~1.5 us later
+        // K-block cycles: 2 * block_n / eff for the 256- and 512-wide tiles (calibrated on whole runs); narrower tiles
+        // and the 128-row pairs from what bounds them (profiles/r2_notes.md sections 12, 13): the bytes one CTA stages
+        // at ~82 B/clk, the tensor pipe (MACs, or its operand reads at 128 B/clk), the barrier hand-shake per group.
+        double kb_cycles = 2.0 * c.bn / c.eff;
+        if (c.mc == 1 && (c.bn < 256 || c_half)) {
+          const int rows_cta = c_half ? kBlockM / 2 : kBlockM;
+          const int a_rows = (c.cg == 1 && d->m < kBlockM) ? (d->m + 7) / 8 * 8 : rows_cta;  // short problems fetch only their rows
+          const int b_rows = c.bn / c.cg;
+          const double bytes = (a_rows + b_rows) * 128.0 / 82.0;
+          const double mma = rows_cta * c.bn / 256.0, reads = (rows_cta + b_rows) / 4.0;
+          const double pipe = 4.0 * (mma > reads ? mma : reads);
+          const double shake = 300.0 / (c.bn <= 32 ? 4 : c.bn <= 128 ? 2 : 1);
+          kb_cycles = bytes > pipe ? bytes : pipe;
+          if (shake > kb_cycles) kb_cycles = shake;
+        }
+        double tile = kb * kb_cycles + (c.bn > 256 ? 8000.0 : 0.0);
+        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? ((c.bn >= 256 && !c_half) ? 3000.0 : 1500.0) : 0.0);  // pairs start later (cluster launch and sync)
         if (split == 1 && allow_split && allow_tail && d->reserved[1] != 1 && c.mc == 1 && c.bn <= 256 && d->ab_dtype != TLB200_INT8 &&
             items > clusters && items % clusters != 0) {
           // the tail split (decided below) shortens the last, partial wave to 1/S of a wave plus a small reduction

@@ -102,20 +102,22 @@ def reset():
 
 # ------------------------------------------------------------------------------------------------ measuring
 def plan_space(m: int, n: int, k: int, es: int) -> Iterable[dict]:
-    """Explicit plans worth timing for an (m, n, k) problem with `es`-byte operands: {1, 2, 4 CTAs per cluster} x
+    """Explicit plans worth timing for an (m, n, k) problem with `es`-byte operands: {1, 2, 2 x 64 rows, 4 CTAs per cluster} x
     tile width x K slices (x raster for many-tile problems).  `resolve()` rejects what is not legal for the shape."""
     yield {}
     widths = [w for w in (32, 64, 128, 256, 512) if w // 2 < n or w == 32]
     kb = -(-k * es // 128)
-    for cg in (1, 2, 4):
-        if cg >= 2 and m <= 128:
+    for cg in (1, 2, 3, 4):
+        if cg in (2, 4) and m <= 128 or cg == 3 and m <= 64:
             continue
         for bn in widths:
             if bn == 512 and (cg != 2 or es != 2):
                 continue
             if cg == 4 and (bn > 256 or n <= bn):
                 continue
-            tiles = -(-m // (128 * min(cg, 2))) * -(-n // bn)
+            if cg == 3 and (bn % 64 or bn > 256):  # pair tiles of 128 rows
+                continue
+            tiles = -(-m // (128 if cg == 3 else 128 * min(cg, 2))) * -(-n // bn)
             splits = [1]
             if cg != 4 and tiles < 148 and kb >= 16:
                 splits += [s for s in (2, 4, 8, 16) if kb // s >= 8 and tiles * s <= 2 * 148]
