@@ -41,8 +41,8 @@ M_PER_GPU, N_DIM, K_DIM = 8192, 8192, 8192
 NOMINAL = {"bf16": 2250.0, "fp8": 4500.0}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel bench.py times, from the
 # `ncu --set full` captures named in NCU_TRAFFIC_SOURCE (8192^3, default plan).
-NCU_DRAM_TRAFFIC = {"bf16": 849_556_480 + 120_777_984, "fp8": 230_059_264 + 118_074_624}
-NCU_TRAFFIC_SOURCE = {"bf16": "profiles/prof_bf16_r2b.txt", "fp8": "profiles/prof_fp8_r2b.txt"}
+NCU_DRAM_TRAFFIC = {"bf16": 850_035_456 + 120_999_680, "fp8": 230_059_264 + 118_074_624}
+NCU_TRAFFIC_SOURCE = {"bf16": "profiles/prof_bf16_r2c.txt", "fp8": "profiles/prof_fp8_r2b.txt"}
 NVLINK_GBS = 770.0  # measured unidirectional NVLink rate per GPU on this pool (profiles/r1_notes.md)
 METRIC = {"bf16": "GEMM TFLOP/s (bf16, 8192^3 per GPU, fp32 accumulate)",
           "fp8": "GEMM TFLOP/s (fp8 e4m3, 8192^3 per GPU, per-tensor scales, fp32 accumulate)"}
