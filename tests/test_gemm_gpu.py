@@ -97,16 +97,20 @@ def test_ragged_shapes_bit_exact(m, n, k, cg):
     assert torch.equal(c, want)
 
 
-def test_untouched_outside_of_c_window():
-    # C is a strided window of a larger buffer: nothing outside [m, n] may be written
+@pytest.mark.parametrize("cfg", [dict(), dict(cta_group=3, block_n=128), dict(cta_group=3, block_n=64), dict(cta_group=3, block_n=256, epi_warps=8),
+                                 dict(cta_group=2, block_n=64, kgroup=4)], ids=["auto", "h128", "h64", "h256w8", "c2n64g4"])
+def test_untouched_outside_of_c_window(cfg):
+    # C is a strided window of a larger buffer: nothing outside [m, n] may be written (rows above and below, columns right)
     m, n, k, ldc = 200, 136, 64, 160
     a, b = operands(m, n, k, torch.bfloat16, kind="int")
     for epi in (1, 2):
-        big = torch.full((m + 3, ldc), -7.0, device="cuda", dtype=torch.bfloat16)
-        c = big[:m, :n]
-        G.gemm(a, b, c, epilogue=epi)
+        if epi == 2 and cfg.get("block_n") == 64 and cfg.get("cta_group") == 3:
+            continue  # 32 columns per warp do not fill a 128-byte staging slab of bf16
+        big = torch.full((m + 6, ldc), -7.0, device="cuda", dtype=torch.bfloat16)
+        c = big[3:m + 3, :n]
+        G.gemm(a, b, c, epilogue=epi, **cfg)
         assert torch.equal(c.float(), a.float() @ b.float().t())
-        assert (big[:, n:] == -7).all() and (big[m:] == -7).all()
+        assert (big[:, n:] == -7).all() and (big[m + 3:] == -7).all() and (big[:3] == -7).all()
 
 
 @pytest.mark.parametrize("dt,n,pad", [(torch.bfloat16, 500, 12), (torch.float16, 1001, 7), (torch.float32, 333, 3),
