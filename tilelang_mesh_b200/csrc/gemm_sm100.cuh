@@ -38,7 +38,7 @@ constexpr int kMaxThreads = 384;      // 4 control warps + up to 8 epilogue warp
 constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple of 4)
 constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
 constexpr int kEpiSlabs = 8;               // staging slabs per CTA by default: 4 warps x 2 or 8 warps x 1 (32 KiB); 16 = 8 warps x 2
-constexpr int kMaxStages = 12;
+constexpr int kMaxStages = 32;  // small stages (short problems, narrow tiles) want many: cold operands are latency-bound by the bytes in flight
 constexpr int kMaxGroups = 64;   // grouped GEMM: row groups of A/C, each with its own B
 constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
@@ -106,6 +106,9 @@ struct alignas(64) GemmKernelParams {
   // raster, tiles_m % raster and tail_tiles.  Divisions by run-time values (~60 dependent instructions each) sat
   // between the set-up barrier and the first TMA issue of every CTA.
   unsigned long long magic_tiles_mn, magic_group, magic_raster, magic_last_rows, magic_tail_tiles;
+  int a_stage_bytes; // shared-memory bytes between consecutive A stages: 16 KB (128 rows); 8 KB with half_m; the rows actually
+                     // fetched, in whole 8-row swizzle atoms, for a problem shorter than one tile (the MMA still reads 128
+                     // rows - what lies behind the fetched ones feeds accumulator rows that are never stored)
   int half_m;        // pair tiles of 128 rows: 64 rows per CTA (cta_group::2 MMAs with M = 128).  An accumulator then is
                      // block_n / 2 TMEM columns over all 128 lanes: lanes [0, 64) hold rows 0-63 of the tile columns
                      // [0, block_n / 2), lanes [64, 128) the same rows of columns [block_n / 2, block_n)
@@ -525,7 +528,7 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const int stages = p.stages;
   const bool half_m = kCta == 2 && kNSub == 1 && kMc == 1 && p.half_m != 0;
   const int rows_cta = half_m ? kBlockM / 2 : kBlockM;                       // tile rows of one CTA
-  const uint32_t a_stage_bytes = half_m ? kABytesPerStage / 2 : kABytesPerStage;
+  const uint32_t a_stage_bytes = static_cast<uint32_t>(p.a_stage_bytes);
   const int acc_w = half_m ? p.block_n / 2 : p.block_n;                      // TMEM columns of one accumulator
   const int kg = (kNSub == 2 || p.kgroup < 2) ? 1 : p.kgroup;  // K blocks (stages) per full / empty barrier pair
   const int groups = stages / kg;            // ring slots; stages beyond groups * kg stay unused

@@ -147,6 +147,8 @@ struct Resolved {
   int n_sub, umma_n, acc_stages, epi_warps, epi_slabs;
   int mc;                 // 2 = clusters of two pairs sharing every A box by TMA multicast, else 1
   int half;               // 1 = pair tiles of 128 rows (64 per CTA, cta_group::2 MMAs with M = 128)
+  int a_stage_bytes;      // shared-memory bytes per A stage (GemmKernelParams::a_stage_bytes)
+  bool short_m;           // the problem is shorter than one single-CTA tile: A boxes hold only its rows
   int b_rows_per_cta;
   int num_k_blocks;
   bool epi_tma, epi_lsu;
@@ -367,7 +369,11 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
   if (((half ? r->umma_n / 2 : r->umma_n) / (ew / 4)) % 32) return fail("tlb200: block_n=%d cannot be split over %d epilogue warps", bn, ew);
   r->epi_warps = ew;
   r->b_rows_per_cta = r->umma_n / cg;
-  const int per_stage = (half ? kABytesPerStage / 2 : kABytesPerStage) + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
+  // A problem shorter than one tile (decode-time shapes) fetches only the rows it has, rounded up to the 8-row swizzle
+  // atom, and its A stages are that small: more stages fit, and with cold operands the bytes in flight are the pace.
+  r->short_m = allow_half && cg == 1 && !r->a_mn && d->m < kBlockM;
+  r->a_stage_bytes = half ? kABytesPerStage / 2 : r->short_m ? (d->m + 7) / 8 * 8 * kStageRowBytes : kABytesPerStage;
+  const int per_stage = r->a_stage_bytes + r->n_sub * r->b_rows_per_cta * kStageRowBytes;
   int stages = d->cfg_stages;
   // Eight epilogue warps get two staging slabs each (so a slab can be refilled while the TMA store of the previous
   // one is still reading it) whenever at least three pipeline stages still fit, or the stage count the caller asked for.
@@ -1116,7 +1122,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
     // swizzle atom: the other rows of the stage feed accumulator rows that are never stored, and filling them
     // with zeros would still cost the SM's TMA write bandwidth (the bound for such shapes).
     int a_box_rows = r.half ? kBlockM / 2 : kBlockM / r.mc;
-    if (pl.cta_group == 1 && n_groups == 0 && d->m < kBlockM) a_box_rows = (d->m + 7) / 8 * 8;
+    if (r.short_m) a_box_rows = (d->m + 7) / 8 * 8;
     if (int rc = encode_2d(&kp.tm_a, d->ab_dtype, a, d->m, d->k, lda, bk, a_box_rows, "A[M,K]")) return rc;
     kp.a_boxes = 1; kp.a_box_bytes = a_box_rows * kStageRowBytes;
   } else {
@@ -1234,6 +1240,7 @@ static int gemm_impl(const tlb200_gemm_desc* d, const void* a, const void* b, vo
   // Narrow tiles (one accumulator, <= 128 columns) are bound by the per-barrier hand-shake of the stage ring, not by
   // the tensor pipe: two K blocks share a barrier pair (four for <= 32 columns) when the ring keeps >= 3 groups.
   kp.half_m = r.half;
+  kp.a_stage_bytes = r.a_stage_bytes;
   kp.kgroup = 1;
   if (pl.block_n <= 128 && r.n_sub == 1) {
     int kgw = pl.block_n <= 32 ? 4 : 2;
