@@ -82,7 +82,7 @@ typedef struct tlb200_gemm_desc {
   uint32_t epilogue;  /* TLB200_EPI_* */
   int32_t cfg_cta_group; /* 0 auto, 1 = single-CTA tiles (128 rows), 2 = 2-CTA cluster tiles (256 rows),
                             3 = 2-CTA cluster tiles of 128 rows (64 per CTA; block_n a multiple of 64, K-contiguous A,
-                            not for tlb200_gemm_grouped or several destinations), 4 = two pairs of 2 per cluster
+                            one destination; tlb200_gemm_grouped takes it only when asked by name), 4 = two pairs of 2 per cluster
                             on neighbouring column tiles, every A box fetched once and TMA-multicast to both
                             (only when all of A is proven to lie in the current device's own memory, see
                             tlb200_is_own_device_memory - an error otherwise; chosen automatically under the

@@ -368,7 +368,8 @@ def torch_gmm(a, b, rows, trans_b):
 
 @pytest.mark.parametrize("rows", [[64, 128, 512, 33], [300, 0, 1, 700, 256], [4096, 4096], [7] * 40, [129, 255, 257, 511]])
 @pytest.mark.parametrize("trans_b", [False, True], ids=["b_kn", "b_nk"])
-@pytest.mark.parametrize("cfg", [dict(), dict(cta_group=1, block_n=128), dict(cta_group=2, block_n=256)], ids=["auto", "c1", "c2"])
+@pytest.mark.parametrize("cfg", [dict(), dict(cta_group=1, block_n=128), dict(cta_group=2, block_n=256), dict(cta_group=3, block_n=128),
+                                 dict(cta_group=3, block_n=256)], ids=["auto", "c1", "c2", "h128", "h256"])
 def test_grouped_gemm(rows, trans_b, cfg):
     k, n = 512, 768
     a = rand((sum(rows), k), torch.bfloat16, "int")

@@ -813,8 +813,10 @@ int current_device_ready(int* dev_out) {
 int plan_call(const tlb200_gemm_desc* d, int dev, const void* a, const void* b, const void* c, const void* ws,
               int64_t ws_bytes, int n_peer, int n_groups, Resolved* r) {
   // never with grouped row tiles (not paired across column tiles) nor on the multi-GPU entry point
-  const bool plain = n_groups == 0 && n_peer == 0;  // the pair tiles of 128 rows are offered to ordinary contractions only
-  bool allow_mc = plain && !g_no_multicast;
+  // the pair tiles of 128 rows: any single-destination contraction may ask for them, the automatic plan takes them for
+  // ordinary (not grouped) ones only
+  const bool plain = n_peer == 0 && (n_groups == 0 || d->cfg_cta_group == 3);
+  bool allow_mc = n_groups == 0 && n_peer == 0 && !g_no_multicast;
   const int sms = g_sm_count[dev].load();
   for (int attempt = 0; attempt < 2; ++attempt) {
     if (int rc = resolve(d, sms, c, r, ws != nullptr, a, b, allow_mc, true, plain)) return rc;
@@ -1326,7 +1328,6 @@ int tlb200_gemm_grouped(const tlb200_gemm_desc* d, const void* a, const void* b,
   if (total != d->m) return fail("tlb200_gemm_grouped: group rows sum to %lld but desc.m = %d", total, d->m);
   if (d->trans_a) return fail("tlb200_gemm_grouped: A must be [sum_rows, K] (transpose_A = 0)");
   if (d->reserved[1] > 1) return fail("tlb200_gemm_grouped: split-K is not offered for grouped contractions");
-  if (d->cfg_cta_group == 3) return fail("tlb200_gemm_grouped: cfg_cta_group=3 is not offered for grouped contractions");
   tlb200_gemm_desc d1 = *d;
   d1.reserved[1] = 1;
   if (d1.cfg_block_n == 0 && d1.cfg_cta_group == 0) {  // tiles must not waste rows on small groups
