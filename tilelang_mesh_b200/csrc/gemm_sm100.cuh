@@ -825,16 +825,6 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       uint32_t ph = 0;
       int as = 0;
       uint32_t aph = 0;
-      auto issue_kblock = [&](int stage, uint32_t d_tmem, uint32_t b_extra, bool first_kb) {
-        const uint32_t a_lo = a_lo0 + stage * a_step;
-        const uint32_t b_lo = b_lo0 + stage * b_step + b_extra;
-#pragma unroll
-        for (int k = 0; k < kStageRowBytes / kUmmaKBytes; ++k) {
-          const uint64_t da = hi_a | ((a_lo + k * kadv_a) & 0x3FFFu);
-          const uint64_t db = hi_b | ((b_lo + k * kadv_b) & 0x3FFFu);
-          umma_ss<kCta, kKind>(d_tmem, da, db, idesc, (first_kb && k == 0) ? 0u : 1u);
-        }
-      };
       if constexpr (kNSub == 1) {
         // Narrow tiles are bound by THIS loop, not by the tensor pipe or the loads.  tools/ubench/umma_pace.cu: a
         // 256x64 MMA runs every 43 cycles when issued back to back (172 per K block), but the pipe holds next to no
