@@ -124,6 +124,27 @@ def test_plan_split_k(built_lib):
         G.plan(128, 128, 1024, split_k=65)
 
 
+def test_plan_narrow_tiles_and_short_problems(built_lib):
+    """Host-side plan choices of profiles/r2_notes.md sections 12-16 (no GPU needed): the cycle model takes the pair tiles
+    of 128 rows where a CTA then stages the fewest bytes per K block, short problems get small A stages and many of them,
+    and the wide shapes keep their wide tiles."""
+    h = G.plan(512, 2048, 4096)
+    assert (h["cta_group"], h["block_m"], h["block_n"]) == (2, 128, 128) and h["stages"] >= 10 and h["tmem_cols"] == 128
+    assert G.plan(256, 4096, 4096)["block_m"] == 128
+    w = G.plan(8192, 8192, 8192)
+    assert (w["cta_group"], w["block_m"], w["block_n"], w["stages"]) == (2, 256, 512, 3)
+    assert G.plan(8192, 8192, 8192, torch.float8_e4m3fn, torch.bfloat16)["block_n"] == 256
+    assert G.plan(2048, 2048, 2048)["block_m"] in (128, 256) and G.plan(2048, 2048, 2048)["block_n"] == 256
+    # 64 rows: the A stage holds 64 rows (8 KB), not 128: twice the stages of a full-height tile of the same width
+    short, full = G.plan(64, 8192, 8192, cta_group=1, block_n=64), G.plan(128, 8192, 8192, cta_group=1, block_n=64)
+    assert short["stages"] > full["stages"] and short["smem_bytes"] <= 232448
+    assert G.plan(16, 4096, 4096, cta_group=1, block_n=32)["stages"] == 32  # the cap
+    for bad in (3, 5, -1):
+        with pytest.raises(RuntimeError, match="cfg_kgroup"):
+            G.plan(512, 512, 512, kgroup=bad)
+    assert G.plan(512, 512, 512, kgroup=4)["stages"] >= 2
+
+
 def test_plan_rejects_bad_arguments(built_lib):
     p = G.plan(128, 128, 100)  # K*2 bytes not a multiple of 16: operands are re-pitched through the workspace
     assert p["workspace_bytes"] == 2 * 128 * 128 * 2 and p["split_k"] == 1
