@@ -694,36 +694,39 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   // this CTA's barriers, which must not happen before the cluster-wide barrier, so pairs keep the ordinary order.
   const bool early_producer = kCluster == 1 && warp == 0;
 
+  // The ring's barrier pairs are initialised one per lane (at most 32 groups; only `groups` of the `stages` slots are
+  // used): a single thread looping over up to 64 mbarrier.init sat at the head of the producer's way to its first load.
+  static_assert(kMaxStages <= 32, "one lane per stage-group barrier pair");
   if (warp == 0) {
+    if constexpr (kCluster == 1) {
+      if (lane < groups) {
+        mbar_init(bar_full + 8 * lane, 1);
+        mbar_init(bar_empty + 8 * lane, 1);
+      }
+      fence_mbar_init();
+    }
     if (elect_one()) {
       tma_prefetch_desc(&p.tm_a);
       tma_prefetch_desc(&p.tm_b);
-      if constexpr (kCluster == 1) {
-        for (int s = 0; s < stages; ++s) {
-          mbar_init(bar_full + 8 * s, 1);
-          mbar_init(bar_empty + 8 * s, 1);
-        }
-        fence_mbar_init();
-      }
       if (p.epi_tma) {
         tma_prefetch_desc(&p.tm_c);
         for (int g = 0; g < p.n_peer; ++g) tma_prefetch_desc(&p.tm_c_peer[g]);
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      if constexpr (kCluster > 1) {
-        for (int s = 0; s < stages; ++s) {
-          mbar_init(bar_full + 8 * s, 1);   // producer's arrive.expect_tx (leader CTA only for a pair)
-          mbar_init(bar_empty + 8 * s, kMc);  // one tcgen05.commit per pair that reads the stage
-        }
+    if constexpr (kCluster > 1) {
+      if (lane < groups) {
+        mbar_init(bar_full + 8 * lane, 1);    // producer's arrive.expect_tx (leader CTA only for a pair)
+        mbar_init(bar_empty + 8 * lane, kMc);  // one tcgen05.commit per pair that reads the stages
       }
+    }
+    if (elect_one()) {
       for (int a = 0; a < 2; ++a) {
         mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
         mbar_init(bar_tempty + 8 * a, p.epi_warps * kCta);    // one arrive per epilogue warp (per CTA)
       }
-      fence_mbar_init();
     }
+    fence_mbar_init();
   } else if (warp == 2) {
     tmem_alloc<kCta>(smem_tptr, tmem_cols);
   }
