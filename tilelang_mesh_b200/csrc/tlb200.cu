@@ -268,7 +268,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
     // Tiles narrower than 256 columns: eff = 2 * block_n / (bytes one CTA stages per K block / 82 B per clock), the
     // measured main-loop pace since the stage barriers are grouped (245 / 269 / 319 / 406 cycles for 256x64, 256x128,
     // 128x64, 128x128; tools/tune_b2b.py is the check: which shapes still have a better explicit plan, and by how much).
-    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.89}, {2, 128, 1, 0.95}, {1, 128, 1, 0.63},
+    const Cand cands[] = {{2, 512, 1, 1.07}, {2, 256, 1, 1.0}, {1, 256, 1, 0.93}, {2, 128, 1, 0.95}, {1, 128, 1, 0.63},
                           {1, 64, 1, 0.40}, {2, 64, 1, 0.52}, {1, 32, 1, 0.26},
                           {2, 256, 2, kEffMc256}, {2, 128, 2, kEffMc128}, {2, 64, 2, kEffMc64},
                           {2, 64, 3, 0.85}, {2, 128, 3, 1.28}, {2, 256, 3, 1.70}};
@@ -319,7 +319,7 @@ int resolve(const tlb200_gemm_desc* d, int sm_count, const void* c_ptr, Resolved
           if (shake > kb_cycles) kb_cycles = shake;
         }
         double tile = kb * kb_cycles + (c.bn > 256 ? 8000.0 : 0.0);
-        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? ((c.bn >= 256 && !c_half) ? 3000.0 : 1500.0) : 0.0);  // pairs start later (cluster launch and sync)
+        double total = 3000.0 + waves * tile + (c.bn > 256 ? 0.0 : 12.0 * c.bn) + (c.cg == 2 ? ((c.bn >= 256 && !c_half) ? 3000.0 : 500.0) : 0.0);  // pairs start later (cluster launch and sync)
         if (split == 1 && allow_split && allow_tail && d->reserved[1] != 1 && c.mc == 1 && c.bn <= 256 && d->ab_dtype != TLB200_INT8 &&
             items > clusters && items % clusters != 0) {
           // the tail split (decided below) shortens the last, partial wave to 1/S of a wave plus a small reduction
