@@ -1330,9 +1330,16 @@ int tlb200_gemm_grouped(const tlb200_gemm_desc* d, const void* a, const void* b,
   tlb200_gemm_desc d1 = *d;
   d1.reserved[1] = 1;
   if (d1.cfg_block_n == 0 && d1.cfg_cta_group == 0) {  // tiles must not waste rows on small groups
-    long long biggest = 0;
-    for (int g = 0; g < n_groups; ++g) biggest = group_rows[g] > biggest ? group_rows[g] : biggest;
-    d1.cfg_cta_group = biggest > 192 ? 2 : 1;
+    // A row tile never spans two groups, so every group is padded to whole tiles: pairs (256 rows) only when some group is
+    // big enough to fill one and the padding they add over 128-row tiles stays under 15 % (a ragged mix of 8 ... 1000
+    // rows per group pads 30 % more with pairs: 418 vs 369 us; profiles/r2_notes.md section 20).
+    long long biggest = 0, pad256 = 0, pad128 = 0;
+    for (int g = 0; g < n_groups; ++g) {
+      biggest = group_rows[g] > biggest ? group_rows[g] : biggest;
+      pad256 += (group_rows[g] + 2 * kBlockM - 1) / (2 * kBlockM) * (2 * kBlockM);
+      pad128 += (group_rows[g] + kBlockM - 1) / kBlockM * kBlockM;
+    }
+    d1.cfg_cta_group = (biggest > 192 && pad256 * 100 <= pad128 * 115) ? 2 : 1;
   }
   return gemm_impl(&d1, a, b, c, nullptr, 0, stream_v, nullptr, 0, group_rows, n_groups);
 }
