@@ -183,7 +183,7 @@ int tlb200_gemm_fused(const tlb200_gemm_desc* desc, const void* a, const void* b
 /* Grouped contraction (the reference's examples/grouped_gemm: MoE expert
  * GEMMs): rows of A[sum_rows, K] and C[sum_rows, N] are cut into n_groups
  * consecutive row groups (group_rows[g] rows each, a HOST array, 0 allowed,
- * n_groups <= 64) and group g is multiplied by its own B block:
+ * n_groups <= 256) and group g is multiplied by its own B block:
  *   transpose_B = 1 : B is [n_groups, N, K]      transpose_B = 0 : B is [n_groups, K, N]
  * (blocks contiguous, ldb = row pitch).  desc.m = sum of group_rows.  One
  * persistent launch walks the row tiles of all groups; a tile never spans two

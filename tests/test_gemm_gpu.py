@@ -366,7 +366,8 @@ def torch_gmm(a, b, rows, trans_b):
     return torch.cat(out) if out else a.new_zeros((0, b.shape[1] if trans_b else b.shape[2])).float()
 
 
-@pytest.mark.parametrize("rows", [[64, 128, 512, 33], [300, 0, 1, 700, 256], [4096, 4096], [7] * 40, [129, 255, 257, 511]])
+@pytest.mark.parametrize("rows", [[64, 128, 512, 33], [300, 0, 1, 700, 256], [4096, 4096], [7] * 40, [129, 255, 257, 511],
+                                  [5, 0, 130] * 85 + [1], [64] * 128])  # the last two: 256 and 128 groups (expert counts of MoE layers)
 @pytest.mark.parametrize("trans_b", [False, True], ids=["b_kn", "b_nk"])
 @pytest.mark.parametrize("cfg", [dict(), dict(cta_group=1, block_n=128), dict(cta_group=2, block_n=256), dict(cta_group=3, block_n=128),
                                  dict(cta_group=3, block_n=256)], ids=["auto", "c1", "c2", "h128", "h256"])
@@ -389,7 +390,7 @@ def test_grouped_gemm_random_fp16_and_errors():
     with pytest.raises(ValueError, match="sum to"):
         G.gemm_grouped(a, b, [1, 2, 3, 4])
     with pytest.raises(RuntimeError, match="n_groups"):
-        G.gemm_grouped(rand((65, 64), torch.float16), rand((65, 64, 64), torch.float16), [1] * 65)
+        G.gemm_grouped(rand((257, 64), torch.float16), rand((257, 64, 64), torch.float16), [1] * 257)
 
 
 # ------------------------------------------------------------------ split-K (scratch workspace)

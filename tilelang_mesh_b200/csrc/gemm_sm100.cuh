@@ -39,7 +39,7 @@ constexpr int kEpiWarp0 = 4;          // first epilogue warp (must be a multiple
 constexpr int kEpiBufBytes = 32 * 128;     // one staging slab: 32 rows x 128 B
 constexpr int kEpiSlabs = 8;               // staging slabs per CTA by default: 4 warps x 2 or 8 warps x 1 (32 KiB); 16 = 8 warps x 2
 constexpr int kMaxStages = 32;  // small stages (short problems, narrow tiles) want many: cold operands are latency-bound by the bytes in flight
-constexpr int kMaxGroups = 64;   // grouped GEMM: row groups of A/C, each with its own B
+constexpr int kMaxGroups = 256;  // grouped GEMM: row groups of A/C, each with its own B (an expert count of current MoE layers)
 constexpr int kMaxPeerDst = 7;  // fused all-gather: a C tile is stored into up to 1 + 7 matrices
 constexpr int kABytesPerStage = kBlockM * kStageRowBytes;  // 16 KiB
 
@@ -596,8 +596,12 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
       row_base = tm * kCta * rows_cta;
       row_limit = p.m;
     } else {
-      int gi = 0;
-      while (gi + 1 < p.n_groups && p.group_tile[gi + 1] <= tm) ++gi;
+      int lo = 0, hi = p.n_groups - 1;  // the last group whose first tile is <= tm (empty groups share a first tile)
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (p.group_tile[mid] <= tm) lo = mid; else hi = mid - 1;
+      }
+      const int gi = lo;
       grp = gi;
       row_base = p.group_row[gi] + (tm - p.group_tile[gi]) * kCta * rows_cta;
       row_limit = p.group_row[gi + 1];
