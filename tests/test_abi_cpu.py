@@ -109,6 +109,35 @@ def test_plan_small_and_ragged(built_lib):
     assert p["cta_group"] == 2 and p["tiles_m"] == 2 and p["tiles_n"] == 1
 
 
+def test_plan_invariants_over_random_problems(built_lib):
+    """Whatever the cycle model picks must be a launchable, self-consistent plan: 600 random problems x 3 operand types."""
+    import random
+    rnd = random.Random(1234)
+    kSmemLimit = 232448
+    for i in range(600):
+        m = rnd.choice([1, 7, 16, 64, 65, 100, 128, 129, 256, 300, 512, 1000, 2048, 4096, 8192, rnd.randint(1, 9000)])
+        n = rnd.choice([8, 64, 128, 200, 256, 512, 1000, 2048, 4096, 7168, 14336, rnd.randint(8, 9000) // 8 * 8])
+        k = rnd.choice([16, 64, 128, 520, 1024, 4096, 8192, 14336, rnd.randint(16, 9000) // 16 * 16])
+        ab, cd = rnd.choice([(torch.bfloat16, torch.bfloat16), (torch.float8_e4m3fn, torch.bfloat16), (torch.float16, torch.float32)])
+        p = G.plan(m, n, k, ab, cd)
+        what = (m, n, k, ab, p)
+        assert p["cta_group"] in (1, 2) and p["block_m"] in (128, 256) and p["block_m"] <= 128 * p["cta_group"], what
+        assert 32 <= p["block_n"] <= 512 and p["block_n"] % 32 == 0 and p["umma_n"] in (p["block_n"], p["block_n"] // 2), what
+        assert p["tiles_m"] * p["block_m"] >= m > (p["tiles_m"] - 1) * p["block_m"], what
+        assert p["tiles_n"] * p["block_n"] >= n > (p["tiles_n"] - 1) * p["block_n"], what
+        assert 2 <= p["stages"] <= 32 and p["smem_bytes"] <= kSmemLimit, what
+        assert p["grid"] >= p["cta_group"] and p["grid"] % (p["cta_group"] * p["multicast"]) == 0 and p["grid"] <= 148, what
+        assert p["threads"] in (256, 384) and p["tmem_cols"] in (32, 64, 128, 256, 512), what
+        half = p["cta_group"] == 2 and p["block_m"] == 128
+        acc_cols = (p["block_n"] // 2 if half else p["block_n"]) * (2 if p["block_n"] <= 256 else 1)
+        assert p["tmem_cols"] >= min(acc_cols, 512), what
+        if half:
+            assert m > 64 and p["block_n"] % 64 == 0 and p["block_n"] <= 256, what
+        assert p["split_k"] >= 1 and (p["workspace_bytes"] > 0) == (p["split_k"] > 1 or (k * ab.itemsize) % 16 != 0 or p["workspace_bytes"] > 0), what
+        if p["split_k"] > 1:
+            assert p["workspace_bytes"] >= p["split_k"] * m * n * 4, what
+
+
 def test_plan_split_k(built_lib):
     # decode-like skinny shape: 16 tiles for 148 SMs and K = 14336 -> K is cut into slices
     p = G.plan(128, 4096, 14336)
