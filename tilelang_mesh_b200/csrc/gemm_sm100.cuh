@@ -544,7 +544,9 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   const uint32_t bar_empty = bar_full + 8 * stages;      // [stages]
   const uint32_t bar_tfull = bar_empty + 8 * stages;     // [2]
   const uint32_t bar_tempty = bar_tfull + 16;            // [2]
-  const uint32_t smem_tptr = bar_tempty + 16;            // u32 TMEM base address
+  const uint32_t bar_tmem = bar_tempty + 16;             // clusters: this CTA's tensor memory is allocated (1 arrive)
+  const uint32_t bar_tmem_pair = bar_tmem + 8;           // clusters, pair leader: both CTAs' tensor memory is (kCta arrives)
+  const uint32_t smem_tptr = bar_tmem_pair + 8;          // u32 TMEM base address
   // bytes that land in one stage: the A boxes actually issued (a short problem, M < 128, fetches only its own rows;
   // with A multicast each CTA issues half a box and receives the other half) plus the B rows, per CTA of the pair
   const uint32_t stage_tx_bytes = (static_cast<uint32_t>(p.a_boxes * p.a_box_bytes) * kMc + b_stage_bytes) * kCta;
@@ -729,15 +731,26 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
         mbar_init(bar_tfull + 8 * a, 1);                      // one tcgen05.commit
         mbar_init(bar_tempty + 8 * a, p.epi_warps * kCta);    // one arrive per epilogue warp (per CTA)
       }
+      if constexpr (kCluster > 1) {
+        mbar_init(bar_tmem, 1);
+        mbar_init(bar_tmem_pair, kCta);
+      }
     }
     fence_mbar_init();
   } else if (warp == 2) {
-    tmem_alloc<kCta>(smem_tptr, tmem_cols);
+    if constexpr (kCluster == 1) tmem_alloc<kCta>(smem_tptr, tmem_cols);
   }
   __syncwarp();
   tc_fence_before();
   if constexpr (kCluster > 1) {
-    cluster_sync_all();
+    // Clusters: the cluster-wide barrier only has to publish the mbarriers (the peer's loads and commits signal this CTA's),
+    // so the tensor-memory allocation (~270 cycles and a second warp's worth of latency) is taken out of its way: the
+    // producers start ~1k cycles earlier, the allocation runs next to their first loads and is announced through two
+    // mbarriers of its own - to this CTA's MMA and epilogue warps, and to the pair's leader, whose MMAs write both CTAs'.
+    // The arrive is relaxed: fence.mbarrier_init.release.cluster (above, by the initialising threads) is what publishes
+    // the barriers; a release arrive adds MEMBAR.ALL.GPU + ERRBAR to every thread's way through the set-up.
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
   } else {
     // named barrier 1 over the whole block: warp 0 only arrives (it needs neither the TMEM address nor the accumulator
     // barriers), everybody else waits for all arrivals
@@ -746,7 +759,26 @@ gemm_tcgen05_kernel(const __grid_constant__ GemmKernelParams p) {
   }
   tc_fence_after();
   uint32_t tmem_base = 0;
-  if (!early_producer) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+  if constexpr (kCluster > 1) {
+    if (warp == 2) {
+      tmem_alloc<kCta>(smem_tptr, tmem_cols);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(bar_tmem);
+        mbar_arrive_cluster(mapa(bar_tmem_pair, leader_rank));
+      }
+      __syncwarp();
+    }
+    if (warp == 1 || warp == 2 || warp >= kEpiWarp0) {  // producers 0 and 3 need no tensor memory
+      if (warp == 1 && leader) mbar_wait(bar_tmem_pair, 0, 5);  // the MMAs of a pair write both CTAs' accumulators
+      mbar_wait(bar_tmem, 0, 5);
+      tc_fence_after();
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+    }
+  } else {
+    if (!early_producer) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(smem_tptr) : "memory");
+  }
   // Programmatic dependent launch: everything above touched only this CTA's shared / tensor memory, so it may
   // overlap the tail of the previous kernel in the stream; the next kernel may start its own set-up now.  The warps
   // that read or write global memory wait for the previous grid first (producers before the first TMA load,

@@ -62,7 +62,7 @@ struct HostPipe {
 HostPipe g_pipe[kMaxDevices];
 
 constexpr int kSmemLimit = 232448;  // 227 KiB opt-in per block on sm_100
-constexpr int smem_fixed(int epi_slabs) { return 1024 /*alignment slack*/ + epi_slabs * kEpiBufBytes + (2 * kMaxStages + 4) * 8 + 16; }
+constexpr int smem_fixed(int epi_slabs) { return 1024 /*alignment slack*/ + epi_slabs * kEpiBufBytes + (2 * kMaxStages + 6) * 8 + 16; }
 
 int dtype_bytes(int dt) {
   switch (dt) {
