@@ -109,6 +109,26 @@ def test_plan_small_and_ragged(built_lib):
     assert p["cta_group"] == 2 and p["tiles_m"] == 2 and p["tiles_n"] == 1
 
 
+def test_reciprocal_division_is_exact():
+    """The kernel divides work-item indices by run-time tile counts as the high 64 bits of x * (floor((2^64 - 1) / d) + 1)
+    (GemmKernelParams::magic_*, csrc/tlb200.cu): exact for every 32-bit x and d >= 2.  Checked here in exact integer
+    arithmetic on the edge cases and 200k random pairs."""
+    import random
+    rnd = random.Random(7)
+    def magic(d): return ((1 << 64) - 1) // d + 1
+    edge_d = [2, 3, 5, 7, 74, 148, 255, 256, 257, 65535, 65536, 65537, (1 << 31) - 1, 1 << 31, (1 << 32) - 1]
+    edge_x = [0, 1, 2, 73, 74, 147, 148, 65535, 65536, (1 << 31) - 1, 1 << 31, (1 << 32) - 2, (1 << 32) - 1]
+    for d in edge_d:
+        assert magic(d) < (1 << 64)
+        for x in edge_x + [d - 1, d, d + 1, 2 * d - 1, 2 * d, 3 * d + 1]:
+            if 0 <= x < (1 << 32):
+                assert (x * magic(d)) >> 64 == x // d, (x, d)
+    for _ in range(200000):
+        d = rnd.randint(2, (1 << rnd.randint(2, 32)) - 1)
+        x = rnd.randint(0, (1 << 32) - 1)
+        assert (x * magic(d)) >> 64 == x // d, (x, d)
+
+
 def test_plan_invariants_over_random_problems(built_lib):
     """Whatever the cycle model picks must be a launchable, self-consistent plan: 600 random problems x 3 operand types."""
     import random
