@@ -20,7 +20,8 @@ logger = logging.getLogger("tilelang_mesh_b200")
 
 PLAN_CANDIDATES = [dict(), dict(cta_group=2, block_n=256, raster=8), dict(cta_group=2, block_n=256, raster=4),
                    dict(cta_group=2, block_n=256, raster=16), dict(cta_group=2, block_n=128), dict(cta_group=1, block_n=256),
-                   dict(cta_group=1, block_n=128)]
+                   dict(cta_group=1, block_n=128), dict(cta_group=3, block_n=128), dict(cta_group=3, block_n=64),
+                   dict(cta_group=2, block_n=64)]  # the last three: what small problems prefer (profiles/r2_notes.md 13-14)
 
 
 @dataclass
