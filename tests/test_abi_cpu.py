@@ -109,6 +109,30 @@ def test_plan_small_and_ragged(built_lib):
     assert p["cta_group"] == 2 and p["tiles_m"] == 2 and p["tiles_n"] == 1
 
 
+def test_shipped_plan_table_entries_are_legal_plans(built_lib):
+    """Every entry of the shipped measured-plan table must be a plan resolve() accepts for its problem (a stale or
+    mistyped entry would make the first gemm() of that shape fail instead of falling back to the cycle model)."""
+    import json, os
+    from tilelang_mesh_b200 import plan_cache as PC
+    table = json.load(open(PC.shipped_path(148)))
+    dts = {"bf16": torch.bfloat16, "f16": torch.float16, "e4m3": torch.float8_e4m3fn, "e5m2": torch.float8_e5m2, "f32": torch.float32,
+           "i8": torch.int8, "i32": torch.int32}
+    assert table, "the shipped table is empty"
+    for key, entry in table.items():
+        shape, types, lay = key.split("|")
+        m, n, k = (int(x) for x in shape.split("x"))
+        ab, cd = (dts[x] for x in types.split("->"))
+        cfg = entry["cfg"]
+        assert isinstance(cfg, dict) and cfg, key  # an entry that only repeats the automatic plan has no place in the table
+        assert set(cfg) <= {"cta_group", "block_n", "split_k", "raster", "stages", "epi_warps", "epilogue", "kgroup"}, (key, cfg)
+        p = G.plan(m, n, k, ab, cd, lay[0] == "T", lay[1] == "T", **cfg)
+        if "block_n" in cfg:
+            assert p["block_n"] == cfg["block_n"], (key, p)
+        if cfg.get("cta_group") == 3:
+            assert p["cta_group"] == 2 and p["block_m"] == 128, (key, p)
+        assert entry["us"] > 0 and (entry.get("auto_us") is None or entry["us"] <= entry["auto_us"]), key
+
+
 def test_reciprocal_division_is_exact():
     """The kernel divides work-item indices by run-time tile counts as the high 64 bits of x * (floor((2^64 - 1) / d) + 1)
     (GemmKernelParams::magic_*, csrc/tlb200.cu): exact for every 32-bit x and d >= 2.  Checked here in exact integer
