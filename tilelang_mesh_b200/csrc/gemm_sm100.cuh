@@ -15,13 +15,14 @@
 //                      predicated 16 B global stores)           (replaces copy.cc:1191-1377
 //                      tmem->fragment, copy.cc:920-958 fragment->shared->global)
 //
-// Tiles: BLOCK_M = 128 rows per CTA (256 per 2-CTA pair), BLOCK_N <= 256 columns,
-// BLOCK_K = 128 bytes of K per stage (64 x 16-bit or 128 x 8-bit elements) = one 128B
-// swizzle atom, consumed by 4 MMAs of K = 32 bytes each.  A static persistent scheduler walks
-// the tile grid in L2-friendly row groups (replaces threadblock_swizzle.h:7-41).
+// Tiles: BLOCK_M = 128 rows per CTA (256 per 2-CTA pair; 64 per CTA / 128 per pair with half_m), BLOCK_N <= 256
+// columns per accumulator (two accumulators for 512-wide tiles), BLOCK_K = 128 bytes of K per stage (64 x 16-bit or
+// 128 x 8-bit elements) = one 128B swizzle atom, consumed by 4 MMAs of K = 32 bytes each.  A static persistent
+// scheduler walks the tile grid in L2-friendly row groups (replaces threadblock_swizzle.h:7-41).
 //
-// Pipeline protocol = the reference's warp-specialised ring: parity
-// (k / stages) & 1, producer waits the inverted parity, expect_tx = bytes of the stage.
+// Pipeline protocol = the reference's warp-specialised ring: parity (k / stages) & 1, producer waits the
+// inverted parity, expect_tx = bytes of the stage - with `kgroup` consecutive stages behind one full / empty barrier
+// pair for narrow tiles, whose K block costs less than a barrier hand-shake does (profiles/r2_notes.md section 12).
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
